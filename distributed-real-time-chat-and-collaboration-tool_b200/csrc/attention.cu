@@ -1,0 +1,454 @@
+// Attention kernels (see attention.cuh for the oracle citations).
+//
+// prefill_attn_kernel : flash-style causal attention over packed ragged prompts. One CTA =
+//   64 query rows of one (sequence, head); 4 warps x 16 rows; K/V tiles of 64 keys staged in
+//   padded shared memory; QK^T and PV on the tensor cores (mma.sync m16n8k16 bf16, fp32
+//   accumulate); online softmax in fp32 registers. This is <= 8 % of prefill FLOPs for the
+//   BASELINE configs; the tcgen05 path is used for the GEMMs that dominate.
+//
+// decode_attn_kernel : one new token per sequence against the paged KV cache. HBM-bound:
+//   every K/V byte is read exactly once with 16-byte no-allocate loads, 8 lanes per cached
+//   token (one 128-byte row), 16 tokens (= one 2 KB page of a head) per CTA iteration, 4-way
+//   unrolled so each thread keeps 8 independent 16-byte loads in flight; softmax statistics
+//   by warp shuffles. Optional split-KV for long contexts with a deterministic combine pass.
+#include "attention.cuh"
+
+#include "common.cuh"
+#include "ops.cuh"
+
+namespace b200llm {
+
+namespace {
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kScaleLog2 = 0.125f * kLog2e;  // 1/sqrt(64) folded into the exp2 argument
+
+// ---------------------------------------------------------------------------------------
+// Prefill
+// ---------------------------------------------------------------------------------------
+constexpr int kBQ = 64;
+constexpr int kBKV = 64;
+constexpr int kLds = 72;  // padded smem row stride (bf16 elements): conflict-free ldmatrix
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* smem_ptr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_u32(smem_ptr)));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* smem_ptr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_u32(smem_ptr)));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0,
+                                               uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, "
+      "{%8, %9}, {%0, %1, %2, %3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ void load_tile_64x64(__nv_bfloat16 (*dst)[kLds],
+                                                const __nv_bfloat16* src, int ld, int rows_valid) {
+  // 64 rows x 8 chunks of 16 B; 128 threads -> 4 chunks each
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = threadIdx.x + 128 * i;
+    const int row = c >> 3;
+    const int col = (c & 7) * 8;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row < rows_valid) v = *reinterpret_cast<const uint4*>(src + static_cast<size_t>(row) * ld + col);
+    *reinterpret_cast<uint4*>(&dst[row][col]) = v;
+  }
+}
+
+__global__ void __launch_bounds__(128)
+prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ cu_seqlens,
+                    int n_head, __nv_bfloat16* __restrict__ out) {
+  __shared__ __align__(16) __nv_bfloat16 sQ[kBQ][kLds];
+  __shared__ __align__(16) __nv_bfloat16 sK[kBKV][kLds];
+  __shared__ __align__(16) __nv_bfloat16 sV[kBKV][kLds];
+
+  const int b = blockIdx.z;
+  const int h = blockIdx.y;
+  const int qt = blockIdx.x;
+  const int row0 = cu_seqlens[b];
+  const int len = cu_seqlens[b + 1] - row0;
+  if (qt * kBQ >= len) return;
+  const int d = n_head * kHeadDim;
+  const int ld = 3 * d;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int g = lane >> 2;  // row within the 8-row group
+  const int t = lane & 3;   // column pair
+
+  const __nv_bfloat16* q_base = qkv + static_cast<size_t>(row0 + qt * kBQ) * ld + h * kHeadDim;
+  load_tile_64x64(sQ, q_base, ld, len - qt * kBQ);
+  __syncthreads();
+
+  uint32_t qf[4][4];
+  {
+    const int i = lane >> 3, r = lane & 7;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      ldmatrix_x4(qf[ks], &sQ[warp * 16 + (i & 1) * 8 + r][ks * 16 + (i >> 1) * 8]);
+    }
+  }
+
+  float o[8][4];
+#pragma unroll
+  for (int n = 0; n < 8; ++n) {
+    o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
+  }
+  float m_run[2] = {-INFINITY, -INFINITY};
+  float l_run[2] = {0.f, 0.f};
+  const int qrow_lo = qt * kBQ + warp * 16 + g;  // this thread's rows: qrow_lo, qrow_lo + 8
+
+  for (int kt = 0; kt <= qt; ++kt) {
+    __syncthreads();  // previous tile fully consumed
+    const __nv_bfloat16* k_base =
+        qkv + static_cast<size_t>(row0 + kt * kBKV) * ld + d + h * kHeadDim;
+    load_tile_64x64(sK, k_base, ld, len - kt * kBKV);
+    load_tile_64x64(sV, k_base + d, ld, len - kt * kBKV);
+    __syncthreads();
+
+    float s[8][4];
+#pragma unroll
+    for (int n = 0; n < 8; ++n) {
+      s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f;
+    }
+    {
+      const int i = lane >> 3, r = lane & 7;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+        for (int np = 0; np < 4; ++np) {
+          uint32_t kf[4];
+          ldmatrix_x4(kf, &sK[np * 16 + (i >> 1) * 8 + r][ks * 16 + (i & 1) * 8]);
+          mma_bf16_16816(s[2 * np], qf[ks], kf[0], kf[1]);
+          mma_bf16_16816(s[2 * np + 1], qf[ks], kf[2], kf[3]);
+        }
+      }
+    }
+
+    // causal + length mask, row maxima
+    float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int n = 0; n < 8; ++n) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int col = kt * kBKV + n * 8 + 2 * t + (c & 1);
+        const int row = qrow_lo + (c >> 1) * 8;
+        if (col > row || col >= len) s[n][c] = -INFINITY;
+        mx[c >> 1] = fmaxf(mx[c >> 1], s[n][c]);
+      }
+    }
+    float alpha[2], m_use[2];
+#pragma unroll
+    for (int r2 = 0; r2 < 2; ++r2) {
+      mx[r2] = fmaxf(mx[r2], __shfl_xor_sync(0xffffffffu, mx[r2], 1));
+      mx[r2] = fmaxf(mx[r2], __shfl_xor_sync(0xffffffffu, mx[r2], 2));
+      const float m_new = fmaxf(m_run[r2], mx[r2]);
+      m_use[r2] = (m_new == -INFINITY) ? 0.f : m_new;  // fully masked row (beyond len)
+      alpha[r2] = (m_run[r2] == -INFINITY) ? 0.f : exp2f((m_run[r2] - m_use[r2]) * kScaleLog2);
+      m_run[r2] = m_new;
+      l_run[r2] *= alpha[r2];
+    }
+#pragma unroll
+    for (int n = 0; n < 8; ++n) {
+      o[n][0] *= alpha[0];
+      o[n][1] *= alpha[0];
+      o[n][2] *= alpha[1];
+      o[n][3] *= alpha[1];
+    }
+#pragma unroll
+    for (int n = 0; n < 8; ++n) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float p = exp2f((s[n][c] - m_use[c >> 1]) * kScaleLog2);  // exp2(-inf) = 0
+        s[n][c] = p;
+        l_run[c >> 1] += p;
+      }
+    }
+
+    // O += P V
+    {
+      const int i = lane >> 3, r = lane & 7;
+#pragma unroll
+      for (int ks2 = 0; ks2 < 4; ++ks2) {
+        uint32_t pf[4];
+        pf[0] = pack_bf16x2(s[2 * ks2][0], s[2 * ks2][1]);
+        pf[1] = pack_bf16x2(s[2 * ks2][2], s[2 * ks2][3]);
+        pf[2] = pack_bf16x2(s[2 * ks2 + 1][0], s[2 * ks2 + 1][1]);
+        pf[3] = pack_bf16x2(s[2 * ks2 + 1][2], s[2 * ks2 + 1][3]);
+#pragma unroll
+        for (int dp = 0; dp < 4; ++dp) {
+          uint32_t vf[4];
+          ldmatrix_x4_trans(vf, &sV[ks2 * 16 + (i & 1) * 8 + r][dp * 16 + (i >> 1) * 8]);
+          mma_bf16_16816(o[2 * dp], pf, vf[0], vf[1]);
+          mma_bf16_16816(o[2 * dp + 1], pf, vf[2], vf[3]);
+        }
+      }
+    }
+  }
+
+  // finalize
+#pragma unroll
+  for (int r2 = 0; r2 < 2; ++r2) {
+    l_run[r2] += __shfl_xor_sync(0xffffffffu, l_run[r2], 1);
+    l_run[r2] += __shfl_xor_sync(0xffffffffu, l_run[r2], 2);
+  }
+#pragma unroll
+  for (int r2 = 0; r2 < 2; ++r2) {
+    const int row = qrow_lo + r2 * 8;
+    if (row < len) {
+      const float inv = 1.0f / l_run[r2];
+      __nv_bfloat16* orow = out + static_cast<size_t>(row0 + row) * d + h * kHeadDim;
+#pragma unroll
+      for (int n = 0; n < 8; ++n) {
+        const uint32_t pk = pack_bf16x2(o[n][2 * r2] * inv, o[n][2 * r2 + 1] * inv);
+        *reinterpret_cast<uint32_t*>(orow + n * 8 + 2 * t) = pk;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Decode
+// ---------------------------------------------------------------------------------------
+struct Softmax8 {
+  float m;     // running max (log2 domain)
+  float l;     // running sum
+  float o[8];  // running weighted V for this lane's 8 dims
+};
+
+__device__ __forceinline__ void merge_into(Softmax8& a, float m2, float l2, const float (&o2)[8]) {
+  const float m = fmaxf(a.m, m2);
+  const float f1 = (a.m == -INFINITY) ? 0.f : exp2f(a.m - m);
+  const float f2 = (m2 == -INFINITY) ? 0.f : exp2f(m2 - m);
+  a.l = a.l * f1 + l2 * f2;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) a.o[i] = a.o[i] * f1 + o2[i] * f2;
+  a.m = m;
+}
+
+__device__ __forceinline__ void bf16x8_to_float(const uint4& v, float (&f)[8]) {
+  float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y), c = unpack_bf16x2(v.z),
+         d = unpack_bf16x2(v.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+  f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+
+constexpr int kDecUnroll = 4;
+constexpr int kScratchStride = kHeadDim + 2;  // o[64], m, l
+
+__global__ void __launch_bounds__(128) decode_attn_kernel(DecodeAttnArgs a) {
+  __shared__ float sm_o[4][kHeadDim];
+  __shared__ float sm_ml[4][2];
+
+  const int bh = blockIdx.x;
+  const int b = bh / a.n_head;
+  const int h = bh % a.n_head;
+  const int split = blockIdx.y;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane & 7;                // which 16-byte chunk (8 dims) of the 128-byte row
+  const int grp = warp * 4 + (lane >> 3);  // 0..15: token within the 16-token page
+  const int d = a.n_head * kHeadDim;
+
+  pdl_wait();
+  const int slot = a.active_slots ? a.active_slots[b] : b;
+  if (slot < 0) return;
+  const int pos = a.seq_len[slot];
+  const int ctx = pos + 1;
+  const bool fin = a.finished != nullptr && a.finished[slot] != 0;
+
+  const __nv_bfloat16* row = a.qkv + static_cast<size_t>(b) * 3 * d + h * kHeadDim + sub * 8;
+  float q[8];
+  {
+    const uint4 qv = *reinterpret_cast<const uint4*>(row);
+    bf16x8_to_float(qv, q);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) q[i] *= kScaleLog2;
+  }
+  const uint4 k_new = *reinterpret_cast<const uint4*>(row + d);
+  const uint4 v_new = *reinterpret_cast<const uint4*>(row + 2 * d);
+  const int32_t* pt = a.page_table + static_cast<size_t>(slot) * a.max_pages_per_seq;
+
+  if (split == 0 && !fin && warp == 0 && lane < 8) {
+    const int page = pt[pos / kPageTokens];
+    const size_t dst =
+        ((static_cast<size_t>(page) * a.n_head + h) * kPageTokens + pos % kPageTokens) * kHeadDim +
+        sub * 8;
+    *reinterpret_cast<uint4*>(a.k_pool + dst) = k_new;
+    *reinterpret_cast<uint4*>(a.v_pool + dst) = v_new;
+  }
+
+  int chunk = (ctx + a.n_splits - 1) / a.n_splits;
+  chunk = ((chunk + kPageTokens - 1) / kPageTokens) * kPageTokens;
+  const int t_begin = split * chunk;
+  const int t_end = min(ctx, t_begin + chunk);
+
+  Softmax8 acc;
+  acc.m = -INFINITY;
+  acc.l = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc.o[i] = 0.f;
+
+  for (int base = t_begin; base < t_end; base += kPageTokens * kDecUnroll) {
+    uint4 kv[kDecUnroll], vv[kDecUnroll];
+    bool valid[kDecUnroll];
+#pragma unroll
+    for (int u = 0; u < kDecUnroll; ++u) {
+      const int tpos = base + u * kPageTokens + grp;
+      valid[u] = tpos < t_end;
+      kv[u] = k_new;
+      vv[u] = v_new;
+      if (valid[u] && tpos != pos) {
+        const int page = pt[tpos / kPageTokens];
+        const size_t off =
+            ((static_cast<size_t>(page) * a.n_head + h) * kPageTokens + tpos % kPageTokens) *
+                kHeadDim + sub * 8;
+        kv[u] = ld_nc_v4(a.k_pool + off);
+        vv[u] = ld_nc_v4(a.v_pool + off);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kDecUnroll; ++u) {
+      float kf[8];
+      bf16x8_to_float(kv[u], kf);
+      float s = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s = fmaf(q[i], kf[i], s);
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      s += __shfl_xor_sync(0xffffffffu, s, 4);
+      if (valid[u]) {
+        float vf[8];
+        bf16x8_to_float(vv[u], vf);
+        const float m = fmaxf(acc.m, s);
+        const float f = (acc.m == -INFINITY) ? 0.f : exp2f(acc.m - m);
+        const float p = exp2f(s - m);
+        acc.l = acc.l * f + p;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc.o[i] = fmaf(p, vf[i], acc.o[i] * f);
+        acc.m = m;
+      }
+    }
+  }
+
+  // merge the 4 token groups of this warp (lanes differing in bits 3 and 4)
+#pragma unroll
+  for (int off = 8; off <= 16; off <<= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, acc.m, off);
+    const float l2 = __shfl_xor_sync(0xffffffffu, acc.l, off);
+    float o2[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o2[i] = __shfl_xor_sync(0xffffffffu, acc.o[i], off);
+    merge_into(acc, m2, l2, o2);
+  }
+  if (lane < 8) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sm_o[warp][sub * 8 + i] = acc.o[i];
+    if (lane == 0) {
+      sm_ml[warp][0] = acc.m;
+      sm_ml[warp][1] = acc.l;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < kHeadDim) {
+    const int dim = threadIdx.x;
+    float m = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) m = fmaxf(m, sm_ml[w][0]);
+    float l = 0.f, o = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float f = (sm_ml[w][0] == -INFINITY) ? 0.f : exp2f(sm_ml[w][0] - m);
+      l += sm_ml[w][1] * f;
+      o += sm_o[w][dim] * f;
+    }
+    if (a.n_splits == 1) {
+      a.out[static_cast<size_t>(b) * d + h * kHeadDim + dim] = __float2bfloat16(o / l);
+    } else {
+      float* sc = a.scratch + (static_cast<size_t>(bh) * a.n_splits + split) * kScratchStride;
+      sc[dim] = o;
+      if (dim == 0) {
+        sc[kHeadDim] = m;
+        sc[kHeadDim + 1] = l;
+      }
+    }
+  }
+  pdl_launch_dependents();
+}
+
+__global__ void __launch_bounds__(64) decode_combine_kernel(DecodeAttnArgs a) {
+  const int bh = blockIdx.x;
+  const int b = bh / a.n_head;
+  const int h = bh % a.n_head;
+  const int dim = threadIdx.x;
+  pdl_wait();
+  const int slot = a.active_slots ? a.active_slots[b] : b;
+  if (slot < 0) return;
+  const float* sc = a.scratch + static_cast<size_t>(bh) * a.n_splits * kScratchStride;
+  float m = -INFINITY;
+  for (int s = 0; s < a.n_splits; ++s) m = fmaxf(m, sc[s * kScratchStride + kHeadDim]);
+  float l = 0.f, o = 0.f;
+  for (int s = 0; s < a.n_splits; ++s) {
+    const float ms = sc[s * kScratchStride + kHeadDim];
+    const float f = (ms == -INFINITY) ? 0.f : exp2f(ms - m);
+    l += sc[s * kScratchStride + kHeadDim + 1] * f;
+    o += sc[s * kScratchStride + dim] * f;
+  }
+  const int d = a.n_head * kHeadDim;
+  a.out[static_cast<size_t>(b) * d + h * kHeadDim + dim] = __float2bfloat16(o / l);
+  pdl_launch_dependents();
+}
+
+int launch_with_pdl(void (*kernel)(DecodeAttnArgs), dim3 grid, dim3 block, cudaStream_t stream,
+                    int pdl, const DecodeAttnArgs& a) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, a));
+  return kOk;
+}
+
+}  // namespace
+
+int prefill_attention(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int batch,
+                      int max_seq_len, int n_head, __nv_bfloat16* out, cudaStream_t stream) {
+  B200_CHECK_ARG(batch > 0 && max_seq_len > 0 && n_head > 0, "prefill_attention: bad shape");
+  dim3 grid((max_seq_len + kBQ - 1) / kBQ, n_head, batch);
+  prefill_attn_kernel<<<grid, 128, 0, stream>>>(qkv, cu_seqlens, n_head, out);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+size_t decode_attention_scratch_floats(int batch, int n_head, int n_splits) {
+  if (n_splits <= 1) return 0;
+  return static_cast<size_t>(batch) * n_head * n_splits * kScratchStride;
+}
+
+int decode_attention(const DecodeAttnArgs& a, cudaStream_t stream) {
+  B200_CHECK_ARG(a.batch > 0 && a.n_head > 0 && a.n_splits >= 1, "decode_attention: bad shape");
+  B200_CHECK_ARG(a.n_splits == 1 || a.scratch != nullptr,
+                 "decode_attention: split-KV needs a scratch buffer");
+  dim3 grid(a.batch * a.n_head, a.n_splits);
+  B200_PROPAGATE(launch_with_pdl(decode_attn_kernel, grid, dim3(128), stream, a.pdl, a));
+  if (a.n_splits > 1) {
+    B200_PROPAGATE(
+        launch_with_pdl(decode_combine_kernel, dim3(a.batch * a.n_head), dim3(64), stream, a.pdl, a));
+  }
+  return kOk;
+}
+
+}  // namespace b200llm

@@ -1,0 +1,44 @@
+// Causal self-attention for GPT-2 (head_dim 64): a tensor-core prefill kernel over packed,
+// ragged prompts and a bandwidth-oriented decode kernel over the paged KV cache.
+//
+// Oracle: eager_attention_forward (modeling_gpt2.py:54-72) / sdpa_attention_forward
+// (integrations/sdpa_attention.py:92-101): softmax(Q K^T / sqrt(64) + causal mask) V with the
+// softmax evaluated in fp32; KV cache growth at cache_utils.py:119-120.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200llm {
+
+// Prefill: qkv is the packed [n_tok, 3*d] bf16 output of the QKV GEMM (q | k | v along the
+// feature axis, each [n_head, 64]); sequence b owns rows [cu_seqlens[b], cu_seqlens[b+1]).
+// out is [n_tok, d] bf16 with heads merged (modeling_gpt2.py:222).
+int prefill_attention(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int batch,
+                      int max_seq_len, int n_head, __nv_bfloat16* out, cudaStream_t stream);
+
+struct DecodeAttnArgs {
+  const __nv_bfloat16* qkv;      // [batch, 3*d] current token (bias already added)
+  const int32_t* active_slots;   // [batch] slot per row (-1 = padding)
+  const int32_t* seq_len;        // [n_slots] tokens already cached == position of this token
+  const int32_t* finished;       // [n_slots] or null; finished rows do not append
+  const int32_t* page_table;     // [n_slots, max_pages_per_seq]
+  int max_pages_per_seq;
+  __nv_bfloat16* k_pool;         // [n_pages, n_head, 16, 64]
+  __nv_bfloat16* v_pool;
+  __nv_bfloat16* out;            // [batch, d]
+  int batch;
+  int n_head;
+  int n_splits;                  // KV splits per (row, head); > 1 needs scratch
+  float* scratch;                // n_splits > 1: [batch*n_head*n_splits*(64+2)] fp32
+  int pdl;
+};
+// One decode step of attention: appends this token's K/V to its pages, then attends over
+// positions 0..seq_len (inclusive).
+int decode_attention(const DecodeAttnArgs& a, cudaStream_t stream);
+
+// Floats of scratch decode_attention needs for (batch, n_head, n_splits).
+size_t decode_attention_scratch_floats(int batch, int n_head, int n_splits);
+
+}  // namespace b200llm

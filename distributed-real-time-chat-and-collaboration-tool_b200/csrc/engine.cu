@@ -1,0 +1,1089 @@
+// Generation engine: model executor + paged KV-cache manager + sampler state, exported
+// through the C ABI in include/b200llm.h.
+//
+// It replaces the remote generator behind the reference's LLMService
+// (llm_server/llm_server.py:32-33, call sites :167, :231, :287, :403) with local GPT-2
+// generation whose arithmetic follows transformers' GPT2LMHeadModel.generate
+// (generation/utils.py:2131, :2658-2841; models/gpt2/modeling_gpt2.py:522-725).
+//
+// HBM layout (one engine = one GPU):
+//   weights   wte fp32 [V,d] (embedding gather) + wte bf16 [V,d] (tied LM head, K-major),
+//             wpe fp32 [P,d]; per layer bf16 K-major [out,in] GEMM weights, fp32 biases and
+//             LayerNorm parameters.
+//   KV pool   per layer K and V: [n_pages][n_head][16 tokens][64] bf16; page table int32
+//             [max_seqs][max_pages_per_seq]; the host owns the free list.
+//   slots     per-sequence generation state (seq_len, last token, finished, counters,
+//             sampling controls, generated tokens) so a decode step needs no host input.
+//   workspace residual stream x fp32 [rows,d]; h / qkv / attn / ffn bf16; logits fp32
+//             [max_batch_rows, V]; split-K partial planes; split-KV attention scratch.
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/b200llm.h"
+#include "attention.cuh"
+#include "common.cuh"
+#include "gemm_tcgen05.cuh"
+#include "ops.cuh"
+
+namespace b200llm {
+
+static thread_local std::string g_last_error;
+
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+int fail(int code, const std::string& msg) {
+  g_last_error = msg;
+  return code;
+}
+
+namespace {
+
+constexpr size_t kAlign = 256;
+inline size_t align_up(size_t v, size_t a = kAlign) { return (v + a - 1) / a * a; }
+
+__global__ void prefill_meta_kernel(const int32_t* __restrict__ cu, const int32_t* __restrict__ slots,
+                                    int batch, int32_t* __restrict__ row_pos,
+                                    int32_t* __restrict__ row_slot, int32_t* __restrict__ last_rows,
+                                    int32_t* __restrict__ seq_len) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n_tok = cu[batch];
+  if (t < n_tok) {
+    int lo = 0, hi = batch;  // largest b with cu[b] <= t
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (cu[mid] <= t) lo = mid; else hi = mid;
+    }
+    row_pos[t] = t - cu[lo];
+    row_slot[t] = slots[lo];
+  }
+  if (t < batch) {
+    last_rows[t] = cu[t + 1] - 1;
+    seq_len[slots[t]] = cu[t + 1] - cu[t];
+  }
+}
+
+struct SlotInit {
+  int32_t slot;
+  int32_t max_new;
+  int32_t min_new;
+  int32_t top_k;
+  float temperature;
+  uint32_t pad;
+  uint64_t seed;
+};
+
+__global__ void init_slots_kernel(const SlotInit* __restrict__ init, int batch, int32_t* last_tok,
+                                  int32_t* finished, int32_t* n_gen, int32_t* min_new,
+                                  int32_t* max_new, float* temperature, int32_t* top_k,
+                                  uint64_t* seed) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  const SlotInit s = init[b];
+  last_tok[s.slot] = 0;
+  finished[s.slot] = 0;
+  n_gen[s.slot] = 0;
+  min_new[s.slot] = s.min_new;
+  max_new[s.slot] = s.max_new;
+  temperature[s.slot] = s.temperature;
+  top_k[s.slot] = s.top_k;
+  seed[s.slot] = s.seed;
+}
+
+__global__ void gather_status_kernel(const int32_t* __restrict__ slots, int batch,
+                                     const int32_t* __restrict__ n_gen,
+                                     const int32_t* __restrict__ finished, int32_t* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  out[b] = n_gen[slots[b]];
+  out[batch + b] = finished[slots[b]];
+}
+
+struct LayerWeights {
+  float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+  __nv_bfloat16 *w_qkv, *w_o, *w_fc, *w_proj;
+  float *b_qkv, *b_o, *b_fc, *b_proj;
+};
+
+}  // namespace
+
+}  // namespace b200llm
+
+using namespace b200llm;
+
+struct b200llm_engine {
+  b200llm_config cfg;
+  int d, H, L, V, P;
+  int max_pages_per_seq;
+  int64_t n_pages;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+
+  std::vector<void*> allocations;
+
+  // weights
+  float* wte_f32 = nullptr;
+  __nv_bfloat16* wte_bf16 = nullptr;
+  float* wpe = nullptr;
+  float *lnf_g = nullptr, *lnf_b = nullptr;
+  std::vector<LayerWeights> layers;
+
+  // KV
+  __nv_bfloat16* k_pool = nullptr;  // [L][n_pages][H][16][64]
+  __nv_bfloat16* v_pool = nullptr;
+  size_t pool_layer_stride = 0;  // elements
+  int32_t* page_table = nullptr;  // device
+  std::vector<int32_t> free_pages;
+  std::vector<std::vector<int32_t>> slot_pages;
+  std::vector<char> slot_used;
+  std::vector<int32_t> slot_capacity;
+  std::vector<int32_t> slot_len_host;  // host mirror of seq_len upper bound
+
+  // slot state (device)
+  int32_t *seq_len = nullptr, *last_tok = nullptr, *finished = nullptr, *n_gen = nullptr;
+  int32_t *min_new = nullptr, *max_new = nullptr, *top_k = nullptr, *out_tokens = nullptr;
+  float* temperature = nullptr;
+  uint64_t* seed = nullptr;
+
+  // workspace
+  int max_rows = 0;
+  float* x = nullptr;
+  __nv_bfloat16 *h = nullptr, *qkv = nullptr, *attn = nullptr, *ffn = nullptr;
+  float* logits = nullptr;
+  int logits_rows = 0;
+  float* partials = nullptr;
+  size_t partials_floats = 0;
+  float* attn_scratch = nullptr;
+  size_t attn_scratch_floats = 0;
+  int32_t *ids_dev = nullptr, *row_pos = nullptr, *row_slot = nullptr, *cu_dev = nullptr,
+          *slots_dev = nullptr, *last_rows = nullptr, *active_dev = nullptr, *status_dev = nullptr;
+  SlotInit* init_dev = nullptr;
+
+  // pinned staging
+  int32_t* pin_i32 = nullptr;
+  size_t pin_i32_count = 0;
+  SlotInit* pin_init = nullptr;
+
+  // decode graphs
+  struct GraphKey {
+    int bucket, splits;
+    bool operator<(const GraphKey& o) const {
+      return bucket != o.bucket ? bucket < o.bucket : splits < o.splits;
+    }
+  };
+  struct GraphEntry {
+    cudaGraphExec_t exec = nullptr;
+    int kernels = 0;
+  };
+  std::map<GraphKey, GraphEntry> graphs;
+  std::vector<int32_t> active_host;  // last active set uploaded (padded)
+  int64_t launches = 0;
+  int launches_in_capture = 0;
+
+  int last_batch = 0;
+};
+
+namespace b200llm {
+namespace {
+
+int dev_alloc(b200llm_engine* e, void** p, size_t bytes) {
+  void* q = nullptr;
+  cudaError_t err = cudaMalloc(&q, align_up(std::max<size_t>(bytes, 1)));
+  if (err != cudaSuccess) {
+    return fail(kErrOutOfMemory, std::string("cudaMalloc failed: ") + cudaGetErrorString(err));
+  }
+  e->allocations.push_back(q);
+  *p = q;
+  return kOk;
+}
+
+template <typename T>
+int dev_alloc_t(b200llm_engine* e, T** p, size_t count) {
+  return dev_alloc(e, reinterpret_cast<void**>(p), count * sizeof(T));
+}
+
+int bucket_for(int batch) {
+  if (batch <= 16) return 16;
+  if (batch <= 32) return 32;
+  if (batch <= 64) return 64;
+  if (batch <= 128) return 128;
+  return (batch + 255) / 256 * 256;
+}
+
+// Largest divisor s of k_blocks with tiles * s <= sms and s <= cap.
+int pick_split(int features, int k, int sms, int cap) {
+  const int tiles = (features + 127) / 128;
+  const int kb = k / 64;
+  int best = 1;
+  for (int s = 1; s <= kb && s <= cap; ++s) {
+    if (kb % s == 0 && tiles * s <= sms) best = s;
+  }
+  return best;
+}
+
+struct StepPlan {
+  int rows;           // activation rows fed to the GEMMs
+  bool decode;        // decode step (slot-driven) or prefill
+  int split_o = 1;    // split-K of the attention out-proj
+  int split_p = 1;    // split-K of the MLP down-proj
+  int attn_splits = 1;
+  int pdl = 0;
+  int batch = 0;       // sequences (prefill) / bucket rows (decode)
+  int max_len = 0;     // prefill: longest prompt
+  float* logits_all = nullptr;
+};
+
+int count(b200llm_engine* e, int rc) {
+  if (rc == kOk) {
+    e->launches += 1;
+    e->launches_in_capture += 1;
+  }
+  return rc;
+}
+
+int gemm(b200llm_engine* e, const __nv_bfloat16* act, const __nv_bfloat16* w, const float* bias,
+         void* out, int tokens, int features, int k, int ld_out, int epi, int split, int pdl) {
+  GemmArgs g = {};
+  g.act = act;
+  g.w = w;
+  g.bias = bias;
+  g.out = out;
+  g.tokens = tokens;
+  g.features = features;
+  g.k = k;
+  g.ld_out = ld_out;
+  g.epilogue = epi;
+  g.split_k = split;
+  g.act_rows_alloc = e->max_rows;
+  g.force_orientation = -1;
+  g.pdl = pdl;
+  return count(e, gemm_bf16(g, e->stream));
+}
+
+int ln(b200llm_engine* e, const float* partials, int n_partials, int partial_rows,
+       const float* add_bias, const float* gamma, const float* beta, const int32_t* row_index,
+       int rows, int pdl) {
+  LayerNormArgs a = {};
+  a.x = e->x;
+  a.partials = partials;
+  a.n_partials = n_partials;
+  a.partial_rows = partial_rows;
+  a.add_bias = add_bias;
+  a.gamma = gamma;
+  a.beta = beta;
+  a.row_index = row_index;
+  a.out = e->h;
+  a.rows = rows;
+  a.d = e->d;
+  a.eps = e->cfg.ln_eps;
+  a.pdl = pdl;
+  return count(e, layernorm(a, e->stream));
+}
+
+// The transformer stack on `rows` activation rows already embedded in e->x, followed by the
+// final LayerNorm, the LM head and token selection.
+int run_stack(b200llm_engine* e, const StepPlan& p) {
+  const int d = e->d, rows = p.rows;
+  const int pdl = p.pdl;
+  const float* pending_partials = nullptr;  // split-K planes not yet folded into x
+  int pending_n = 0;
+  const float* pending_bias = nullptr;
+
+  for (int l = 0; l < e->L; ++l) {
+    const LayerWeights& w = e->layers[l];
+    __nv_bfloat16* kp = e->k_pool + static_cast<size_t>(l) * e->pool_layer_stride;
+    __nv_bfloat16* vp = e->v_pool + static_cast<size_t>(l) * e->pool_layer_stride;
+
+    // ln_1 (modeling_gpt2.py:273), folding the previous layer's MLP partials into x first
+    B200_PROPAGATE(ln(e, pending_partials, pending_n, rows, pending_bias, w.ln1_g, w.ln1_b,
+                      nullptr, rows, pdl));
+    pending_partials = nullptr;
+    pending_n = 0;
+    // c_attn (:185)
+    B200_PROPAGATE(gemm(e, e->h, w.w_qkv, w.b_qkv, e->qkv, rows, 3 * d, d, 3 * d, kEpiBiasBf16, 1, pdl));
+    // attention (:186-222)
+    if (p.decode) {
+      DecodeAttnArgs a = {};
+      a.qkv = e->qkv;
+      a.active_slots = e->active_dev;
+      a.seq_len = e->seq_len;
+      a.finished = e->finished;
+      a.page_table = e->page_table;
+      a.max_pages_per_seq = e->max_pages_per_seq;
+      a.k_pool = kp;
+      a.v_pool = vp;
+      a.out = e->attn;
+      a.batch = rows;
+      a.n_head = e->H;
+      a.n_splits = p.attn_splits;
+      a.scratch = e->attn_scratch;
+      a.pdl = pdl;
+      B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
+      if (p.attn_splits > 1) e->launches += 1, e->launches_in_capture += 1;
+    } else {
+      B200_PROPAGATE(count(e, kv_scatter(e->qkv, e->row_slot, e->row_pos, e->page_table,
+                                         e->max_pages_per_seq, kp, vp, rows, e->H, e->stream)));
+      B200_PROPAGATE(count(e, prefill_attention(e->qkv, e->cu_dev, p.batch, p.max_len, e->H,
+                                                e->attn, e->stream)));
+    }
+    // attn c_proj + residual (:223, :282)
+    if (p.split_o > 1) {
+      B200_PROPAGATE(gemm(e, e->attn, w.w_o, nullptr, e->partials, rows, d, d, d, kEpiPartialF32,
+                          p.split_o, pdl));
+      B200_PROPAGATE(ln(e, e->partials, p.split_o, rows, w.b_o, w.ln2_g, w.ln2_b, nullptr, rows, pdl));
+    } else {
+      B200_PROPAGATE(gemm(e, e->attn, w.w_o, w.b_o, e->x, rows, d, d, d, kEpiBiasResidF32, 1, pdl));
+      B200_PROPAGATE(ln(e, nullptr, 0, rows, nullptr, w.ln2_g, w.ln2_b, nullptr, rows, pdl));
+    }
+    // mlp c_fc + gelu_new (:239-240)
+    B200_PROPAGATE(gemm(e, e->h, w.w_fc, w.b_fc, e->ffn, rows, 4 * d, d, 4 * d, kEpiBiasGeluBf16, 1, pdl));
+    // mlp c_proj + residual (:241, :307)
+    if (p.split_p > 1) {
+      B200_PROPAGATE(gemm(e, e->ffn, w.w_proj, nullptr, e->partials, rows, d, 4 * d, d,
+                          kEpiPartialF32, p.split_p, pdl));
+      pending_partials = e->partials;
+      pending_n = p.split_p;
+      pending_bias = w.b_proj;
+    } else {
+      B200_PROPAGATE(gemm(e, e->ffn, w.w_proj, w.b_proj, e->x, rows, d, 4 * d, d, kEpiBiasResidF32, 1, pdl));
+    }
+  }
+
+  // ln_f (:628) and the tied LM head (:705-706)
+  if (p.logits_all != nullptr) {
+    B200_PROPAGATE(ln(e, pending_partials, pending_n, rows, pending_bias, e->lnf_g, e->lnf_b,
+                      nullptr, rows, pdl));
+    B200_PROPAGATE(gemm(e, e->h, e->wte_bf16, nullptr, p.logits_all, rows, e->V, d, e->V, kEpiF32, 1, pdl));
+    pending_partials = nullptr;
+    pending_n = 0;
+  }
+  const int head_rows = p.decode ? rows : p.batch;
+  B200_PROPAGATE(ln(e, pending_partials, pending_n, rows, pending_bias, e->lnf_g, e->lnf_b,
+                    p.decode ? nullptr : e->last_rows, head_rows, pdl));
+  B200_PROPAGATE(gemm(e, e->h, e->wte_bf16, nullptr, e->logits, head_rows, e->V, d, e->V, kEpiF32, 1, pdl));
+
+  SelectArgs s = {};
+  s.logits = e->logits;
+  s.ld = e->V;
+  s.vocab = e->V;
+  s.active_slots = p.decode ? e->active_dev : e->slots_dev;
+  s.batch = head_rows;
+  s.last_tok = e->last_tok;
+  s.seq_len = e->seq_len;
+  s.finished = e->finished;
+  s.n_gen = e->n_gen;
+  s.min_new = e->min_new;
+  s.max_new = e->max_new;
+  s.out_tokens = e->out_tokens;
+  s.out_stride = e->cfg.max_new_tokens;
+  s.eos_id = e->cfg.eos_token_id;
+  s.pad_id = e->cfg.pad_token_id;
+  s.temperature = e->temperature;
+  s.top_k = e->top_k;
+  s.seed = e->seed;
+  s.advance_seq = p.decode ? 1 : 0;
+  B200_PROPAGATE(count(e, select_tokens(s, e->stream)));
+  return kOk;
+}
+
+int decode_step_launches(b200llm_engine* e, const StepPlan& p) {
+  B200_PROPAGATE(count(e, embed_decode(e->wte_f32, e->wpe, e->active_dev, e->last_tok, e->seq_len,
+                                       e->x, p.rows, e->d, e->V, e->P, e->stream)));
+  return run_stack(e, p);
+}
+
+int ensure_pinned(b200llm_engine* e, size_t count_i32) {
+  if (count_i32 <= e->pin_i32_count) return kOk;
+  if (e->pin_i32) cudaFreeHost(e->pin_i32);
+  e->pin_i32 = nullptr;
+  const size_t n = std::max<size_t>(count_i32, 1 << 16);
+  B200_CUDA_OK(cudaMallocHost(reinterpret_cast<void**>(&e->pin_i32), n * sizeof(int32_t)));
+  e->pin_i32_count = n;
+  return kOk;
+}
+
+}  // namespace
+}  // namespace b200llm
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+extern "C" {
+
+const char* b200llm_last_error(void) { return g_last_error.c_str(); }
+int b200llm_abi_version(void) { return B200LLM_ABI_VERSION; }
+
+size_t b200llm_weight_blob_floats(const b200llm_config* c) {
+  if (c == nullptr) return 0;
+  const size_t d = c->d_model, V = c->vocab_size, P = c->n_positions, L = c->n_layer;
+  const size_t per_layer = 2 * d + d * 3 * d + 3 * d + d * d + d + 2 * d + d * 4 * d + 4 * d + 4 * d * d + d;
+  return V * d + P * d + L * per_layer + 2 * d;
+}
+
+int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, size_t n_floats,
+                          b200llm_engine** out_engine) {
+  B200_CHECK_ARG(cfg && weights_host && out_engine, "engine_create: null argument");
+  B200_CHECK_ARG(cfg->n_head > 0 && cfg->d_model == cfg->n_head * kHeadDim,
+                 "engine_create: head_dim must be 64 (d_model == 64 * n_head)");
+  B200_CHECK_ARG(cfg->d_model % 128 == 0, "engine_create: d_model must be a multiple of 128");
+  B200_CHECK_ARG(cfg->n_layer > 0 && cfg->vocab_size > 0 && cfg->n_positions > 0,
+                 "engine_create: bad model shape");
+  B200_CHECK_ARG(cfg->max_seqs > 0 && cfg->max_seq_len > 0 && cfg->max_batch_tokens > 0 &&
+                     cfg->max_new_tokens > 0,
+                 "engine_create: capacities must be positive");
+  B200_CHECK_ARG(n_floats == b200llm_weight_blob_floats(cfg),
+                 "engine_create: weight blob size does not match the config");
+  B200_CUDA_OK(cudaSetDevice(cfg->device));
+
+  std::unique_ptr<b200llm_engine> e(new b200llm_engine());
+  e->cfg = *cfg;
+  e->d = cfg->d_model;
+  e->H = cfg->n_head;
+  e->L = cfg->n_layer;
+  e->V = cfg->vocab_size;
+  e->P = cfg->n_positions;
+  const int d = e->d, V = e->V, P = e->P, L = e->L, H = e->H;
+  B200_CUDA_OK(cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking));
+  e->stream = e->own_stream;
+  cudaStream_t st = e->stream;
+
+  auto cleanup = [&](int rc) {
+    b200llm_engine_destroy(e.release());
+    return rc;
+  };
+#define E_TRY(expr)                         \
+  do {                                      \
+    int _rc = (expr);                       \
+    if (_rc != 0) return cleanup(_rc);      \
+  } while (0)
+#define E_CUDA(expr)                                                                         \
+  do {                                                                                       \
+    cudaError_t _e = (expr);                                                                 \
+    if (_e != cudaSuccess)                                                                   \
+      return cleanup(fail(kErrCuda, std::string(#expr) + ": " + cudaGetErrorString(_e)));    \
+  } while (0)
+
+  // ---- weights: stage fp32 pieces through one device buffer, convert on the GPU ----------
+  const size_t biggest = std::max<size_t>(static_cast<size_t>(V) * d, static_cast<size_t>(4) * d * d);
+  float* stage = nullptr;
+  E_CUDA(cudaMalloc(reinterpret_cast<void**>(&stage), biggest * sizeof(float)));
+  const float* src = weights_host;
+  auto upload_f32 = [&](float** dst, size_t n) -> int {
+    B200_PROPAGATE(dev_alloc_t(e.get(), dst, n));
+    B200_CUDA_OK(cudaMemcpyAsync(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    src += n;
+    return kOk;
+  };
+  auto upload_conv1d = [&](__nv_bfloat16** dst, int in, int out) -> int {
+    const size_t n = static_cast<size_t>(in) * out;
+    B200_PROPAGATE(dev_alloc_t(e.get(), dst, n));
+    B200_CUDA_OK(cudaMemcpyAsync(stage, src, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    B200_PROPAGATE(convert_transpose_bf16(stage, *dst, in, out, st));
+    B200_CUDA_OK(cudaStreamSynchronize(st));  // `stage` is reused by the next tensor
+    src += n;
+    return kOk;
+  };
+  auto free_stage = [&](int rc) {
+    cudaFree(stage);
+    return rc;
+  };
+#define W_TRY(expr)                                    \
+  do {                                                 \
+    int _rc = (expr);                                  \
+    if (_rc != 0) return cleanup(free_stage(_rc));     \
+  } while (0)
+
+  W_TRY(upload_f32(&e->wte_f32, static_cast<size_t>(V) * d));
+  W_TRY(dev_alloc_t(e.get(), &e->wte_bf16, static_cast<size_t>(V) * d));
+  W_TRY(convert_bf16(e->wte_f32, e->wte_bf16, static_cast<size_t>(V) * d, st));
+  W_TRY(upload_f32(&e->wpe, static_cast<size_t>(P) * d));
+  e->layers.resize(L);
+  for (int l = 0; l < L; ++l) {
+    LayerWeights& w = e->layers[l];
+    W_TRY(upload_f32(&w.ln1_g, d));
+    W_TRY(upload_f32(&w.ln1_b, d));
+    W_TRY(upload_conv1d(&w.w_qkv, d, 3 * d));
+    W_TRY(upload_f32(&w.b_qkv, 3 * d));
+    W_TRY(upload_conv1d(&w.w_o, d, d));
+    W_TRY(upload_f32(&w.b_o, d));
+    W_TRY(upload_f32(&w.ln2_g, d));
+    W_TRY(upload_f32(&w.ln2_b, d));
+    W_TRY(upload_conv1d(&w.w_fc, d, 4 * d));
+    W_TRY(upload_f32(&w.b_fc, 4 * d));
+    W_TRY(upload_conv1d(&w.w_proj, 4 * d, d));
+    W_TRY(upload_f32(&w.b_proj, d));
+  }
+  W_TRY(upload_f32(&e->lnf_g, d));
+  W_TRY(upload_f32(&e->lnf_b, d));
+  cudaStreamSynchronize(st);
+  cudaFree(stage);
+
+  // ---- KV pool ---------------------------------------------------------------------------
+  e->max_pages_per_seq = (cfg->max_seq_len + kPageTokens - 1) / kPageTokens;
+  int64_t pool_tokens = cfg->kv_pool_tokens > 0
+                            ? cfg->kv_pool_tokens
+                            : static_cast<int64_t>(cfg->max_seqs) * e->max_pages_per_seq * kPageTokens;
+  e->n_pages = (pool_tokens + kPageTokens - 1) / kPageTokens;
+  e->pool_layer_stride = static_cast<size_t>(e->n_pages) * H * kPageTokens * kHeadDim;
+  E_TRY(dev_alloc_t(e.get(), &e->k_pool, e->pool_layer_stride * L));
+  E_TRY(dev_alloc_t(e.get(), &e->v_pool, e->pool_layer_stride * L));
+  E_TRY(dev_alloc_t(e.get(), &e->page_table, static_cast<size_t>(cfg->max_seqs) * e->max_pages_per_seq));
+  E_CUDA(cudaMemsetAsync(e->page_table, 0,
+                         static_cast<size_t>(cfg->max_seqs) * e->max_pages_per_seq * sizeof(int32_t), st));
+  e->free_pages.resize(e->n_pages);
+  for (int64_t i = 0; i < e->n_pages; ++i) e->free_pages[i] = static_cast<int32_t>(e->n_pages - 1 - i);
+  e->slot_pages.resize(cfg->max_seqs);
+  e->slot_used.assign(cfg->max_seqs, 0);
+  e->slot_capacity.assign(cfg->max_seqs, 0);
+  e->slot_len_host.assign(cfg->max_seqs, 0);
+
+  // ---- slot state -------------------------------------------------------------------------
+  const size_t S = cfg->max_seqs;
+  E_TRY(dev_alloc_t(e.get(), &e->seq_len, S));
+  E_TRY(dev_alloc_t(e.get(), &e->last_tok, S));
+  E_TRY(dev_alloc_t(e.get(), &e->finished, S));
+  E_TRY(dev_alloc_t(e.get(), &e->n_gen, S));
+  E_TRY(dev_alloc_t(e.get(), &e->min_new, S));
+  E_TRY(dev_alloc_t(e.get(), &e->max_new, S));
+  E_TRY(dev_alloc_t(e.get(), &e->top_k, S));
+  E_TRY(dev_alloc_t(e.get(), &e->temperature, S));
+  E_TRY(dev_alloc_t(e.get(), &e->seed, S));
+  E_TRY(dev_alloc_t(e.get(), &e->out_tokens, S * cfg->max_new_tokens));
+  E_CUDA(cudaMemsetAsync(e->seq_len, 0, S * sizeof(int32_t), st));
+  E_CUDA(cudaMemsetAsync(e->last_tok, 0, S * sizeof(int32_t), st));
+  E_CUDA(cudaMemsetAsync(e->finished, 0, S * sizeof(int32_t), st));
+  E_CUDA(cudaMemsetAsync(e->n_gen, 0, S * sizeof(int32_t), st));
+
+  // ---- workspace --------------------------------------------------------------------------
+  const int dec_rows = bucket_for(cfg->max_seqs);
+  e->max_rows = std::max(cfg->max_batch_tokens, dec_rows);
+  e->max_rows = (e->max_rows + 127) / 128 * 128;
+  const size_t R = e->max_rows;
+  E_TRY(dev_alloc_t(e.get(), &e->x, R * d));
+  E_TRY(dev_alloc_t(e.get(), &e->h, R * d));
+  E_TRY(dev_alloc_t(e.get(), &e->qkv, R * 3 * d));
+  E_TRY(dev_alloc_t(e.get(), &e->attn, R * d));
+  E_TRY(dev_alloc_t(e.get(), &e->ffn, R * 4 * d));
+  E_CUDA(cudaMemsetAsync(e->h, 0, R * d * sizeof(__nv_bfloat16), st));
+  E_CUDA(cudaMemsetAsync(e->qkv, 0, R * 3 * d * sizeof(__nv_bfloat16), st));
+  E_CUDA(cudaMemsetAsync(e->attn, 0, R * d * sizeof(__nv_bfloat16), st));
+  E_CUDA(cudaMemsetAsync(e->ffn, 0, R * 4 * d * sizeof(__nv_bfloat16), st));
+  E_CUDA(cudaMemsetAsync(e->x, 0, R * d * sizeof(float), st));
+  e->logits_rows = dec_rows;
+  E_TRY(dev_alloc_t(e.get(), &e->logits, static_cast<size_t>(e->logits_rows) * V));
+  // split-K planes: at most 32 splits of [decode rows, d]
+  e->partials_floats = static_cast<size_t>(32) * dec_rows * d;
+  E_TRY(dev_alloc_t(e.get(), &e->partials, e->partials_floats));
+  e->attn_scratch_floats = decode_attention_scratch_floats(dec_rows, H, 16);
+  E_TRY(dev_alloc_t(e.get(), &e->attn_scratch, e->attn_scratch_floats));
+  E_TRY(dev_alloc_t(e.get(), &e->ids_dev, R));
+  E_TRY(dev_alloc_t(e.get(), &e->row_pos, R));
+  E_TRY(dev_alloc_t(e.get(), &e->row_slot, R));
+  E_TRY(dev_alloc_t(e.get(), &e->cu_dev, S + 1));
+  E_TRY(dev_alloc_t(e.get(), &e->slots_dev, S));
+  E_TRY(dev_alloc_t(e.get(), &e->last_rows, S));
+  E_TRY(dev_alloc_t(e.get(), &e->active_dev, static_cast<size_t>(dec_rows)));
+  E_TRY(dev_alloc_t(e.get(), &e->status_dev, 2 * S));
+  E_TRY(dev_alloc_t(e.get(), &e->init_dev, S));
+  E_CUDA(cudaMallocHost(reinterpret_cast<void**>(&e->pin_init), S * sizeof(SlotInit)));
+  E_TRY(ensure_pinned(e.get(), R + 4 * S + 16));
+  E_CUDA(cudaStreamSynchronize(st));
+#undef E_TRY
+#undef E_CUDA
+#undef W_TRY
+  *out_engine = e.release();
+  return kOk;
+}
+
+int b200llm_engine_destroy(b200llm_engine* e) {
+  if (e == nullptr) return kOk;
+  cudaSetDevice(e->cfg.device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (auto& kv : e->graphs) {
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  }
+  for (void* p : e->allocations) cudaFree(p);
+  if (e->pin_i32) cudaFreeHost(e->pin_i32);
+  if (e->pin_init) cudaFreeHost(e->pin_init);
+  if (e->own_stream) cudaStreamDestroy(e->own_stream);
+  gemm_clear_tensor_map_cache();
+  delete e;
+  return kOk;
+}
+
+int b200llm_engine_set_stream(b200llm_engine* e, void* stream) {
+  B200_CHECK_ARG(e != nullptr, "set_stream: null engine");
+  B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+  e->stream = stream ? reinterpret_cast<cudaStream_t>(stream) : e->own_stream;
+  // graphs were captured on the previous stream's topology; they replay on any stream
+  return kOk;
+}
+
+int b200llm_seq_alloc(b200llm_engine* e, int32_t capacity_tokens, int32_t* out_slot) {
+  B200_CHECK_ARG(e && out_slot, "seq_alloc: null argument");
+  B200_CHECK_ARG(capacity_tokens > 0 && capacity_tokens <= e->cfg.max_seq_len,
+                 "seq_alloc: capacity exceeds max_seq_len");
+  const int need = (capacity_tokens + kPageTokens - 1) / kPageTokens;
+  if (static_cast<int64_t>(e->free_pages.size()) < need) {
+    return fail(kErrCapacity, "seq_alloc: KV pool exhausted");
+  }
+  int slot = -1;
+  for (int s = 0; s < e->cfg.max_seqs; ++s) {
+    if (!e->slot_used[s]) {
+      slot = s;
+      break;
+    }
+  }
+  if (slot < 0) return fail(kErrCapacity, "seq_alloc: no free sequence slot");
+  std::vector<int32_t>& pages = e->slot_pages[slot];
+  pages.clear();
+  for (int i = 0; i < need; ++i) {
+    pages.push_back(e->free_pages.back());
+    e->free_pages.pop_back();
+  }
+  // The page-table row is uploaded from pageable memory: cudaMemcpyAsync stages it before
+  // returning, so `pages` may change afterwards.
+  cudaError_t err = cudaMemcpyAsync(e->page_table + static_cast<size_t>(slot) * e->max_pages_per_seq,
+                                    pages.data(), need * sizeof(int32_t), cudaMemcpyHostToDevice,
+                                    e->stream);
+  if (err != cudaSuccess) {
+    for (int32_t p : pages) e->free_pages.push_back(p);
+    pages.clear();
+    return fail(kErrCuda, std::string("seq_alloc: page table upload: ") + cudaGetErrorString(err));
+  }
+  e->slot_used[slot] = 1;
+  e->slot_capacity[slot] = capacity_tokens;
+  e->slot_len_host[slot] = 0;
+  *out_slot = slot;
+  return kOk;
+}
+
+int b200llm_seq_free(b200llm_engine* e, int32_t slot) {
+  B200_CHECK_ARG(e != nullptr, "seq_free: null engine");
+  B200_CHECK_ARG(slot >= 0 && slot < e->cfg.max_seqs && e->slot_used[slot], "seq_free: bad slot");
+  for (int32_t p : e->slot_pages[slot]) e->free_pages.push_back(p);
+  e->slot_pages[slot].clear();
+  e->slot_used[slot] = 0;
+  e->slot_capacity[slot] = 0;
+  e->slot_len_host[slot] = 0;
+  return kOk;
+}
+
+int b200llm_kv_pages_free(b200llm_engine* e, int64_t* out_free, int64_t* out_total) {
+  B200_CHECK_ARG(e != nullptr, "kv_pages_free: null engine");
+  if (out_free) *out_free = static_cast<int64_t>(e->free_pages.size());
+  if (out_total) *out_total = e->n_pages;
+  return kOk;
+}
+
+int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device,
+                    const int32_t* cu, const int32_t* slots, const b200llm_sampling* sampling,
+                    int32_t batch, float* logits_all_dev) {
+  B200_CHECK_ARG(e && ids && cu && slots, "prefill: null argument");
+  B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "prefill: bad batch");
+  B200_CHECK_ARG(batch <= e->logits_rows, "prefill: batch exceeds logits workspace");
+  B200_CHECK_ARG(cu[0] == 0, "prefill: cu_seqlens must start at 0");
+  const int n_tok = cu[batch];
+  int max_len = 0;
+  for (int b = 0; b < batch; ++b) {
+    const int len = cu[b + 1] - cu[b];
+    B200_CHECK_ARG(len > 0, "prefill: empty prompt");
+    B200_CHECK_ARG(len <= e->P, "prefill: prompt longer than the position table");
+    const int s = slots[b];
+    B200_CHECK_ARG(s >= 0 && s < e->cfg.max_seqs && e->slot_used[s], "prefill: slot not allocated");
+    B200_CHECK_ARG(len <= e->slot_capacity[s], "prefill: prompt exceeds the slot's KV capacity");
+    max_len = std::max(max_len, len);
+  }
+  if (n_tok > e->cfg.max_batch_tokens) {
+    return fail(kErrCapacity, "prefill: packed tokens exceed max_batch_tokens");
+  }
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = e->stream;
+
+  // staging: [cu (batch+1) | slots (batch) | ids (n_tok, host case)]
+  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(2 * batch + 1 + n_tok)));
+  // pinned buffers are reused call to call: the previous call's copies must have drained
+  B200_CUDA_OK(cudaStreamSynchronize(st));
+  int32_t* pin = e->pin_i32;
+  std::memcpy(pin, cu, (batch + 1) * sizeof(int32_t));
+  std::memcpy(pin + batch + 1, slots, batch * sizeof(int32_t));
+  B200_CUDA_OK(cudaMemcpyAsync(e->cu_dev, pin, (batch + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  B200_CUDA_OK(cudaMemcpyAsync(e->slots_dev, pin + batch + 1, batch * sizeof(int32_t),
+                               cudaMemcpyHostToDevice, st));
+  const int32_t* ids_dev = ids;
+  if (!ids_on_device) {
+    for (int i = 0; i < n_tok; ++i) {
+      if (ids[i] < 0 || ids[i] >= e->V) return fail(kErrInvalidArg, "prefill: token id out of range");
+    }
+    std::memcpy(pin + 2 * batch + 1, ids, n_tok * sizeof(int32_t));
+    B200_CUDA_OK(cudaMemcpyAsync(e->ids_dev, pin + 2 * batch + 1, n_tok * sizeof(int32_t),
+                                 cudaMemcpyHostToDevice, st));
+    ids_dev = e->ids_dev;
+  }
+  for (int b = 0; b < batch; ++b) {
+    SlotInit& si = e->pin_init[b];
+    si.slot = slots[b];
+    const int cap_gen = e->cfg.max_new_tokens;
+    int mx = sampling ? sampling[b].max_new_tokens : cap_gen;
+    if (mx <= 0 || mx > cap_gen) mx = cap_gen;
+    const int room = e->slot_capacity[slots[b]] - (cu[b + 1] - cu[b]) + 1;  // last token needs no KV
+    if (mx > room) mx = room;
+    if (mx < 1) mx = 1;
+    si.max_new = mx;
+    si.min_new = sampling ? std::min(sampling[b].min_new_tokens, mx) : 0;
+    si.temperature = sampling ? sampling[b].temperature : 0.0f;
+    si.top_k = sampling ? sampling[b].top_k : 0;
+    si.seed = sampling ? sampling[b].seed : 0;
+    si.pad = 0;
+    e->slot_len_host[slots[b]] = cu[b + 1] - cu[b];
+  }
+  B200_CUDA_OK(cudaMemcpyAsync(e->init_dev, e->pin_init, batch * sizeof(SlotInit),
+                               cudaMemcpyHostToDevice, st));
+  init_slots_kernel<<<(batch + 127) / 128, 128, 0, st>>>(e->init_dev, batch, e->last_tok, e->finished,
+                                                         e->n_gen, e->min_new, e->max_new,
+                                                         e->temperature, e->top_k, e->seed);
+  B200_CUDA_OK(cudaGetLastError());
+  const int meta_threads = std::max(n_tok, batch);
+  prefill_meta_kernel<<<(meta_threads + 255) / 256, 256, 0, st>>>(
+      e->cu_dev, e->slots_dev, batch, e->row_pos, e->row_slot, e->last_rows, e->seq_len);
+  B200_CUDA_OK(cudaGetLastError());
+  e->launches += 2;
+
+  B200_PROPAGATE(count(e, embed_tokens(e->wte_f32, e->wpe, ids_dev, e->row_pos, e->x, n_tok, e->d,
+                                       e->V, e->P, st)));
+  StepPlan p;
+  p.rows = n_tok;
+  p.decode = false;
+  p.batch = batch;
+  p.max_len = max_len;
+  p.logits_all = logits_all_dev;
+  p.pdl = 0;
+  B200_PROPAGATE(run_stack(e, p));
+  e->last_batch = batch;
+  return kOk;
+}
+
+int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32_t n_steps) {
+  B200_CHECK_ARG(e && slots, "decode: null argument");
+  B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "decode: bad batch");
+  B200_CHECK_ARG(n_steps > 0, "decode: n_steps must be positive");
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = e->stream;
+  const int bucket = bucket_for(batch);
+  B200_CHECK_ARG(bucket <= e->logits_rows, "decode: batch exceeds workspace");
+
+  int max_ctx = 1;
+  for (int b = 0; b < batch; ++b) {
+    const int s = slots[b];
+    B200_CHECK_ARG(s >= 0 && s < e->cfg.max_seqs && e->slot_used[s], "decode: slot not allocated");
+    max_ctx = std::max(max_ctx, e->slot_len_host[s] + n_steps);
+  }
+
+  // upload the active set when it changed
+  std::vector<int32_t> active(bucket, -1);
+  std::copy(slots, slots + batch, active.begin());
+  if (active != e->active_host) {
+    B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(bucket)));
+    B200_CUDA_OK(cudaStreamSynchronize(st));
+    std::memcpy(e->pin_i32, active.data(), bucket * sizeof(int32_t));
+    B200_CUDA_OK(cudaMemcpyAsync(e->active_dev, e->pin_i32, bucket * sizeof(int32_t),
+                                 cudaMemcpyHostToDevice, st));
+    e->active_host = active;
+  }
+
+  StepPlan p;
+  p.rows = bucket;
+  p.decode = true;
+  p.batch = bucket;
+  p.pdl = e->cfg.use_pdl ? 1 : 0;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.device);
+  const int cap = e->cfg.decode_split_k == 0 ? 32 : std::min(e->cfg.decode_split_k, 32);
+  if (bucket <= 256 && cap > 1) {
+    p.split_o = pick_split(e->d, e->d, sms, cap);
+    p.split_p = pick_split(e->d, 4 * e->d, sms, cap);
+  }
+  // split-KV when (rows x heads) alone cannot fill the machine and contexts are long
+  {
+    const int ctas = bucket * e->H;
+    int splits = 1;
+    while (splits < 16 && ctas * splits < 4 * sms && max_ctx / (splits * 2) >= 64) splits *= 2;
+    p.attn_splits = splits;
+  }
+
+  if (!e->cfg.use_cuda_graphs) {
+    for (int i = 0; i < n_steps; ++i) B200_PROPAGATE(decode_step_launches(e, p));
+  } else {
+    b200llm_engine::GraphKey key{bucket, p.attn_splits};
+    auto it = e->graphs.find(key);
+    if (it == e->graphs.end()) {
+      cudaGraph_t graph = nullptr;
+      const int64_t launches_before = e->launches;
+      e->launches_in_capture = 0;
+      B200_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+      int rc = decode_step_launches(e, p);
+      cudaError_t cerr = cudaStreamEndCapture(st, &graph);
+      e->launches = launches_before;  // captured, not executed
+      if (rc != kOk) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+      }
+      if (cerr != cudaSuccess) {
+        return fail(kErrCuda, std::string("decode: graph capture failed: ") + cudaGetErrorString(cerr));
+      }
+      b200llm_engine::GraphEntry entry;
+      entry.kernels = e->launches_in_capture;
+      cerr = cudaGraphInstantiate(&entry.exec, graph, 0);
+      cudaGraphDestroy(graph);
+      if (cerr != cudaSuccess) {
+        return fail(kErrCuda, std::string("decode: graph instantiate failed: ") + cudaGetErrorString(cerr));
+      }
+      it = e->graphs.emplace(key, entry).first;
+    }
+    for (int i = 0; i < n_steps; ++i) {
+      B200_CUDA_OK(cudaGraphLaunch(it->second.exec, st));
+      e->launches += it->second.kernels;
+    }
+  }
+  for (int b = 0; b < batch; ++b) {
+    int& len = e->slot_len_host[slots[b]];
+    len = std::min(len + n_steps, e->slot_capacity[slots[b]]);
+  }
+  e->last_batch = bucket;
+  return kOk;
+}
+
+int b200llm_sync(b200llm_engine* e) {
+  B200_CHECK_ARG(e != nullptr, "sync: null engine");
+  B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+  return kOk;
+}
+
+int b200llm_read_tokens(b200llm_engine* e, int32_t slot, int32_t* out, int32_t max_tokens,
+                        int32_t* out_count, int32_t* out_finished) {
+  B200_CHECK_ARG(e && out && out_count, "read_tokens: null argument");
+  B200_CHECK_ARG(slot >= 0 && slot < e->cfg.max_seqs, "read_tokens: bad slot");
+  int32_t st2[2] = {0, 0};
+  B200_CUDA_OK(cudaMemcpyAsync(&st2[0], e->n_gen + slot, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+  B200_CUDA_OK(cudaMemcpyAsync(&st2[1], e->finished + slot, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+  B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+  const int n = std::min(st2[0], max_tokens);
+  if (n > 0) {
+    B200_CUDA_OK(cudaMemcpyAsync(out, e->out_tokens + static_cast<size_t>(slot) * e->cfg.max_new_tokens,
+                                 n * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+    B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+  }
+  *out_count = n;
+  if (out_finished) *out_finished = st2[1];
+  return kOk;
+}
+
+int b200llm_read_status(b200llm_engine* e, const int32_t* slots, int32_t batch, int32_t* out_counts,
+                        int32_t* out_finished) {
+  B200_CHECK_ARG(e && slots && out_counts && out_finished, "read_status: null argument");
+  B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "read_status: bad batch");
+  cudaStream_t st = e->stream;
+  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(3 * batch)));
+  B200_CUDA_OK(cudaStreamSynchronize(st));
+  std::memcpy(e->pin_i32, slots, batch * sizeof(int32_t));
+  B200_CUDA_OK(cudaMemcpyAsync(e->last_rows, e->pin_i32, batch * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  gather_status_kernel<<<(batch + 127) / 128, 128, 0, st>>>(e->last_rows, batch, e->n_gen, e->finished,
+                                                            e->status_dev);
+  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(cudaMemcpyAsync(e->pin_i32 + batch, e->status_dev, 2 * batch * sizeof(int32_t),
+                               cudaMemcpyDeviceToHost, st));
+  B200_CUDA_OK(cudaStreamSynchronize(st));
+  std::memcpy(out_counts, e->pin_i32 + batch, batch * sizeof(int32_t));
+  std::memcpy(out_finished, e->pin_i32 + 2 * batch, batch * sizeof(int32_t));
+  return kOk;
+}
+
+int b200llm_read_last_logits(b200llm_engine* e, int32_t batch, float* out) {
+  B200_CHECK_ARG(e && out, "read_last_logits: null argument");
+  B200_CHECK_ARG(batch > 0 && batch <= e->logits_rows, "read_last_logits: bad batch");
+  B200_CUDA_OK(cudaMemcpyAsync(out, e->logits, static_cast<size_t>(batch) * e->V * sizeof(float),
+                               cudaMemcpyDeviceToHost, e->stream));
+  B200_CUDA_OK(cudaStreamSynchronize(e->stream));
+  return kOk;
+}
+
+int b200llm_generate(b200llm_engine* e, const int32_t* ids_host, const int32_t* cu,
+                     const b200llm_sampling* sampling, int32_t batch, int32_t* out_tokens,
+                     int32_t out_stride, int32_t* out_counts) {
+  B200_CHECK_ARG(e && ids_host && cu && out_tokens && out_counts, "generate: null argument");
+  B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "generate: bad batch");
+  std::vector<int32_t> slots(batch, -1);
+  int max_new = 1;
+  auto release = [&](int rc) {
+    for (int s : slots) {
+      if (s >= 0) b200llm_seq_free(e, s);
+    }
+    return rc;
+  };
+  for (int b = 0; b < batch; ++b) {
+    int mx = sampling ? sampling[b].max_new_tokens : e->cfg.max_new_tokens;
+    if (mx <= 0 || mx > e->cfg.max_new_tokens) mx = e->cfg.max_new_tokens;
+    const int len = cu[b + 1] - cu[b];
+    int cap = std::min(len + mx, e->cfg.max_seq_len);
+    if (len > cap) return release(fail(kErrCapacity, "generate: prompt exceeds max_seq_len"));
+    int rc = b200llm_seq_alloc(e, cap, &slots[b]);
+    if (rc != kOk) return release(rc);
+    max_new = std::max(max_new, mx);
+  }
+  int rc = b200llm_prefill(e, ids_host, 0, cu, slots.data(), sampling, batch, nullptr);
+  if (rc != kOk) return release(rc);
+
+  // Decode in chunks; between chunks one small device->host status read decides whether
+  // every sequence is finished (EOS) so the loop can stop early.
+  std::vector<int32_t> counts(batch), fin(batch);
+  int done_steps = 1;  // prefill produced the first token
+  bool can_finish_early = false;
+  for (int b = 0; b < batch; ++b) {
+    const int mn = sampling ? sampling[b].min_new_tokens : 0;
+    int mx = sampling ? sampling[b].max_new_tokens : e->cfg.max_new_tokens;
+    if (mx <= 0 || mx > e->cfg.max_new_tokens) mx = e->cfg.max_new_tokens;
+    if (mn < mx) can_finish_early = true;
+  }
+  while (done_steps < max_new) {
+    const int chunk = can_finish_early ? std::min(16, max_new - done_steps) : (max_new - done_steps);
+    rc = b200llm_decode(e, slots.data(), batch, chunk);
+    if (rc != kOk) return release(rc);
+    done_steps += chunk;
+    if (can_finish_early && done_steps < max_new) {
+      rc = b200llm_read_status(e, slots.data(), batch, counts.data(), fin.data());
+      if (rc != kOk) return release(rc);
+      bool all = true;
+      for (int b = 0; b < batch; ++b) all = all && fin[b] != 0;
+      if (all) break;
+    }
+  }
+  rc = b200llm_read_status(e, slots.data(), batch, counts.data(), fin.data());
+  if (rc != kOk) return release(rc);
+  // one strided device->host copy of every row, then trim on the host
+  std::vector<int32_t> rows(static_cast<size_t>(batch) * e->cfg.max_new_tokens);
+  for (int b = 0; b < batch; ++b) {
+    const int n = std::min(counts[b], out_stride);
+    if (n > 0) {
+      cudaError_t err = cudaMemcpyAsync(rows.data() + static_cast<size_t>(b) * e->cfg.max_new_tokens,
+                                        e->out_tokens + static_cast<size_t>(slots[b]) * e->cfg.max_new_tokens,
+                                        n * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream);
+      if (err != cudaSuccess) return release(fail(kErrCuda, cudaGetErrorString(err)));
+    }
+  }
+  cudaError_t err = cudaStreamSynchronize(e->stream);
+  if (err != cudaSuccess) return release(fail(kErrCuda, cudaGetErrorString(err)));
+  for (int b = 0; b < batch; ++b) {
+    const int n = std::min(counts[b], out_stride);
+    for (int i = 0; i < out_stride; ++i) {
+      out_tokens[static_cast<size_t>(b) * out_stride + i] =
+          i < n ? rows[static_cast<size_t>(b) * e->cfg.max_new_tokens + i] : e->cfg.pad_token_id;
+    }
+    out_counts[b] = n;
+  }
+  return release(kOk);
+}
+
+int64_t b200llm_kernel_launches(const b200llm_engine* e) { return e ? e->launches : 0; }
+
+// ---- operator-level entry points ----------------------------------------------------------
+int b200llm_op_gemm(const void* act, const void* w, const float* bias, void* out, int32_t tokens,
+                    int32_t features, int32_t k, int32_t ld_out, int32_t epilogue, int32_t split_k,
+                    int32_t orientation, void* stream) {
+  GemmArgs g = {};
+  g.act = static_cast<const __nv_bfloat16*>(act);
+  g.w = static_cast<const __nv_bfloat16*>(w);
+  g.bias = bias;
+  g.out = out;
+  g.tokens = tokens;
+  g.features = features;
+  g.k = k;
+  g.ld_out = ld_out;
+  g.epilogue = epilogue;
+  g.split_k = split_k;
+  g.act_rows_alloc = tokens;
+  g.force_orientation = orientation;
+  g.pdl = 0;
+  return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_layernorm(float* x, const float* partials, int32_t n_partials, const float* add_bias,
+                         const float* gamma, const float* beta, void* out, int32_t rows, int32_t d,
+                         float eps, void* stream) {
+  B200_CHECK_ARG(x && gamma && beta && out, "op_layernorm: null argument");
+  LayerNormArgs a = {};
+  a.x = x;
+  a.partials = partials;
+  a.n_partials = n_partials;
+  a.partial_rows = rows;
+  a.add_bias = add_bias;
+  a.gamma = gamma;
+  a.beta = beta;
+  a.row_index = nullptr;
+  a.out = static_cast<__nv_bfloat16*>(out);
+  a.rows = rows;
+  a.d = d;
+  a.eps = eps;
+  a.pdl = 0;
+  return layernorm(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_embed(const float* wte, const float* wpe, const int32_t* ids, const int32_t* pos,
+                     float* x, int32_t n_tok, int32_t d, int32_t vocab, int32_t n_positions,
+                     void* stream) {
+  B200_CHECK_ARG(wte && wpe && ids && pos && x, "op_embed: null argument");
+  return embed_tokens(wte, wpe, ids, pos, x, n_tok, d, vocab, n_positions,
+                      reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_prefill_attention(const void* qkv, const int32_t* cu_seqlens_dev, int32_t batch,
+                                 int32_t max_seq_len, int32_t n_head, void* out, void* stream) {
+  B200_CHECK_ARG(qkv && cu_seqlens_dev && out, "op_prefill_attention: null argument");
+  return prefill_attention(static_cast<const __nv_bfloat16*>(qkv), cu_seqlens_dev, batch, max_seq_len,
+                           n_head, static_cast<__nv_bfloat16*>(out),
+                           reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_decode_attention(const void* qkv, const int32_t* seq_len, const int32_t* page_table,
+                                int32_t max_pages_per_seq, void* k_pool, void* v_pool, void* out,
+                                int32_t batch, int32_t n_head, int32_t n_splits, float* scratch,
+                                void* stream) {
+  B200_CHECK_ARG(qkv && seq_len && page_table && k_pool && v_pool && out,
+                 "op_decode_attention: null argument");
+  DecodeAttnArgs a = {};
+  a.qkv = static_cast<const __nv_bfloat16*>(qkv);
+  a.active_slots = nullptr;
+  a.seq_len = seq_len;
+  a.finished = nullptr;
+  a.page_table = page_table;
+  a.max_pages_per_seq = max_pages_per_seq;
+  a.k_pool = static_cast<__nv_bfloat16*>(k_pool);
+  a.v_pool = static_cast<__nv_bfloat16*>(v_pool);
+  a.out = static_cast<__nv_bfloat16*>(out);
+  a.batch = batch;
+  a.n_head = n_head;
+  a.n_splits = n_splits;
+  a.scratch = scratch;
+  a.pdl = 0;
+  return decode_attention(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t b200llm_decode_attention_scratch_floats(int32_t batch, int32_t n_head, int32_t n_splits) {
+  return decode_attention_scratch_floats(batch, n_head, n_splits);
+}
+
+int b200llm_op_argmax(const float* logits, int32_t rows, int32_t ld, int32_t vocab, int32_t* out,
+                      void* stream) {
+  B200_CHECK_ARG(logits && out, "op_argmax: null argument");
+  return argmax_rows(logits, rows, ld, vocab, out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_convert_transpose(const float* src, void* dst, int32_t rows, int32_t cols,
+                                 void* stream) {
+  B200_CHECK_ARG(src && dst, "op_convert_transpose: null argument");
+  return convert_transpose_bf16(src, static_cast<__nv_bfloat16*>(dst), rows, cols,
+                                reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

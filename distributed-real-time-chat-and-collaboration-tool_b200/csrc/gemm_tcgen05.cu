@@ -1,0 +1,566 @@
+// bf16 GEMM for the dense contractions of GPT-2 (QKV, attention out-proj, MLP up/down, LM
+// head) on B200: TMA-fed shared-memory ring, tcgen05.mma (UMMA 128xN, fp32 accumulators in
+// TMEM), warp-specialised persistent CTAs, fused epilogues.
+//
+// Oracle being reproduced: transformers Conv1D = addmm(bias, x, W[in,out])
+// (pytorch_utils.py:97-123) used at modeling_gpt2.py:106-107 (c_attn / c_proj),
+// :233-241 (MLP c_fc + gelu_new + c_proj), residual adds at :282 and :307, and the tied
+// LM head at :646-651 / :705-706.
+//
+// Logical problem:  out[token, feature] = sum_k act[token, k] * w[feature, k]   (+ epilogue)
+// Both operands are K-major (row-major [rows, k]); weights are transposed once at load.
+//
+// Two orientations share one kernel body:
+//   TRANS = false : UMMA M (128 TMEM lanes) = tokens,   UMMA N = features   (prefill)
+//   TRANS = true  : UMMA M (128 TMEM lanes) = features, UMMA N = tokens     (decode: "swap
+//                   AB" so a batch of 1..256 tokens does not waste the 128-row MMA and the
+//                   weight matrix is streamed exactly once)
+//
+// Warp roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM
+// allocator, warps 4-7 = epilogue (TMEM -> registers -> global).
+// Pipelines: smem ring full/empty (TMA <-> MMA), TMEM accumulator full/empty (MMA <->
+// epilogue, two accumulator stages so the epilogue of tile i overlaps the MMAs of tile i+1).
+#include "gemm_tcgen05.cuh"
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "common.cuh"
+
+namespace b200llm {
+
+namespace {
+
+constexpr int kBlockM = 128;  // UMMA M
+constexpr int kBlockK = 64;   // 64 bf16 = 128 B = one SWIZZLE_128B row
+constexpr int kUmmaK = 16;
+constexpr int kThreads = 256;
+constexpr int kAccumStages = 2;
+
+template <int BLOCK_N>
+struct TileCfg {
+  static constexpr int kABytes = kBlockM * kBlockK * 2;
+  static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BLOCK_N >= 256) ? 4 : (BLOCK_N >= 128) ? 6 : 8;
+  static constexpr int kTmemCols = (kAccumStages * BLOCK_N < 32) ? 32 : kAccumStages * BLOCK_N;
+  // ring + barriers + tmem base slot, plus 1024 B slack for manual alignment.
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
+};
+
+struct KernelArgs {
+  const float* bias;
+  void* out;
+  int a_rows;  // real rows of the 128-row operand
+  int b_rows;  // real rows of the N operand
+  int k_blocks_total;
+  int k_blocks_per_split;
+  int ld_out;
+  int tokens;  // logical token count (partials stride)
+};
+
+template <int N>
+__device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&r)[32]);
+
+template <>
+__device__ __forceinline__ void tmem_ld_cols<32>(uint32_t taddr, uint32_t (&r)[32]) {
+  tmem_ld_32x32(taddr, r);
+}
+
+template <>
+__device__ __forceinline__ void tmem_ld_cols<16>(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+template <int BLOCK_N, int EPI, bool TRANS>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+            const KernelArgs args) {
+  using Cfg = TileCfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr int kChunk = (BLOCK_N >= 32) ? 32 : 16;  // columns per tcgen05.ld
+
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles need 1024 B alignment.
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~static_cast<uintptr_t>(1023u));
+  uint8_t* ring = smem;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full_bar = empty_bar + kStages;
+  uint64_t* tmem_empty_bar = tmem_full_bar + kAccumStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + kAccumStages);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int num_m_blocks = (args.a_rows + kBlockM - 1) / kBlockM;
+  const int num_n_blocks = (args.b_rows + BLOCK_N - 1) / BLOCK_N;
+  const int num_tiles = num_m_blocks * num_n_blocks;
+  const int split = blockIdx.y;
+  const int kb_begin = split * args.k_blocks_per_split;
+  int kb_end = kb_begin + args.k_blocks_per_split;
+  if (kb_end > args.k_blocks_total) kb_end = args.k_blocks_total;
+  const int num_kb = kb_end - kb_begin;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < kAccumStages; ++s) {
+      mbar_init(&tmem_full_bar[s], 1);
+      mbar_init(&tmem_empty_bar[s], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      const int my_tiles =
+          (static_cast<int>(blockIdx.x) < num_tiles)
+              ? (num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                    static_cast<int>(gridDim.x)
+              : 0;
+      const int total_iters = my_tiles * num_kb;
+      // In the swapped orientation operand A is the weight matrix, which does not depend on
+      // the upstream kernel: fill the whole ring with weight tiles BEFORE the grid
+      // dependency resolves (programmatic dependent launch), so the weight stream of this
+      // GEMM overlaps the tail of the previous kernel. The activation operand must wait.
+      const int pre = TRANS ? (total_iters < kStages ? total_iters : kStages) : 0;
+      for (int it = 0; it < pre; ++it) {
+        const int tile = blockIdx.x + (it / num_kb) * gridDim.x;
+        const int kb = kb_begin + it % num_kb;
+        const int m_blk = tile % num_m_blocks;
+        uint8_t* sa = ring + it * Cfg::kStageBytes;
+        mbar_arrive_expect_tx(&full_bar[it], Cfg::kStageBytes);
+        tma_load_2d(sa, &map_a, &full_bar[it], kb * kBlockK, m_blk * kBlockM, kEvictFirst);
+      }
+      pdl_wait();
+      for (int it = 0; it < pre; ++it) {
+        const int tile = blockIdx.x + (it / num_kb) * gridDim.x;
+        const int kb = kb_begin + it % num_kb;
+        const int n_blk = tile / num_m_blocks;
+        uint8_t* sb = ring + it * Cfg::kStageBytes + Cfg::kABytes;
+        tma_load_2d(sb, &map_b, &full_bar[it], kb * kBlockK, n_blk * BLOCK_N, kEvictLast);
+      }
+      for (int it = pre; it < total_iters; ++it) {
+        const int stage = it % kStages;
+        const uint32_t phase = static_cast<uint32_t>(it / kStages) & 1u;
+        const int tile = blockIdx.x + (it / num_kb) * gridDim.x;
+        const int kb = kb_begin + it % num_kb;
+        const int m_blk = tile % num_m_blocks;
+        const int n_blk = tile / num_m_blocks;
+        mbar_wait(&empty_bar[stage], phase ^ 1u);
+        uint8_t* sa = ring + stage * Cfg::kStageBytes;
+        uint8_t* sb = sa + Cfg::kABytes;
+        mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        tma_load_2d(sa, &map_a, &full_bar[stage], kb * kBlockK, m_blk * kBlockM,
+                    TRANS ? kEvictFirst : kEvictNormal);
+        tma_load_2d(sb, &map_b, &full_bar[stage], kb * kBlockK, n_blk * BLOCK_N, kEvictLast);
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer (single thread) =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N);
+      int stage = 0;
+      uint32_t phase = 0;
+      int astage = 0;
+      uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty_bar[astage], aphase ^ 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(astage * BLOCK_N);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(ring + stage * Cfg::kStageBytes);
+          const uint32_t sb = sa + Cfg::kABytes;
+          const uint64_t desc_a = umma_desc_k_sw128(sa);
+          const uint64_t desc_b = umma_desc_k_sw128(sb);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in 16-byte units
+            umma_bf16_ss(tmem_d, desc_a + static_cast<uint64_t>(k * 2),
+                         desc_b + static_cast<uint64_t>(k * 2), idesc,
+                         (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma_commit(&tmem_full_bar[astage]);  // accumulator complete
+        if (++astage == kAccumStages) {
+          astage = 0;
+          aphase ^= 1u;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= Epilogue (128 threads, one TMEM lane each) =================
+    const int q = warp - 4;  // == warp % 4: TMEM lane quarter this warp may access
+    int astage = 0;
+    uint32_t aphase = 0;
+    pdl_wait();  // residual / output buffers may be read by the upstream kernel
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_blk = tile % num_m_blocks;
+      const int n_blk = tile / num_m_blocks;
+      mbar_wait(&tmem_full_bar[astage], aphase);
+      tc_fence_after();
+      const int a_row = m_blk * kBlockM + q * 32 + lane;  // row of the 128-row operand
+      const bool a_ok = a_row < args.a_rows;
+
+      float bias_lane = 0.0f;
+      if (TRANS && EPI != kEpiF32 && EPI != kEpiPartialF32 && a_ok && args.bias != nullptr) {
+        bias_lane = args.bias[a_row];
+      }
+
+#pragma unroll 1
+      for (int c0 = 0; c0 < BLOCK_N; c0 += kChunk) {
+        uint32_t r[32];
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                               static_cast<uint32_t>(astage * BLOCK_N + c0);
+        tmem_ld_cols<kChunk>(taddr, r);
+        tmem_ld_wait();
+        const int b_row0 = n_blk * BLOCK_N + c0;  // first row of the N operand in this chunk
+
+        if (TRANS) {
+          // lane = feature (a_row), columns = tokens. For each token the warp's 32 lanes
+          // write 32 consecutive features -> coalesced.
+          const int feature = a_row;
+#pragma unroll
+          for (int j = 0; j < kChunk; ++j) {
+            const int token = b_row0 + j;
+            if (a_ok && token < args.b_rows) {
+              float v = __uint_as_float(r[j]);
+              const size_t idx = static_cast<size_t>(token) * args.ld_out + feature;
+              if (EPI == kEpiBiasBf16) {
+                reinterpret_cast<__nv_bfloat16*>(args.out)[idx] = __float2bfloat16(v + bias_lane);
+              } else if (EPI == kEpiBiasGeluBf16) {
+                reinterpret_cast<__nv_bfloat16*>(args.out)[idx] =
+                    __float2bfloat16(gelu_new(v + bias_lane));
+              } else if (EPI == kEpiBiasResidF32) {
+                float* o = reinterpret_cast<float*>(args.out);
+                o[idx] = o[idx] + (v + bias_lane);
+              } else if (EPI == kEpiF32) {
+                reinterpret_cast<float*>(args.out)[idx] = v;
+              } else {  // kEpiPartialF32
+                const size_t pidx =
+                    (static_cast<size_t>(split) * args.tokens + token) * args.ld_out + feature;
+                reinterpret_cast<float*>(args.out)[pidx] = v;
+              }
+            }
+          }
+        } else {
+          // lane = token (a_row), columns = features: each thread owns a contiguous run of
+          // kChunk features of its token row.
+          const int token = a_row;
+          const int f0 = b_row0;
+          if (a_ok && f0 < args.b_rows) {
+            const bool full = (f0 + kChunk <= args.b_rows);
+            if (EPI == kEpiBiasBf16 || EPI == kEpiBiasGeluBf16) {
+              __nv_bfloat16* o =
+                  reinterpret_cast<__nv_bfloat16*>(args.out) + static_cast<size_t>(token) * args.ld_out + f0;
+              if (full && ((reinterpret_cast<uintptr_t>(o) & 15u) == 0)) {
+#pragma unroll
+                for (int j = 0; j < kChunk; j += 8) {
+                  float v[8];
+#pragma unroll
+                  for (int t = 0; t < 8; ++t) {
+                    float b = args.bias ? __ldg(args.bias + f0 + j + t) : 0.0f;
+                    float x = __uint_as_float(r[j + t]) + b;
+                    v[t] = (EPI == kEpiBiasGeluBf16) ? gelu_new(x) : x;
+                  }
+                  uint4 pk;
+                  pk.x = pack_bf16x2(v[0], v[1]);
+                  pk.y = pack_bf16x2(v[2], v[3]);
+                  pk.z = pack_bf16x2(v[4], v[5]);
+                  pk.w = pack_bf16x2(v[6], v[7]);
+                  *reinterpret_cast<uint4*>(o + j) = pk;
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < kChunk; ++j) {
+                  if (f0 + j < args.b_rows) {
+                    float b = args.bias ? __ldg(args.bias + f0 + j) : 0.0f;
+                    float x = __uint_as_float(r[j]) + b;
+                    o[j] = __float2bfloat16((EPI == kEpiBiasGeluBf16) ? gelu_new(x) : x);
+                  }
+                }
+              }
+            } else {
+              float* o;
+              if (EPI == kEpiPartialF32) {
+                o = reinterpret_cast<float*>(args.out) +
+                    (static_cast<size_t>(split) * args.tokens + token) * args.ld_out + f0;
+              } else {
+                o = reinterpret_cast<float*>(args.out) + static_cast<size_t>(token) * args.ld_out + f0;
+              }
+              if (full && ((reinterpret_cast<uintptr_t>(o) & 15u) == 0)) {
+#pragma unroll
+                for (int j = 0; j < kChunk; j += 4) {
+                  float4 v;
+                  v.x = __uint_as_float(r[j + 0]);
+                  v.y = __uint_as_float(r[j + 1]);
+                  v.z = __uint_as_float(r[j + 2]);
+                  v.w = __uint_as_float(r[j + 3]);
+                  if (EPI == kEpiBiasResidF32) {
+                    const float4 old = *reinterpret_cast<const float4*>(o + j);
+                    const float4 b = args.bias
+                                         ? __ldg(reinterpret_cast<const float4*>(args.bias + f0 + j))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v.x = old.x + (v.x + b.x);
+                    v.y = old.y + (v.y + b.y);
+                    v.z = old.z + (v.z + b.z);
+                    v.w = old.w + (v.w + b.w);
+                  }
+                  *reinterpret_cast<float4*>(o + j) = v;
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < kChunk; ++j) {
+                  if (f0 + j < args.b_rows) {
+                    float x = __uint_as_float(r[j]);
+                    if (EPI == kEpiBiasResidF32) {
+                      float b = args.bias ? __ldg(args.bias + f0 + j) : 0.0f;
+                      x = o[j] + (x + b);
+                    }
+                    o[j] = x;
+                  }
+                }
+              }
+            }
+          }
+        }
+      }
+      // All TMEM reads of this accumulator stage are complete (tcgen05.wait::ld above).
+      tc_fence_before();
+      mbar_arrive(&tmem_empty_bar[astage]);
+      if (++astage == kAccumStages) {
+        astage = 0;
+        aphase ^= 1u;
+      }
+    }
+  }
+
+  pdl_launch_dependents();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Host side: tensor maps + dispatch
+// ---------------------------------------------------------------------------------------
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess) {
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+  });
+  return fn;
+}
+
+using MapKey = std::tuple<const void*, int, int, int>;  // ptr, rows, cols, box_rows
+std::map<MapKey, CUtensorMap>& map_cache() {
+  static std::map<MapKey, CUtensorMap> cache;
+  return cache;
+}
+std::mutex& map_mutex() {
+  static std::mutex m;
+  return m;
+}
+
+// Row-major bf16 [rows, cols] matrix; box = [box_rows, 64 cols] with 128 B swizzle.
+int get_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lock(map_mutex());
+  MapKey key{ptr, rows, cols, box_rows};
+  auto it = map_cache().find(key);
+  if (it != map_cache().end()) {
+    *out = it->second;
+    return kOk;
+  }
+  EncodeTiledFn encode = get_encode_fn();
+  if (encode == nullptr) return fail(kErrCuda, "cuTensorMapEncodeTiled entry point unavailable");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15u) != 0) {
+    return fail(kErrInvalidArg, "GEMM operand must be 16-byte aligned for TMA");
+  }
+  CUtensorMap map;
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(kBlockK), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t elem_strides[2] = {1, 1};
+  CUresult r = encode(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
+                      strides, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    return fail(kErrCuda, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string(r));
+  }
+  map_cache()[key] = map;
+  *out = map;
+  return kOk;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <int BLOCK_N, int EPI, bool TRANS>
+int launch(const GemmArgs& g, cudaStream_t stream) {
+  using Cfg = TileCfg<BLOCK_N>;
+  const int a_rows = TRANS ? g.features : g.tokens;
+  const int b_rows = TRANS ? g.tokens : g.features;
+  const void* a_ptr = TRANS ? static_cast<const void*>(g.w) : static_cast<const void*>(g.act);
+  const void* b_ptr = TRANS ? static_cast<const void*>(g.act) : static_cast<const void*>(g.w);
+  const int act_rows = g.act_rows_alloc > 0 ? g.act_rows_alloc : g.tokens;
+  const int a_rows_map = TRANS ? g.features : act_rows;
+  const int b_rows_map = TRANS ? act_rows : g.features;
+
+  CUtensorMap map_a, map_b;
+  B200_PROPAGATE(get_tensor_map(a_ptr, a_rows_map, g.k, kBlockM, &map_a));
+  B200_PROPAGATE(get_tensor_map(b_ptr, b_rows_map, g.k, BLOCK_N, &map_b));
+
+  KernelArgs ka;
+  ka.bias = g.bias;
+  ka.out = g.out;
+  ka.a_rows = a_rows;
+  ka.b_rows = b_rows;
+  ka.k_blocks_total = g.k / kBlockK;
+  const int split = g.split_k > 0 ? g.split_k : 1;
+  ka.k_blocks_per_split = (ka.k_blocks_total + split - 1) / split;
+  ka.ld_out = g.ld_out;
+  ka.tokens = g.tokens;
+
+  const int num_tiles = ((a_rows + kBlockM - 1) / kBlockM) * ((b_rows + BLOCK_N - 1) / BLOCK_N);
+  int grid_x = num_tiles < num_sms() ? num_tiles : num_sms();
+  if (split > 1) {
+    int cap = num_sms() / split;
+    if (cap < 1) cap = 1;
+    if (grid_x > cap) grid_x = cap;
+  }
+
+  auto kernel = gemm_kernel<BLOCK_N, EPI, TRANS>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid_x, split, 1);
+  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = g.pdl ? 1 : 0;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, ka));
+  return kOk;
+}
+
+template <int BLOCK_N, bool TRANS>
+int dispatch_epi(const GemmArgs& g, cudaStream_t stream) {
+  switch (g.epilogue) {
+    case kEpiBiasBf16:
+      return launch<BLOCK_N, kEpiBiasBf16, TRANS>(g, stream);
+    case kEpiBiasGeluBf16:
+      return launch<BLOCK_N, kEpiBiasGeluBf16, TRANS>(g, stream);
+    case kEpiBiasResidF32:
+      return launch<BLOCK_N, kEpiBiasResidF32, TRANS>(g, stream);
+    case kEpiF32:
+      return launch<BLOCK_N, kEpiF32, TRANS>(g, stream);
+    case kEpiPartialF32:
+      return launch<BLOCK_N, kEpiPartialF32, TRANS>(g, stream);
+    default:
+      return fail(kErrInvalidArg, "unknown GEMM epilogue");
+  }
+}
+
+}  // namespace
+
+void gemm_clear_tensor_map_cache() {
+  std::lock_guard<std::mutex> lock(map_mutex());
+  map_cache().clear();
+}
+
+int gemm_bf16(const GemmArgs& g, cudaStream_t stream) {
+  B200_CHECK_ARG(g.act && g.w && g.out, "gemm: null operand");
+  B200_CHECK_ARG(g.tokens > 0 && g.features > 0 && g.k > 0, "gemm: empty problem");
+  B200_CHECK_ARG(g.k % kBlockK == 0, "gemm: k must be a multiple of 64");
+  B200_CHECK_ARG(g.split_k <= 1 || g.epilogue == kEpiPartialF32,
+                 "gemm: split_k > 1 requires the partial epilogue");
+  B200_CHECK_ARG(g.split_k <= 1 || (g.k / kBlockK) % g.split_k == 0,
+                 "gemm: split_k must divide the number of 64-wide k blocks");
+
+  bool trans;
+  if (g.force_orientation == 0) {
+    trans = false;
+  } else if (g.force_orientation == 1) {
+    trans = true;
+  } else {
+    // Up to 256 tokens fit one UMMA N tile: stream the weights once, tokens on N.
+    trans = g.tokens <= 256;
+  }
+
+  if (trans) {
+    if (g.tokens <= 16) return dispatch_epi<16, true>(g, stream);
+    if (g.tokens <= 32) return dispatch_epi<32, true>(g, stream);
+    if (g.tokens <= 64) return dispatch_epi<64, true>(g, stream);
+    if (g.tokens <= 128) return dispatch_epi<128, true>(g, stream);
+    return dispatch_epi<256, true>(g, stream);
+  }
+  // tokens on M. Wide N tiles when there is enough work to fill the machine.
+  const long tiles256 = static_cast<long>((g.tokens + 127) / 128) * ((g.features + 255) / 256);
+  if (g.features % 256 == 0 && tiles256 >= num_sms()) return dispatch_epi<256, false>(g, stream);
+  return dispatch_epi<128, false>(g, stream);
+}
+
+}  // namespace b200llm

@@ -1,0 +1,43 @@
+// Host-visible interface of the tcgen05/TMA GEMM (gemm_tcgen05.cu).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200llm {
+
+// Epilogue selector. "token" / "feature" below are logical output coordinates: the GEMM
+// always produces out[token, feature] = sum_k act[token, k] * w[feature, k].
+enum GemmEpilogue : int {
+  kEpiBiasBf16 = 0,      // out_bf16 = acc + bias[feature]
+  kEpiBiasGeluBf16 = 1,  // out_bf16 = gelu_new(acc + bias[feature])
+  kEpiBiasResidF32 = 2,  // out_f32 += acc + bias[feature]   (in-place residual stream)
+  kEpiF32 = 3,           // out_f32 = acc                    (LM-head logits, no bias)
+  kEpiPartialF32 = 4,    // split-K partial: out_f32[split][token, feature] = acc
+};
+
+struct GemmArgs {
+  const __nv_bfloat16* act;  // [tokens, k] row-major
+  const __nv_bfloat16* w;    // [features, k] row-major (pre-transposed Conv1D weight)
+  const float* bias;         // [features] or null
+  void* out;                 // [tokens, ld_out] bf16 or fp32 depending on epilogue
+  int tokens;
+  int features;
+  int k;
+  int ld_out;
+  int epilogue;
+  int split_k;         // >= 1; > 1 only with kEpiPartialF32 (partials reduced by the consumer)
+  int act_rows_alloc;  // rows backing `act` (>= tokens) for the tensor map
+  int force_orientation;  // -1 auto, 0 tokens-on-M, 1 weights-on-M (swap-AB)
+  int pdl;                // launch with programmatic stream serialization
+};
+
+// Enqueue one GEMM on `stream`. Returns 0 or an error code (see common.cuh Status).
+int gemm_bf16(const GemmArgs& args, cudaStream_t stream);
+
+// Drop cached tensor maps (engine teardown / tests).
+void gemm_clear_tensor_map_cache();
+
+}  // namespace b200llm

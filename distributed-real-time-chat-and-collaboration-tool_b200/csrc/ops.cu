@@ -1,0 +1,451 @@
+// Memory-bound kernels of the GPT-2 step (see ops.cuh for the oracle citations).
+// All are HBM/L2 streaming kernels: 16-byte vector accesses, one warp per activation row,
+// warp-shuffle reductions, no shared-memory staging unless a cross-warp reduction needs it.
+#include "ops.cuh"
+
+#include "common.cuh"
+
+namespace b200llm {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------
+// Embedding
+// ---------------------------------------------------------------------------------------
+__global__ void embed_kernel(const float* __restrict__ wte, const float* __restrict__ wpe,
+                             const int32_t* __restrict__ ids, const int32_t* __restrict__ pos,
+                             const int32_t* __restrict__ active_slots,
+                             const int32_t* __restrict__ last_tok,
+                             const int32_t* __restrict__ seq_len, float* __restrict__ x,
+                             int n_rows, int d, int vocab, int n_positions) {
+  pdl_wait();
+  const int row = blockIdx.x;
+  if (row >= n_rows) return;
+  int tok, p;
+  if (active_slots != nullptr) {
+    const int slot = active_slots[row];
+    if (slot < 0) {
+      tok = 0;
+      p = 0;
+    } else {
+      tok = last_tok[slot];
+      p = seq_len[slot];
+    }
+  } else {
+    tok = ids[row];
+    p = pos[row];
+  }
+  // Clamp instead of faulting on a corrupt id; the host validates ids up front.
+  tok = min(max(tok, 0), vocab - 1);
+  p = min(max(p, 0), n_positions - 1);
+  const float4* e = reinterpret_cast<const float4*>(wte + static_cast<size_t>(tok) * d);
+  const float4* q = reinterpret_cast<const float4*>(wpe + static_cast<size_t>(p) * d);
+  float4* o = reinterpret_cast<float4*>(x + static_cast<size_t>(row) * d);
+  for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
+    const float4 a = __ldg(e + i);
+    const float4 b = __ldg(q + i);
+    o[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+  }
+  pdl_launch_dependents();
+}
+
+// ---------------------------------------------------------------------------------------
+// LayerNorm (+ residual / split-K reduction)
+// ---------------------------------------------------------------------------------------
+template <int VEC>  // float4 per lane; d = VEC * 128
+__global__ void __launch_bounds__(128)
+layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int n_partials,
+                 const float* __restrict__ add_bias, const float* __restrict__ gamma,
+                 const float* __restrict__ beta, const int32_t* __restrict__ row_index,
+                 __nv_bfloat16* __restrict__ out, int rows, int rows_total, float eps) {
+  constexpr int D = VEC * 128;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int orow = blockIdx.x * 4 + warp;
+  pdl_wait();
+  if (orow >= rows) return;
+  const int irow = row_index ? row_index[orow] : orow;
+
+  float4 v[VEC];
+  float4* xr = reinterpret_cast<float4*>(x + static_cast<size_t>(irow) * D);
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) v[i] = xr[lane + 32 * i];
+
+  if (n_partials > 0) {
+    // x += bias + sum_s partial[s]  -- fixed summation order => deterministic
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+      float4 acc = add_bias ? __ldg(reinterpret_cast<const float4*>(add_bias) + lane + 32 * i)
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int s = 0; s < n_partials; ++s) {
+        const float4 p = *(reinterpret_cast<const float4*>(
+                               partials + (static_cast<size_t>(s) * rows_total + irow) * D) +
+                           lane + 32 * i);
+        acc.x += p.x;
+        acc.y += p.y;
+        acc.z += p.z;
+        acc.w += p.w;
+      }
+      v[i].x += acc.x;
+      v[i].y += acc.y;
+      v[i].z += acc.z;
+      v[i].w += acc.w;
+      xr[lane + 32 * i] = v[i];
+    }
+  }
+
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  const float mean = warp_sum(sum) * (1.0f / D);
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) {
+    const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, e = v[i].w - mean;
+    sq += (a * a + b * b) + (c * c + e * e);
+  }
+  const float var = warp_sum(sq) * (1.0f / D);
+  const float rstd = 1.0f / sqrtf(var + eps);
+
+  uint2* orow_ptr = reinterpret_cast<uint2*>(out + static_cast<size_t>(orow) * D);
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) {
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + lane + 32 * i);
+    uint2 pk;
+    pk.x = pack_bf16x2((v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y);
+    pk.y = pack_bf16x2((v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w);
+    orow_ptr[lane + 32 * i] = pk;
+  }
+  pdl_launch_dependents();
+}
+
+// ---------------------------------------------------------------------------------------
+// Token selection
+// ---------------------------------------------------------------------------------------
+struct MaxIdx {
+  float v;
+  int i;
+};
+
+__device__ __forceinline__ MaxIdx better(MaxIdx a, MaxIdx b) {
+  // larger value wins; on equal values the lower index wins (torch.argmax on ties)
+  if (b.v > a.v || (b.v == a.v && b.i < a.i)) return b;
+  return a;
+}
+
+__device__ __forceinline__ MaxIdx block_argmax(MaxIdx m, MaxIdx* smem) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    MaxIdx other;
+    other.v = __shfl_xor_sync(0xffffffffu, m.v, o);
+    other.i = __shfl_xor_sync(0xffffffffu, m.i, o);
+    m = better(m, other);
+  }
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nwarps = blockDim.x >> 5;
+  __syncthreads();
+  if (lane == 0) smem[warp] = m;
+  __syncthreads();
+  if (warp == 0) {
+    MaxIdx t;
+    t.v = -INFINITY;
+    t.i = 0x7fffffff;
+    if (lane < nwarps) t = smem[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      MaxIdx other;
+      other.v = __shfl_xor_sync(0xffffffffu, t.v, o);
+      other.i = __shfl_xor_sync(0xffffffffu, t.i, o);
+      t = better(t, other);
+    }
+    if (lane == 0) smem[0] = t;
+  }
+  __syncthreads();
+  return smem[0];
+}
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+constexpr int kMaxTopK = 64;
+
+__global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
+  __shared__ MaxIdx red[32];
+  __shared__ float top_v[kMaxTopK];
+  __shared__ int top_i[kMaxTopK];
+  pdl_wait();
+  const int row = blockIdx.x;
+  const int slot = a.active_slots ? a.active_slots[row] : row;
+  if (slot < 0) return;
+  const float* lg = a.logits + static_cast<size_t>(row) * a.ld;
+  const int g = a.n_gen[slot];
+  const bool ban_eos = g < a.min_new[slot];  // MinNewTokensLength: EOS logit = -inf
+  const int was_finished = a.finished[slot];
+
+  const float temperature = a.temperature ? a.temperature[slot] : 0.0f;
+  const int top_k_req = a.top_k ? a.top_k[slot] : 0;
+  const uint64_t seed = a.seed ? a.seed[slot] : 0ull;
+
+  int chosen;
+  if (temperature <= 0.0f || top_k_req <= 1) {
+    MaxIdx m;
+    m.v = -INFINITY;
+    m.i = 0x7fffffff;
+    for (int i = threadIdx.x; i < a.vocab; i += blockDim.x) {
+      if (ban_eos && i == a.eos_id) continue;
+      MaxIdx c;
+      c.v = lg[i];
+      c.i = i;
+      m = better(m, c);
+    }
+    m = block_argmax(m, red);
+    chosen = m.i;
+  } else {
+    // top-k by k successive block-wide argmax passes over the (L2-resident) logits row,
+    // then a temperature softmax over the k survivors and one inverse-CDF draw.
+    const int k = top_k_req < kMaxTopK ? top_k_req : kMaxTopK;
+    float prev_v = INFINITY;
+    int prev_i = -1;
+    for (int r = 0; r < k; ++r) {
+      MaxIdx m;
+      m.v = -INFINITY;
+      m.i = 0x7fffffff;
+      for (int i = threadIdx.x; i < a.vocab; i += blockDim.x) {
+        if (ban_eos && i == a.eos_id) continue;
+        const float v = lg[i];
+        // strictly after (prev_v, prev_i) in (value desc, index asc) order
+        if (v > prev_v || (v == prev_v && i <= prev_i)) continue;
+        MaxIdx c;
+        c.v = v;
+        c.i = i;
+        m = better(m, c);
+      }
+      m = block_argmax(m, red);
+      prev_v = m.v;
+      prev_i = m.i;
+      if (threadIdx.x == 0) {
+        top_v[r] = m.v;
+        top_i[r] = m.i;
+      }
+    }
+    __syncthreads();
+    chosen = top_i[0];
+    if (threadIdx.x == 0) {
+      const float inv_t = 1.0f / temperature;
+      const float mx = top_v[0];
+      float z = 0.f;
+      for (int r = 0; r < k; ++r) z += expf((top_v[r] - mx) * inv_t);
+      const uint64_t h = splitmix64(seed ^ splitmix64(static_cast<uint64_t>(slot) << 32 | static_cast<uint32_t>(g)));
+      const float u = static_cast<float>(h >> 40) * (1.0f / 16777216.0f) * z;
+      float c = 0.f;
+      int pick = top_i[k - 1];
+      for (int r = 0; r < k; ++r) {
+        c += expf((top_v[r] - mx) * inv_t);
+        if (u < c) {
+          pick = top_i[r];
+          break;
+        }
+      }
+      red[1].i = pick;
+    }
+    __syncthreads();
+    chosen = red[1].i;
+  }
+
+  if (threadIdx.x == 0) {
+    const int tok = was_finished ? a.pad_id : chosen;
+    const int cap = a.max_new[slot];
+    if (g < cap) {
+      a.out_tokens[static_cast<size_t>(slot) * a.out_stride + g] = tok;
+      a.n_gen[slot] = g + 1;
+    }
+    a.last_tok[slot] = tok;
+    if (!was_finished && (tok == a.eos_id || g + 1 >= cap)) a.finished[slot] = 1;
+    if (a.advance_seq && !was_finished) a.seq_len[slot] = a.seq_len[slot] + 1;
+  }
+  pdl_launch_dependents();
+}
+
+__global__ void __launch_bounds__(1024)
+argmax_rows_kernel(const float* __restrict__ logits, int ld, int vocab, int32_t* __restrict__ out) {
+  __shared__ MaxIdx red[32];
+  const float* lg = logits + static_cast<size_t>(blockIdx.x) * ld;
+  MaxIdx m;
+  m.v = -INFINITY;
+  m.i = 0x7fffffff;
+  for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+    MaxIdx c;
+    c.v = lg[i];
+    c.i = i;
+    m = better(m, c);
+  }
+  m = block_argmax(m, red);
+  if (threadIdx.x == 0) out[blockIdx.x] = m.i;
+}
+
+// ---------------------------------------------------------------------------------------
+// KV scatter (prefill): qkv rows -> pages  [page][head][16 tokens][64 dims]
+// ---------------------------------------------------------------------------------------
+__global__ void kv_scatter_kernel(const __nv_bfloat16* __restrict__ qkv,
+                                  const int32_t* __restrict__ row_slot,
+                                  const int32_t* __restrict__ row_pos,
+                                  const int32_t* __restrict__ page_table, int max_pages_per_seq,
+                                  __nv_bfloat16* __restrict__ k_pool,
+                                  __nv_bfloat16* __restrict__ v_pool, int n_tok, int n_head) {
+  const int d = n_head * kHeadDim;
+  const int chunks_per_row = 2 * d / 8;  // 16-byte chunks of K then V
+  const long gid = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (gid >= static_cast<long>(n_tok) * chunks_per_row) return;
+  const int t = static_cast<int>(gid / chunks_per_row);
+  const int c = static_cast<int>(gid % chunks_per_row);
+  const int is_v = c >= d / 8;
+  const int cc = is_v ? c - d / 8 : c;
+  const int head = cc / 8;
+  const int sub = cc % 8;
+  const int slot = row_slot[t];
+  const int pos = row_pos[t];
+  const int page = page_table[static_cast<size_t>(slot) * max_pages_per_seq + pos / kPageTokens];
+  const uint4 val = *reinterpret_cast<const uint4*>(qkv + static_cast<size_t>(t) * 3 * d +
+                                                   (is_v ? 2 * d : d) + head * kHeadDim + sub * 8);
+  __nv_bfloat16* pool = is_v ? v_pool : k_pool;
+  const size_t dst = ((static_cast<size_t>(page) * n_head + head) * kPageTokens + pos % kPageTokens) *
+                         kHeadDim + sub * 8;
+  *reinterpret_cast<uint4*>(pool + dst) = val;
+}
+
+// ---------------------------------------------------------------------------------------
+// Weight conversion
+// ---------------------------------------------------------------------------------------
+__global__ void convert_transpose_kernel(const float* __restrict__ src,
+                                         __nv_bfloat16* __restrict__ dst, int rows, int cols) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int r = r0 + j, c = c0 + threadIdx.x;
+    tile[j][threadIdx.x] = (r < rows && c < cols) ? src[static_cast<size_t>(r) * cols + c] : 0.f;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int c = c0 + j, r = r0 + threadIdx.x;  // dst[c][r]
+    if (c < cols && r < rows) dst[static_cast<size_t>(c) * rows + r] = __float2bfloat16(tile[threadIdx.x][j]);
+  }
+}
+
+__global__ void convert_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                               size_t n) {
+  size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (; i < n; i += stride) dst[i] = __float2bfloat16(src[i]);
+}
+
+template <typename Kernel, typename... Args>
+int launch_pdl(Kernel kernel, dim3 grid, dim3 block, cudaStream_t stream, int pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, args...));
+  return kOk;
+}
+
+}  // namespace
+
+int embed_tokens(const float* wte, const float* wpe, const int32_t* ids, const int32_t* pos,
+                 float* x, int n_tok, int d, int vocab, int n_positions, cudaStream_t stream) {
+  B200_CHECK_ARG(n_tok > 0 && d % 4 == 0, "embed: bad shape");
+  embed_kernel<<<n_tok, 128, 0, stream>>>(wte, wpe, ids, pos, nullptr, nullptr, nullptr, x, n_tok,
+                                          d, vocab, n_positions);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+int embed_decode(const float* wte, const float* wpe, const int32_t* active_slots,
+                 const int32_t* last_tok, const int32_t* seq_len, float* x, int batch, int d,
+                 int vocab, int n_positions, cudaStream_t stream) {
+  B200_CHECK_ARG(batch > 0 && d % 4 == 0, "embed: bad shape");
+  embed_kernel<<<batch, 128, 0, stream>>>(wte, wpe, nullptr, nullptr, active_slots, last_tok,
+                                          seq_len, x, batch, d, vocab, n_positions);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+int layernorm(const LayerNormArgs& a, cudaStream_t stream) {
+  B200_CHECK_ARG(a.rows > 0 && a.d % 128 == 0, "layernorm: d must be a multiple of 128");
+  const dim3 grid((a.rows + 3) / 4), block(128);
+  // rows_total (stride between split-K partial planes) is the number of input rows.
+  const int rows_total = a.partial_rows > 0 ? a.partial_rows : a.rows;
+#define B200_LN_CASE(V)                                                                        \
+  case V:                                                                                      \
+    return launch_pdl(layernorm_kernel<V>, grid, block, stream, a.pdl, a.x, a.partials,        \
+                      a.n_partials, a.add_bias, a.gamma, a.beta, a.row_index, a.out, a.rows,   \
+                      rows_total, a.eps);
+  switch (a.d / 128) {
+    B200_LN_CASE(1)
+    B200_LN_CASE(2)
+    B200_LN_CASE(3)
+    B200_LN_CASE(4)
+    B200_LN_CASE(6)
+    B200_LN_CASE(8)
+    B200_LN_CASE(10)
+    B200_LN_CASE(12)
+    B200_LN_CASE(16)
+    default:
+      return fail(kErrUnsupported, "layernorm: unsupported hidden size");
+  }
+#undef B200_LN_CASE
+}
+
+int select_tokens(const SelectArgs& a, cudaStream_t stream) {
+  B200_CHECK_ARG(a.batch > 0 && a.vocab > 0, "select: bad shape");
+  select_kernel<<<a.batch, 1024, 0, stream>>>(a);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+int argmax_rows(const float* logits, int rows, int ld, int vocab, int32_t* out,
+                cudaStream_t stream) {
+  B200_CHECK_ARG(rows > 0 && vocab > 0, "argmax: bad shape");
+  argmax_rows_kernel<<<rows, 1024, 0, stream>>>(logits, ld, vocab, out);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+int kv_scatter(const __nv_bfloat16* qkv, const int32_t* row_slot, const int32_t* row_pos,
+               const int32_t* page_table, int max_pages_per_seq, __nv_bfloat16* k_pool,
+               __nv_bfloat16* v_pool, int n_tok, int n_head, cudaStream_t stream) {
+  const long total = static_cast<long>(n_tok) * (2 * n_head * kHeadDim / 8);
+  const int block = 256;
+  const long grid = (total + block - 1) / block;
+  kv_scatter_kernel<<<static_cast<unsigned>(grid), block, 0, stream>>>(
+      qkv, row_slot, row_pos, page_table, max_pages_per_seq, k_pool, v_pool, n_tok, n_head);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+int convert_transpose_bf16(const float* src, __nv_bfloat16* dst, int rows, int cols,
+                           cudaStream_t stream) {
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32), block(32, 8);
+  convert_transpose_kernel<<<grid, block, 0, stream>>>(src, dst, rows, cols);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+int convert_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t stream) {
+  convert_kernel<<<1024, 256, 0, stream>>>(src, dst, n);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+}  // namespace b200llm

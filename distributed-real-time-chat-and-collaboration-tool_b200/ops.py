@@ -1,0 +1,103 @@
+"""Operator-level calls into the C ABI with torch tensors as device buffers.
+
+torch is plumbing here (allocation + streams); every computation happens in libb200llm.so.
+Used by the kernel parity tests and the profiling scripts.
+"""
+from __future__ import annotations
+
+import torch
+
+from ._lib import check, lib
+
+EPI_BIAS_BF16 = 0
+EPI_BIAS_GELU_BF16 = 1
+EPI_BIAS_RESID_F32 = 2
+EPI_F32 = 3
+EPI_PARTIAL_F32 = 4
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: torch.Tensor | None) -> int | None:
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "device-resident contiguous tensor required"
+    return t.data_ptr()
+
+
+def gemm(act: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, out: torch.Tensor,
+         epilogue: int, split_k: int = 1, orientation: int = -1) -> torch.Tensor:
+    """out[token, feature] (+)= act[token, :] . w[feature, :]  (+ epilogue)."""
+    tokens, k = act.shape
+    features, k2 = w.shape
+    assert k == k2 and act.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    ld_out = out.shape[-1]
+    check(lib.b200llm_op_gemm(_ptr(act), _ptr(w), _ptr(bias), _ptr(out), tokens, features, k,
+                              ld_out, epilogue, split_k, orientation, _stream()))
+    return out
+
+
+def layernorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,
+              partials: torch.Tensor | None = None, add_bias: torch.Tensor | None = None) -> torch.Tensor:
+    rows, d = x.shape
+    assert x.dtype == torch.float32
+    out = torch.empty(rows, d, dtype=torch.bfloat16, device=x.device)
+    n_partials = 0 if partials is None else partials.shape[0]
+    check(lib.b200llm_op_layernorm(_ptr(x), _ptr(partials), n_partials, _ptr(add_bias), _ptr(gamma),
+                                   _ptr(beta), _ptr(out), rows, d, eps, _stream()))
+    return out
+
+
+def embed(wte: torch.Tensor, wpe: torch.Tensor, ids: torch.Tensor, pos: torch.Tensor) -> torch.Tensor:
+    n_tok = ids.numel()
+    vocab, d = wte.shape
+    x = torch.empty(n_tok, d, dtype=torch.float32, device=wte.device)
+    check(lib.b200llm_op_embed(_ptr(wte), _ptr(wpe), _ptr(ids), _ptr(pos), _ptr(x), n_tok, d, vocab,
+                               wpe.shape[0], _stream()))
+    return x
+
+
+def prefill_attention(qkv: torch.Tensor, cu_seqlens: torch.Tensor, max_seq_len: int,
+                      n_head: int) -> torch.Tensor:
+    n_tok = qkv.shape[0]
+    d = n_head * 64
+    assert qkv.shape[1] == 3 * d and qkv.dtype == torch.bfloat16
+    out = torch.zeros(n_tok, d, dtype=torch.bfloat16, device=qkv.device)
+    check(lib.b200llm_op_prefill_attention(_ptr(qkv), _ptr(cu_seqlens), cu_seqlens.numel() - 1,
+                                           max_seq_len, n_head, _ptr(out), _stream()))
+    return out
+
+
+def decode_attention_scratch_floats(batch: int, n_head: int, n_splits: int) -> int:
+    return int(lib.b200llm_decode_attention_scratch_floats(batch, n_head, n_splits))
+
+
+def decode_attention(qkv: torch.Tensor, seq_len: torch.Tensor, page_table: torch.Tensor,
+                     k_pool: torch.Tensor, v_pool: torch.Tensor, n_head: int, n_splits: int = 1,
+                     scratch: torch.Tensor | None = None) -> torch.Tensor:
+    batch = qkv.shape[0]
+    d = n_head * 64
+    out = torch.zeros(batch, d, dtype=torch.bfloat16, device=qkv.device)
+    if n_splits > 1 and scratch is None:
+        scratch = torch.empty(decode_attention_scratch_floats(batch, n_head, n_splits),
+                              dtype=torch.float32, device=qkv.device)
+    check(lib.b200llm_op_decode_attention(_ptr(qkv), _ptr(seq_len), _ptr(page_table),
+                                          page_table.shape[1], _ptr(k_pool), _ptr(v_pool), _ptr(out),
+                                          batch, n_head, n_splits, _ptr(scratch), _stream()))
+    return out
+
+
+def argmax(logits: torch.Tensor, vocab: int | None = None) -> torch.Tensor:
+    rows, ld = logits.shape
+    out = torch.empty(rows, dtype=torch.int32, device=logits.device)
+    check(lib.b200llm_op_argmax(_ptr(logits), rows, ld, vocab or ld, _ptr(out), _stream()))
+    return out
+
+
+def convert_transpose(src: torch.Tensor) -> torch.Tensor:
+    rows, cols = src.shape
+    dst = torch.empty(cols, rows, dtype=torch.bfloat16, device=src.device)
+    check(lib.b200llm_op_convert_transpose(_ptr(src), _ptr(dst), rows, cols, _stream()))
+    return dst

@@ -1,0 +1,223 @@
+"""Kernel-level parity: each CUDA op, called through the C ABI, against a plain PyTorch fp32
+reference of the same op on the same inputs (oracle citations live in include/b200llm.h).
+
+Tolerances: GEMM inputs are bf16 and accumulate in fp32 -> the only error vs the fp32 reference
+of the SAME bf16 inputs is summation order (1e-3 relative on O(1) outputs) plus the bf16
+rounding of bf16 outputs (2^-8 relative)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+
+def gelu_new(x):
+    return 0.5 * x * (1.0 + torch.tanh(math.sqrt(2.0 / math.pi) * (x + 0.044715 * x.pow(3))))
+
+
+def _gemm_inputs(tokens, features, k, dev, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    act = (torch.randn(tokens, k, generator=g) * 0.5).to(torch.bfloat16).to(dev)
+    w = (torch.randn(features, k, generator=g) * 0.05).to(torch.bfloat16).to(dev)
+    bias = (torch.randn(features, generator=g) * 0.1).to(dev)
+    return act, w, bias
+
+
+@pytest.mark.parametrize("tokens,features,k,orientation", [
+    (64, 2304, 768, 1),     # decode QKV, swap-AB
+    (1, 768, 768, 1),       # single token
+    (13, 3072, 768, 1),     # ragged batch -> 16-wide N tile
+    (40, 1024, 1024, 1),    # 64-wide tile with padding rows
+    (100, 1280, 5120, 1),   # large-model MLP down-proj
+    (256, 768, 3072, 1),
+    (300, 768, 768, 1),     # > 256 tokens in swap-AB: two N tiles
+    (128, 2304, 768, 0),    # prefill orientation, single M tile
+    (1000, 3072, 768, 0),   # ragged M, 128-wide N
+    (8192, 2304, 768, 0),   # BASELINE config 2 prefill QKV -> 256-wide N tiles, persistent
+    (333, 768, 3072, -1),   # auto
+])
+def test_gemm_bias_bf16(ops, cuda, tokens, features, k, orientation):
+    act, w, bias = _gemm_inputs(tokens, features, k, cuda)
+    out = torch.zeros(tokens, features, dtype=torch.bfloat16, device=cuda)
+    ops.gemm(act, w, bias, out, ops.EPI_BIAS_BF16, orientation=orientation)
+    torch.cuda.synchronize()
+    ref = act.float() @ w.float().t() + bias
+    err = (out.float() - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    assert err <= 2e-3 * scale + 2 ** -8 * scale, (err, scale)
+
+
+@pytest.mark.parametrize("orientation,tokens", [(1, 64), (0, 512)])
+def test_gemm_gelu(ops, cuda, orientation, tokens):
+    act, w, bias = _gemm_inputs(tokens, 3072, 768, cuda, seed=1)
+    out = torch.zeros(tokens, 3072, dtype=torch.bfloat16, device=cuda)
+    ops.gemm(act, w, bias, out, ops.EPI_BIAS_GELU_BF16, orientation=orientation)
+    torch.cuda.synchronize()
+    ref = gelu_new(act.float() @ w.float().t() + bias)
+    assert (out.float() - ref).abs().max().item() <= 1e-2 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("orientation,tokens", [(1, 64), (1, 7), (0, 640)])
+def test_gemm_residual_f32(ops, cuda, orientation, tokens):
+    act, w, bias = _gemm_inputs(tokens, 768, 3072, cuda, seed=2)
+    resid = torch.randn(tokens, 768, device=cuda)
+    out = resid.clone()
+    ops.gemm(act, w, bias, out, ops.EPI_BIAS_RESID_F32, orientation=orientation)
+    torch.cuda.synchronize()
+    ref = resid + act.float() @ w.float().t() + bias
+    assert (out - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("orientation,tokens", [(1, 64), (1, 3), (0, 260)])
+def test_gemm_lm_head_f32_odd_vocab(ops, cuda, orientation, tokens):
+    vocab = 50257  # not a multiple of anything: masked tail tile + unaligned rows
+    act, w, _ = _gemm_inputs(tokens, vocab, 768, cuda, seed=3)
+    out = torch.full((tokens, vocab), float("nan"), device=cuda)
+    ops.gemm(act, w, None, out, ops.EPI_F32, orientation=orientation)
+    torch.cuda.synchronize()
+    ref = act.float() @ w.float().t()
+    assert torch.isfinite(out).all()
+    assert (out - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("split", [2, 6, 12, 24])
+def test_gemm_split_k_partials_then_layernorm(ops, cuda, split):
+    tokens, d, k = 64, 768, 3072
+    if (k // 64) % split:
+        pytest.skip("split must divide k blocks")
+    act, w, bias = _gemm_inputs(tokens, d, k, cuda, seed=4)
+    partials = torch.zeros(split, tokens, d, device=cuda)
+    ops.gemm(act, w, None, partials, ops.EPI_PARTIAL_F32, split_k=split, orientation=1)
+    x = torch.randn(tokens, d, device=cuda)
+    x0 = x.clone()
+    gamma = torch.rand(d, device=cuda) + 0.5
+    beta = torch.randn(d, device=cuda) * 0.1
+    h = ops.layernorm(x, gamma, beta, 1e-5, partials=partials, add_bias=bias)
+    torch.cuda.synchronize()
+    ref_x = x0 + act.float() @ w.float().t() + bias
+    assert (x - ref_x).abs().max().item() <= 2e-3 * ref_x.abs().max().item()
+    ref_h = torch.nn.functional.layer_norm(ref_x, (d,), gamma, beta, 1e-5)
+    assert (h.float() - ref_h).abs().max().item() <= 3e-2
+
+
+@pytest.mark.parametrize("rows,d", [(1, 768), (64, 768), (257, 1024), (33, 1280), (5, 128)])
+def test_layernorm(ops, cuda, rows, d):
+    x = torch.randn(rows, d, device=cuda) * 3 + 0.7
+    gamma = torch.rand(d, device=cuda) + 0.5
+    beta = torch.randn(d, device=cuda)
+    out = ops.layernorm(x, gamma, beta, 1e-5)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.layer_norm(x, (d,), gamma, beta, 1e-5)
+    # bf16 output rounding: 2^-8 relative
+    assert (out.float() - ref).abs().max().item() <= 2 ** -7 * ref.abs().max().item()
+
+
+def test_embed(ops, cuda):
+    vocab, npos, d, n = 1000, 64, 768, 77
+    wte = torch.randn(vocab, d, device=cuda)
+    wpe = torch.randn(npos, d, device=cuda)
+    ids = torch.randint(0, vocab, (n,), dtype=torch.int32, device=cuda)
+    pos = torch.randint(0, npos, (n,), dtype=torch.int32, device=cuda)
+    x = ops.embed(wte, wpe, ids, pos)
+    torch.cuda.synchronize()
+    assert torch.equal(x, wte[ids.long()] + wpe[pos.long()])
+
+
+def test_convert_transpose(ops, cuda):
+    src = torch.randn(768, 2304, device=cuda)
+    dst = ops.convert_transpose(src)
+    torch.cuda.synchronize()
+    assert torch.equal(dst, src.t().contiguous().to(torch.bfloat16))
+
+
+def test_argmax_ties_and_tail(ops, cuda):
+    logits = torch.randn(9, 50257, device=cuda)
+    logits[0, 50256] = 100.0          # last element
+    logits[1, 0] = 100.0              # first element
+    logits[2, 77] = 50.0
+    logits[2, 99] = 50.0              # tie -> lowest index
+    out = ops.argmax(logits)
+    torch.cuda.synchronize()
+    ref = logits.argmax(-1).int()
+    assert out[0] == 50256 and out[1] == 0 and out[2] == 77
+    assert torch.equal(out[3:], ref[3:])
+
+
+def _ref_attention(q, k, v):
+    # q [T, H, 64], k/v [S, H, 64], causal with q occupying the last T positions of S
+    T, S = q.shape[0], k.shape[0]
+    s = torch.einsum("thd,shd->hts", q.float(), k.float()) / 8.0
+    mask = torch.ones(T, S, dtype=torch.bool, device=q.device).tril(S - T)
+    s = s.masked_fill(~mask, float("-inf"))
+    p = torch.softmax(s, dim=-1)
+    return torch.einsum("hts,shd->thd", p, v.float())
+
+
+@pytest.mark.parametrize("lens,n_head", [
+    ([128] * 4, 12),            # BASELINE config 2 shape (subset of batch)
+    ([1, 5, 64, 65, 200], 12),  # ragged, tile boundaries
+    ([1024], 16),               # long prompt (config 3)
+    ([37, 300], 20),
+])
+def test_prefill_attention(ops, cuda, lens, n_head):
+    d = n_head * 64
+    n_tok = sum(lens)
+    qkv = (torch.randn(n_tok, 3 * d, device=cuda) * 0.8).to(torch.bfloat16)
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32, device=cuda)
+    out = ops.prefill_attention(qkv, cu, max(lens), n_head)
+    torch.cuda.synchronize()
+    start = 0
+    for L in lens:
+        blk = qkv[start:start + L].view(L, 3, n_head, 64)
+        ref = _ref_attention(blk[:, 0], blk[:, 1], blk[:, 2]).reshape(L, d)
+        got = out[start:start + L].float()
+        assert (got - ref).abs().max().item() <= 2e-2, (L, (got - ref).abs().max().item())
+        start += L
+
+
+@pytest.mark.parametrize("ctx_lens,n_head,n_splits", [
+    ([0, 1, 15, 16, 17, 159, 160], 12, 1),
+    ([127] * 8, 12, 1),
+    ([1100, 3, 64, 700], 16, 4),
+    ([1100, 3, 64, 700], 16, 16),
+    ([300, 299], 20, 2),
+])
+def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits):
+    """seq_len[b] tokens are cached; the new token (position seq_len[b]) is appended by the
+    kernel, then attends over everything including itself."""
+    d = n_head * 64
+    B = len(ctx_lens)
+    page = 16
+    max_pages = (max(ctx_lens) + 1 + page - 1) // page
+    n_pages = B * max_pages + 3
+    g = torch.Generator(device="cpu").manual_seed(5)
+    perm = torch.randperm(n_pages, generator=g)[: B * max_pages].int()
+    page_table = perm.view(B, max_pages).contiguous().to(cuda)  # scattered physical pages
+    k_pool = torch.zeros(n_pages, n_head, page, 64, dtype=torch.bfloat16, device=cuda)
+    v_pool = torch.zeros_like(k_pool)
+    ks, vs = [], []
+    for b, L in enumerate(ctx_lens):
+        k = (torch.randn(L, n_head, 64, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+        v = (torch.randn(L, n_head, 64, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+        ks.append(k)
+        vs.append(v)
+        for t in range(L):
+            p = page_table[b, t // page].item()
+            k_pool[p, :, t % page] = k[t]
+            v_pool[p, :, t % page] = v[t]
+    qkv = (torch.randn(B, 3 * d, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+    seq_len = torch.tensor(ctx_lens, dtype=torch.int32, device=cuda)
+    out = ops.decode_attention(qkv, seq_len, page_table, k_pool, v_pool, n_head, n_splits)
+    torch.cuda.synchronize()
+    for b, L in enumerate(ctx_lens):
+        cur = qkv[b].view(3, n_head, 64)
+        k_all = torch.cat([ks[b], cur[1][None]], 0)
+        v_all = torch.cat([vs[b], cur[2][None]], 0)
+        ref = _ref_attention(cur[0][None], k_all, v_all).reshape(d)
+        got = out[b].float()
+        assert (got - ref).abs().max().item() <= 2e-2, (b, L)
+        # the new token's K/V landed in its page
+        p = page_table[b, L // page].item()
+        assert torch.equal(k_pool[p, :, L % page], cur[1])
+        assert torch.equal(v_pool[p, :, L % page], cur[2])
