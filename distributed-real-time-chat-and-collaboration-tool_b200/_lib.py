@@ -43,6 +43,7 @@ class Config(C.Structure):
         ("use_cuda_graphs", C.c_int32),
         ("use_pdl", C.c_int32),
         ("decode_split_k", C.c_int32),
+        ("keep_logits", C.c_int32),
     ]
 
 

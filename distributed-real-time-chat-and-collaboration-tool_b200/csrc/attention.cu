@@ -258,6 +258,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(DecodeAttnArgs a) {
   const int d = a.n_head * kHeadDim;
 
   pdl_wait();
+  pdl_launch_dependents();
   const int slot = a.active_slots ? a.active_slots[b] : b;
   if (slot < 0) return;
   const int pos = a.seq_len[slot];
@@ -380,7 +381,6 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(DecodeAttnArgs a) {
       }
     }
   }
-  pdl_launch_dependents();
 }
 
 __global__ void __launch_bounds__(64) decode_combine_kernel(DecodeAttnArgs a) {
@@ -389,6 +389,7 @@ __global__ void __launch_bounds__(64) decode_combine_kernel(DecodeAttnArgs a) {
   const int h = bh % a.n_head;
   const int dim = threadIdx.x;
   pdl_wait();
+  pdl_launch_dependents();
   const int slot = a.active_slots ? a.active_slots[b] : b;
   if (slot < 0) return;
   const float* sc = a.scratch + static_cast<size_t>(bh) * a.n_splits * kScratchStride;
@@ -403,7 +404,6 @@ __global__ void __launch_bounds__(64) decode_combine_kernel(DecodeAttnArgs a) {
   }
   const int d = a.n_head * kHeadDim;
   a.out[static_cast<size_t>(b) * d + h * kHeadDim + dim] = __float2bfloat16(o / l);
-  pdl_launch_dependents();
 }
 
 int launch_with_pdl(void (*kernel)(DecodeAttnArgs), dim3 grid, dim3 block, cudaStream_t stream,

@@ -153,6 +153,11 @@ struct b200llm_engine {
   __nv_bfloat16 *h = nullptr, *qkv = nullptr, *attn = nullptr, *ffn = nullptr;
   float* logits = nullptr;
   int logits_rows = 0;
+  float* amax_val = nullptr;   // [n_groups, logits_rows] LM-head argmax candidates
+  int32_t* amax_idx = nullptr;
+  float* eos_logit = nullptr;  // [logits_rows]
+  int n_groups = 0;
+  std::vector<char> slot_samples;  // host: slot uses temperature/top-k sampling
   float* partials = nullptr;
   size_t partials_floats = 0;
   float* attn_scratch = nullptr;
@@ -168,9 +173,11 @@ struct b200llm_engine {
 
   // decode graphs
   struct GraphKey {
-    int bucket, splits;
+    int bucket, splits, logits;
     bool operator<(const GraphKey& o) const {
-      return bucket != o.bucket ? bucket < o.bucket : splits < o.splits;
+      if (bucket != o.bucket) return bucket < o.bucket;
+      if (splits != o.splits) return splits < o.splits;
+      return logits < o.logits;
     }
   };
   struct GraphEntry {
@@ -233,6 +240,7 @@ struct StepPlan {
   int batch = 0;       // sequences (prefill) / bucket rows (decode)
   int max_len = 0;     // prefill: longest prompt
   float* logits_all = nullptr;
+  bool store_logits = true;  // materialise last-position logits (sampling rows / parity reads)
 };
 
 int count(b200llm_engine* e, int rc) {
@@ -362,12 +370,39 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
   const int head_rows = p.decode ? rows : p.batch;
   B200_PROPAGATE(ln(e, pending_partials, pending_n, rows, pending_bias, e->lnf_g, e->lnf_b,
                     p.decode ? nullptr : e->last_rows, head_rows, pdl));
-  B200_PROPAGATE(gemm(e, e->h, e->wte_bf16, nullptr, e->logits, head_rows, e->V, d, e->V, kEpiF32, 1, pdl));
+  {
+    // LM head with the greedy argmax fused into the epilogue; logits stored only on request
+    GemmArgs g = {};
+    g.act = e->h;
+    g.w = e->wte_bf16;
+    g.bias = nullptr;
+    g.out = p.store_logits ? e->logits : nullptr;
+    g.tokens = head_rows;
+    g.features = e->V;
+    g.k = d;
+    g.ld_out = e->V;
+    g.epilogue = kEpiLogitsArgmax;
+    g.split_k = 1;
+    g.act_rows_alloc = e->max_rows;
+    g.force_orientation = 1;
+    g.pdl = pdl;
+    g.amax_val = e->amax_val;
+    g.amax_idx = e->amax_idx;
+    g.eos_logit = e->eos_logit;
+    g.ld_amax = e->logits_rows;
+    g.eos_id = e->cfg.eos_token_id;
+    B200_PROPAGATE(count(e, gemm_bf16(g, e->stream)));
+  }
 
   SelectArgs s = {};
-  s.logits = e->logits;
+  s.logits = p.store_logits ? e->logits : nullptr;
   s.ld = e->V;
   s.vocab = e->V;
+  s.amax_val = e->amax_val;
+  s.amax_idx = e->amax_idx;
+  s.eos_logit = e->eos_logit;
+  s.n_groups = e->n_groups;
+  s.ld_amax = e->logits_rows;
   s.active_slots = p.decode ? e->active_dev : e->slots_dev;
   s.batch = head_rows;
   s.last_tok = e->last_tok;
@@ -573,6 +608,11 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   E_CUDA(cudaMemsetAsync(e->x, 0, R * d * sizeof(float), st));
   e->logits_rows = dec_rows;
   E_TRY(dev_alloc_t(e.get(), &e->logits, static_cast<size_t>(e->logits_rows) * V));
+  e->n_groups = ((V + 127) / 128) * 4;
+  E_TRY(dev_alloc_t(e.get(), &e->amax_val, static_cast<size_t>(e->n_groups) * e->logits_rows));
+  E_TRY(dev_alloc_t(e.get(), &e->amax_idx, static_cast<size_t>(e->n_groups) * e->logits_rows));
+  E_TRY(dev_alloc_t(e.get(), &e->eos_logit, static_cast<size_t>(e->logits_rows)));
+  e->slot_samples.assign(cfg->max_seqs, 0);
   // split-K planes: at most 32 splits of [decode rows, d]
   e->partials_floats = static_cast<size_t>(32) * dec_rows * d;
   E_TRY(dev_alloc_t(e.get(), &e->partials, e->partials_floats));
@@ -738,6 +778,7 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
     si.seed = sampling ? sampling[b].seed : 0;
     si.pad = 0;
     e->slot_len_host[slots[b]] = cu[b + 1] - cu[b];
+    e->slot_samples[slots[b]] = (si.temperature > 0.0f && si.top_k > 1) ? 1 : 0;
   }
   B200_CUDA_OK(cudaMemcpyAsync(e->init_dev, e->pin_init, batch * sizeof(SlotInit),
                                cudaMemcpyHostToDevice, st));
@@ -759,6 +800,7 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   p.batch = batch;
   p.max_len = max_len;
   p.logits_all = logits_all_dev;
+  p.store_logits = true;
   p.pdl = 0;
   B200_PROPAGATE(run_stack(e, p));
   e->last_batch = batch;
@@ -775,10 +817,12 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   B200_CHECK_ARG(bucket <= e->logits_rows, "decode: batch exceeds workspace");
 
   int max_ctx = 1;
+  bool need_logits = e->cfg.keep_logits != 0;
   for (int b = 0; b < batch; ++b) {
     const int s = slots[b];
     B200_CHECK_ARG(s >= 0 && s < e->cfg.max_seqs && e->slot_used[s], "decode: slot not allocated");
     max_ctx = std::max(max_ctx, e->slot_len_host[s] + n_steps);
+    need_logits = need_logits || e->slot_samples[s] != 0;
   }
 
   // upload the active set when it changed
@@ -798,6 +842,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   p.decode = true;
   p.batch = bucket;
   p.pdl = e->cfg.use_pdl ? 1 : 0;
+  p.store_logits = need_logits;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.device);
   const int cap = e->cfg.decode_split_k == 0 ? 32 : std::min(e->cfg.decode_split_k, 32);
@@ -816,7 +861,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   if (!e->cfg.use_cuda_graphs) {
     for (int i = 0; i < n_steps; ++i) B200_PROPAGATE(decode_step_launches(e, p));
   } else {
-    b200llm_engine::GraphKey key{bucket, p.attn_splits};
+    b200llm_engine::GraphKey key{bucket, p.attn_splits, need_logits ? 1 : 0};
     auto it = e->graphs.find(key);
     if (it == e->graphs.end()) {
       cudaGraph_t graph = nullptr;

@@ -58,6 +58,11 @@ struct KernelArgs {
   int k_blocks_per_split;
   int ld_out;
   int tokens;  // logical token count (partials stride)
+  float* amax_val;
+  int32_t* amax_idx;
+  float* eos_logit;
+  int ld_amax;
+  int eos_id;
 };
 
 template <int N>
@@ -134,6 +139,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Let the next kernel of the step start its own prologue / weight prefetch now; it still
+  // waits (griddepcontrol.wait) for this grid to finish before touching activations.
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ================= TMA producer =================
@@ -235,7 +243,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       const bool a_ok = a_row < args.a_rows;
 
       float bias_lane = 0.0f;
-      if (TRANS && EPI != kEpiF32 && EPI != kEpiPartialF32 && a_ok && args.bias != nullptr) {
+      if (TRANS && EPI != kEpiF32 && EPI != kEpiPartialF32 && EPI != kEpiLogitsArgmax && a_ok &&
+          args.bias != nullptr) {
         bias_lane = args.bias[a_row];
       }
 
@@ -248,7 +257,50 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         tmem_ld_wait();
         const int b_row0 = n_blk * BLOCK_N + c0;  // first row of the N operand in this chunk
 
-        if (TRANS) {
+        if (TRANS && EPI == kEpiLogitsArgmax) {
+          // LM head with the greedy selection fused in: lane = vocabulary entry, column =
+          // token. Each warp reduces its 32 entries to one (max, argmax) candidate per token
+          // with shuffles (ties -> lowest index); lane j keeps the candidate of column j so
+          // the 32 results leave as one coalesced store. EOS is excluded from the candidates
+          // and reported separately so the selector can apply min_new_tokens exactly.
+          const int feature = a_row;
+          float keep_v = -INFINITY;
+          int keep_i = 0x7fffffff;
+#pragma unroll
+          for (int j = 0; j < kChunk; ++j) {
+            const int token = b_row0 + j;
+            float v = a_ok ? __uint_as_float(r[j]) : -INFINITY;
+            int idx = feature;
+            if (a_ok && token < args.b_rows) {
+              if (args.out != nullptr) {
+                reinterpret_cast<float*>(args.out)[static_cast<size_t>(token) * args.ld_out + feature] = v;
+              }
+              if (feature == args.eos_id) {
+                args.eos_logit[token] = v;
+                v = -INFINITY;
+              }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+              const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+              const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+              if (ov > v || (ov == v && oi < idx)) {
+                v = ov;
+                idx = oi;
+              }
+            }
+            if (lane == j) {
+              keep_v = v;
+              keep_i = idx;
+            }
+          }
+          const int token = b_row0 + lane;
+          if (lane < kChunk && token < args.b_rows) {
+            const size_t pidx = static_cast<size_t>(m_blk * 4 + q) * args.ld_amax + token;
+            args.amax_val[pidx] = keep_v;
+            args.amax_idx[pidx] = keep_i;
+          }
+        } else if (TRANS) {
           // lane = feature (a_row), columns = tokens. For each token the warp's 32 lanes
           // write 32 consecutive features -> coalesced.
           const int feature = a_row;
@@ -367,7 +419,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     }
   }
 
-  pdl_launch_dependents();
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -476,6 +527,11 @@ int launch(const GemmArgs& g, cudaStream_t stream) {
   ka.k_blocks_per_split = (ka.k_blocks_total + split - 1) / split;
   ka.ld_out = g.ld_out;
   ka.tokens = g.tokens;
+  ka.amax_val = g.amax_val;
+  ka.amax_idx = g.amax_idx;
+  ka.eos_logit = g.eos_logit;
+  ka.ld_amax = g.ld_amax;
+  ka.eos_id = g.eos_id;
 
   const int num_tiles = ((a_rows + kBlockM - 1) / kBlockM) * ((b_rows + BLOCK_N - 1) / BLOCK_N);
   int grid_x = num_tiles < num_sms() ? num_tiles : num_sms();
@@ -519,6 +575,12 @@ int dispatch_epi(const GemmArgs& g, cudaStream_t stream) {
       return launch<BLOCK_N, kEpiF32, TRANS>(g, stream);
     case kEpiPartialF32:
       return launch<BLOCK_N, kEpiPartialF32, TRANS>(g, stream);
+    case kEpiLogitsArgmax:
+      if constexpr (TRANS) {
+        return launch<BLOCK_N, kEpiLogitsArgmax, true>(g, stream);
+      } else {
+        return fail(kErrUnsupported, "gemm: the fused-argmax epilogue needs the swap-AB orientation");
+      }
     default:
       return fail(kErrInvalidArg, "unknown GEMM epilogue");
   }
@@ -532,7 +594,9 @@ void gemm_clear_tensor_map_cache() {
 }
 
 int gemm_bf16(const GemmArgs& g, cudaStream_t stream) {
-  B200_CHECK_ARG(g.act && g.w && g.out, "gemm: null operand");
+  B200_CHECK_ARG(g.act && g.w && (g.out || g.epilogue == kEpiLogitsArgmax), "gemm: null operand");
+  B200_CHECK_ARG(g.epilogue != kEpiLogitsArgmax || (g.amax_val && g.amax_idx && g.eos_logit),
+                 "gemm: fused-argmax epilogue needs its output arrays");
   B200_CHECK_ARG(g.tokens > 0 && g.features > 0 && g.k > 0, "gemm: empty problem");
   B200_CHECK_ARG(g.k % kBlockK == 0, "gemm: k must be a multiple of 64");
   B200_CHECK_ARG(g.split_k <= 1 || g.epilogue == kEpiPartialF32,

@@ -16,6 +16,9 @@ enum GemmEpilogue : int {
   kEpiBiasResidF32 = 2,  // out_f32 += acc + bias[feature]   (in-place residual stream)
   kEpiF32 = 3,           // out_f32 = acc                    (LM-head logits, no bias)
   kEpiPartialF32 = 4,    // split-K partial: out_f32[split][token, feature] = acc
+  kEpiLogitsArgmax = 5,  // LM head, swap-AB only: per-(32-feature group, token) running argmax
+                         // written to amax_val/amax_idx (EOS excluded, its logit goes to
+                         // eos_logit); fp32 logits also stored when out != null
 };
 
 struct GemmArgs {
@@ -32,6 +35,12 @@ struct GemmArgs {
   int act_rows_alloc;  // rows backing `act` (>= tokens) for the tensor map
   int force_orientation;  // -1 auto, 0 tokens-on-M, 1 weights-on-M (swap-AB)
   int pdl;                // launch with programmatic stream serialization
+  // kEpiLogitsArgmax only: [ceil(features/128)*4, ld_amax] group maxima / indices, [tokens] EOS
+  float* amax_val;
+  int32_t* amax_idx;
+  float* eos_logit;
+  int ld_amax;
+  int eos_id;
 };
 
 // Enqueue one GEMM on `stream`. Returns 0 or an error code (see common.cuh Status).

@@ -19,6 +19,7 @@ __global__ void embed_kernel(const float* __restrict__ wte, const float* __restr
                              const int32_t* __restrict__ seq_len, float* __restrict__ x,
                              int n_rows, int d, int vocab, int n_positions) {
   pdl_wait();
+  pdl_launch_dependents();
   const int row = blockIdx.x;
   if (row >= n_rows) return;
   int tok, p;
@@ -46,78 +47,86 @@ __global__ void embed_kernel(const float* __restrict__ wte, const float* __restr
     const float4 b = __ldg(q + i);
     o[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
   }
-  pdl_launch_dependents();
 }
 
 // ---------------------------------------------------------------------------------------
 // LayerNorm (+ residual / split-K reduction)
 // ---------------------------------------------------------------------------------------
-template <int VEC>  // float4 per lane; d = VEC * 128
-__global__ void __launch_bounds__(128)
+// One CTA per row, one float4 column per thread (d/4 threads). With split-K partials every
+// thread has `n_partials` independent 16-byte loads in flight, so the reduction is bound by
+// L2 bandwidth instead of one warp's load latency; the fixed summation order keeps it
+// deterministic.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  __syncthreads();  // protect `red` from the previous use
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = (lane < nwarps) ? red[lane] : 0.f;
+  return warp_sum(t);
+}
+
+__global__ void __launch_bounds__(512)
 layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int n_partials,
                  const float* __restrict__ add_bias, const float* __restrict__ gamma,
                  const float* __restrict__ beta, const int32_t* __restrict__ row_index,
-                 __nv_bfloat16* __restrict__ out, int rows, int rows_total, float eps) {
-  constexpr int D = VEC * 128;
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  const int orow = blockIdx.x * 4 + warp;
+                 __nv_bfloat16* __restrict__ out, int d, int rows_total, float eps) {
+  __shared__ float red[32];
+  const int orow = blockIdx.x;
+  const int c = threadIdx.x;  // float4 column
+  const int ncol = d >> 2;
+  const bool active = c < ncol;
+  // parameters do not depend on the upstream kernel: fetch them before the dependency wait
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f), b = g, ab = g;
+  if (active) {
+    g = __ldg(reinterpret_cast<const float4*>(gamma) + c);
+    b = __ldg(reinterpret_cast<const float4*>(beta) + c);
+    if (n_partials > 0 && add_bias != nullptr) ab = __ldg(reinterpret_cast<const float4*>(add_bias) + c);
+  }
   pdl_wait();
-  if (orow >= rows) return;
+  pdl_launch_dependents();
   const int irow = row_index ? row_index[orow] : orow;
-
-  float4 v[VEC];
-  float4* xr = reinterpret_cast<float4*>(x + static_cast<size_t>(irow) * D);
-#pragma unroll
-  for (int i = 0; i < VEC; ++i) v[i] = xr[lane + 32 * i];
-
-  if (n_partials > 0) {
-    // x += bias + sum_s partial[s]  -- fixed summation order => deterministic
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) {
-      float4 acc = add_bias ? __ldg(reinterpret_cast<const float4*>(add_bias) + lane + 32 * i)
-                            : make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int s = 0; s < n_partials; ++s) {
-        const float4 p = *(reinterpret_cast<const float4*>(
-                               partials + (static_cast<size_t>(s) * rows_total + irow) * D) +
-                           lane + 32 * i);
-        acc.x += p.x;
-        acc.y += p.y;
-        acc.z += p.z;
-        acc.w += p.w;
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4* xr = reinterpret_cast<float4*>(x + static_cast<size_t>(irow) * d);
+  if (active) {
+    v = xr[c];
+    if (n_partials > 0) {
+      float4 acc = ab;
+      const float4* p = reinterpret_cast<const float4*>(partials + static_cast<size_t>(irow) * d) + c;
+      const size_t plane = static_cast<size_t>(rows_total) * d / 4;
+      int s = 0;
+      for (; s + 4 <= n_partials; s += 4) {
+        const float4 p0 = p[(s + 0) * plane], p1 = p[(s + 1) * plane], p2 = p[(s + 2) * plane],
+                     p3 = p[(s + 3) * plane];
+        acc.x += p0.x; acc.y += p0.y; acc.z += p0.z; acc.w += p0.w;
+        acc.x += p1.x; acc.y += p1.y; acc.z += p1.z; acc.w += p1.w;
+        acc.x += p2.x; acc.y += p2.y; acc.z += p2.z; acc.w += p2.w;
+        acc.x += p3.x; acc.y += p3.y; acc.z += p3.z; acc.w += p3.w;
       }
-      v[i].x += acc.x;
-      v[i].y += acc.y;
-      v[i].z += acc.z;
-      v[i].w += acc.w;
-      xr[lane + 32 * i] = v[i];
+      for (; s < n_partials; ++s) {
+        const float4 p0 = p[s * plane];
+        acc.x += p0.x; acc.y += p0.y; acc.z += p0.z; acc.w += p0.w;
+      }
+      v.x += acc.x; v.y += acc.y; v.z += acc.z; v.w += acc.w;
+      xr[c] = v;
     }
   }
-
-  float sum = 0.f;
-#pragma unroll
-  for (int i = 0; i < VEC; ++i) sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
-  const float mean = warp_sum(sum) * (1.0f / D);
+  const float inv_d = 1.0f / static_cast<float>(d);
+  const float mean = block_sum((v.x + v.y) + (v.z + v.w), red) * inv_d;
   float sq = 0.f;
-#pragma unroll
-  for (int i = 0; i < VEC; ++i) {
-    const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, e = v[i].w - mean;
-    sq += (a * a + b * b) + (c * c + e * e);
+  if (active) {
+    const float a0 = v.x - mean, a1 = v.y - mean, a2 = v.z - mean, a3 = v.w - mean;
+    sq = (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
   }
-  const float var = warp_sum(sq) * (1.0f / D);
+  const float var = block_sum(sq, red) * inv_d;
   const float rstd = 1.0f / sqrtf(var + eps);
-
-  uint2* orow_ptr = reinterpret_cast<uint2*>(out + static_cast<size_t>(orow) * D);
-#pragma unroll
-  for (int i = 0; i < VEC; ++i) {
-    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
-    const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + lane + 32 * i);
+  if (active) {
     uint2 pk;
-    pk.x = pack_bf16x2((v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y);
-    pk.y = pack_bf16x2((v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w);
-    orow_ptr[lane + 32 * i] = pk;
+    pk.x = pack_bf16x2((v.x - mean) * rstd * g.x + b.x, (v.y - mean) * rstd * g.y + b.y);
+    pk.y = pack_bf16x2((v.z - mean) * rstd * g.z + b.z, (v.w - mean) * rstd * g.w + b.w);
+    reinterpret_cast<uint2*>(out + static_cast<size_t>(orow) * d)[c] = pk;
   }
-  pdl_launch_dependents();
 }
 
 // ---------------------------------------------------------------------------------------
@@ -180,6 +189,7 @@ __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
   __shared__ float top_v[kMaxTopK];
   __shared__ int top_i[kMaxTopK];
   pdl_wait();
+  pdl_launch_dependents();
   const int row = blockIdx.x;
   const int slot = a.active_slots ? a.active_slots[row] : row;
   if (slot < 0) return;
@@ -197,14 +207,31 @@ __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
     MaxIdx m;
     m.v = -INFINITY;
     m.i = 0x7fffffff;
-    for (int i = threadIdx.x; i < a.vocab; i += blockDim.x) {
-      if (ban_eos && i == a.eos_id) continue;
-      MaxIdx c;
-      c.v = lg[i];
-      c.i = i;
-      m = better(m, c);
+    if (a.amax_val != nullptr) {
+      // reduce the per-group candidates the LM-head epilogue produced (EOS handled apart)
+      for (int i = threadIdx.x; i < a.n_groups; i += blockDim.x) {
+        MaxIdx c;
+        c.v = a.amax_val[static_cast<size_t>(i) * a.ld_amax + row];
+        c.i = a.amax_idx[static_cast<size_t>(i) * a.ld_amax + row];
+        m = better(m, c);
+      }
+      m = block_argmax(m, red);
+      if (!ban_eos) {
+        MaxIdx e;
+        e.v = a.eos_logit[row];
+        e.i = a.eos_id;
+        m = better(m, e);
+      }
+    } else {
+      for (int i = threadIdx.x; i < a.vocab; i += blockDim.x) {
+        if (ban_eos && i == a.eos_id) continue;
+        MaxIdx c;
+        c.v = lg[i];
+        c.i = i;
+        m = better(m, c);
+      }
+      m = block_argmax(m, red);
     }
-    m = block_argmax(m, red);
     chosen = m.i;
   } else {
     // top-k by k successive block-wide argmax passes over the (L2-resident) logits row,
@@ -382,29 +409,13 @@ int embed_decode(const float* wte, const float* wpe, const int32_t* active_slots
 }
 
 int layernorm(const LayerNormArgs& a, cudaStream_t stream) {
-  B200_CHECK_ARG(a.rows > 0 && a.d % 128 == 0, "layernorm: d must be a multiple of 128");
-  const dim3 grid((a.rows + 3) / 4), block(128);
-  // rows_total (stride between split-K partial planes) is the number of input rows.
+  B200_CHECK_ARG(a.rows > 0 && a.d % 4 == 0 && a.d / 4 <= 512,
+                 "layernorm: d must be a multiple of 4 and at most 2048");
+  const int threads = ((a.d / 4 + 31) / 32) * 32;
   const int rows_total = a.partial_rows > 0 ? a.partial_rows : a.rows;
-#define B200_LN_CASE(V)                                                                        \
-  case V:                                                                                      \
-    return launch_pdl(layernorm_kernel<V>, grid, block, stream, a.pdl, a.x, a.partials,        \
-                      a.n_partials, a.add_bias, a.gamma, a.beta, a.row_index, a.out, a.rows,   \
-                      rows_total, a.eps);
-  switch (a.d / 128) {
-    B200_LN_CASE(1)
-    B200_LN_CASE(2)
-    B200_LN_CASE(3)
-    B200_LN_CASE(4)
-    B200_LN_CASE(6)
-    B200_LN_CASE(8)
-    B200_LN_CASE(10)
-    B200_LN_CASE(12)
-    B200_LN_CASE(16)
-    default:
-      return fail(kErrUnsupported, "layernorm: unsupported hidden size");
-  }
-#undef B200_LN_CASE
+  return launch_pdl(layernorm_kernel, dim3(a.rows), dim3(threads), stream, a.pdl, a.x, a.partials,
+                    a.n_partials, a.add_bias, a.gamma, a.beta, a.row_index, a.out, a.d, rows_total,
+                    a.eps);
 }
 
 int select_tokens(const SelectArgs& a, cudaStream_t stream) {

@@ -42,9 +42,16 @@ struct LayerNormArgs {
 int layernorm(const LayerNormArgs& a, cudaStream_t stream);
 
 struct SelectArgs {
-  const float* logits;           // [batch, ld] fp32
+  const float* logits;           // [batch, ld] fp32 (may be null when every row is greedy and
+                                 // the LM-head GEMM supplied group candidates)
   int ld;
   int vocab;
+  // candidates from the LM-head GEMM's fused argmax (gemm_tcgen05.cuh kEpiLogitsArgmax)
+  const float* amax_val;         // [n_groups, ld_amax] or null
+  const int32_t* amax_idx;
+  const float* eos_logit;        // [batch]
+  int n_groups;
+  int ld_amax;
   const int32_t* active_slots;   // [batch] slot per row (-1 = padding row)
   int batch;
   // per-slot generation state

@@ -53,7 +53,8 @@ class Engine:
     def __init__(self, shape: ModelShape, weights_blob: np.ndarray, *, device: int = 0,
                  max_seqs: int = 64, max_seq_len: int = 256, max_batch_tokens: int = 8192,
                  max_new_tokens: int = 256, kv_pool_tokens: int = 0, use_cuda_graphs: bool = True,
-                 use_pdl: bool = True, decode_split_k: int = 0, pad_token_id: int | None = None):
+                 use_pdl: bool = True, decode_split_k: int = 0, keep_logits: bool = False,
+                 pad_token_id: int | None = None):
         blob = np.ascontiguousarray(weights_blob, dtype=np.float32).reshape(-1)
         self.shape = shape
         self.cfg = Config(
@@ -63,7 +64,8 @@ class Engine:
             pad_token_id=shape.eos_token_id if pad_token_id is None else pad_token_id,
             max_seqs=max_seqs, max_seq_len=max_seq_len, max_batch_tokens=max_batch_tokens,
             max_new_tokens=max_new_tokens, kv_pool_tokens=kv_pool_tokens, device=device,
-            use_cuda_graphs=int(use_cuda_graphs), use_pdl=int(use_pdl), decode_split_k=decode_split_k)
+            use_cuda_graphs=int(use_cuda_graphs), use_pdl=int(use_pdl), decode_split_k=decode_split_k,
+            keep_logits=int(keep_logits))
         expect = lib.b200llm_weight_blob_floats(C.byref(self.cfg))
         if blob.size != expect:
             raise ValueError(f"weight blob has {blob.size} floats, config needs {expect}")

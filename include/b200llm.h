@@ -70,6 +70,8 @@ typedef struct b200llm_config {
   int32_t use_cuda_graphs;  /* 1 = replay the decode step from a captured CUDA graph       */
   int32_t use_pdl;          /* 1 = programmatic dependent launch between step kernels      */
   int32_t decode_split_k;   /* 0 = auto; 1 = off; >1 = split-K factor cap for decode GEMMs */
+  int32_t keep_logits;      /* 1 = decode steps also store the fp32 logits (greedy rows do not
+                               need them: the LM-head GEMM fuses the argmax)                 */
 } b200llm_config;
 
 /* Number of fp32 values in the weight blob for `cfg` (layout below). */

@@ -118,7 +118,7 @@ def test_prefill_then_decode_equals_one_shot_prefill(cuda, small_weights):
     T = 40
     ids = O.synthetic_prompts(3, T, seed=5)
     eng, E = _engine(O.SMALL, small_weights, max_seqs=8, max_seq_len=64, max_batch_tokens=256,
-                     max_new_tokens=4, use_cuda_graphs=False)
+                     max_new_tokens=4, use_cuda_graphs=False, keep_logits=True)
     slots = [eng.seq_alloc(64) for _ in range(3)]
     eng.prefill(ids.tolist(), slots)
     first = [eng.read_tokens(s)[0][0] for s in slots]
