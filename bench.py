@@ -36,6 +36,7 @@ WORKLOADS = {
     "summarize_medium": ("medium", 16, 1024, 128),    # configs[2] (n_positions 2048)
     "ask_large_b32": ("large", 32, 64, 256),          # configs[3] per-GPU shard (256 / 8 GPUs)
     "ask_large_b256": ("large", 256, 64, 256),        # configs[3] on one GPU
+    "probe_short_ctx": ("small", 64, 16, 32),         # profiling probe: negligible KV traffic
 }
 
 

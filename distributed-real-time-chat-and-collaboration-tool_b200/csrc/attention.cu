@@ -16,6 +16,19 @@
 #include "common.cuh"
 #include "ops.cuh"
 
+#ifdef B200_ATTN_TRACE
+// Profiling build only (profiles/attn_trace.cu): CTA 0 records SM-clock milestones.
+__device__ unsigned long long g_attn_trace[16];
+#define B200_ATRACE(slot)                                                                  \
+  do {                                                                                     \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_attn_trace[slot] = clock64(); \
+  } while (0)
+#else
+#define B200_ATRACE(slot) \
+  do {                    \
+  } while (0)
+#endif
+
 namespace b200llm {
 
 namespace {
@@ -240,12 +253,21 @@ __device__ __forceinline__ void bf16x8_to_float(const uint4& v, float (&f)[8]) {
   f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
 }
 
-constexpr int kDecUnroll = 4;
+constexpr int kDecUnroll = 3;
 constexpr int kScratchStride = kHeadDim + 2;  // o[64], m, l
+constexpr int kMaxSmemPages = 256;            // page ids staged in smem (4096 tokens)
 
-__global__ void __launch_bounds__(128) decode_attn_kernel(DecodeAttnArgs a) {
+struct KvBatch {
+  uint4 k[kDecUnroll];
+  uint4 v[kDecUnroll];
+};
+
+__global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   __shared__ float sm_o[4][kHeadDim];
   __shared__ float sm_ml[4][2];
+  __shared__ int32_t sm_pages[kMaxSmemPages];
+  __shared__ __align__(16) float sm_q[kHeadDim];          // this token's q (pre-scaled)
+  __shared__ __align__(16) __nv_bfloat16 sm_kv[2][kHeadDim];  // this token's k, v (cache dtype)
 
   const int bh = blockIdx.x;
   const int b = bh / a.n_head;
@@ -256,40 +278,140 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(DecodeAttnArgs a) {
   const int sub = lane & 7;                // which 16-byte chunk (8 dims) of the 128-byte row
   const int grp = warp * 4 + (lane >> 3);  // 0..15: token within the 16-token page
   const int d = a.n_head * kHeadDim;
+  B200_ATRACE(0);
 
+  // ---- before the grid dependency resolves: only data no kernel of a decode step writes ----
+  // (active set and page table are written by the host between steps, never by the step).
+  const int slot = a.active_slots ? a.active_slots[b] : b;
+  const int32_t* pt = a.page_table + static_cast<size_t>(slot < 0 ? 0 : slot) * a.max_pages_per_seq;
+  const int n_stage = a.max_pages_per_seq < kMaxSmemPages ? a.max_pages_per_seq : kMaxSmemPages;
+  if (slot >= 0) {
+    for (int i = threadIdx.x; i < n_stage; i += blockDim.x) sm_pages[i] = pt[i];
+  }
+  // Each thread owns one or two of the 192 values (q|k|v x 64 dims) of this token's projection.
+  float rbias[2] = {0.f, 0.f};
+  if (a.qkv_partials != nullptr) {
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int vi = threadIdx.x + r * 128;
+      if (vi < 3 * kHeadDim) rbias[r] = __ldg(a.qkv_bias + (vi >> 6) * d + h * kHeadDim + (vi & 63));
+    }
+  }
+  __syncthreads();
+
+  // Speculative KV prefetch into L2. seq_len is written by the selector of the PREVIOUS step,
+  // so a read here (before the dependency wait) may be stale -- but a stale value is only ever
+  // smaller, positions below it are cached and immutable for the whole step, and a prefetch
+  // has no architectural effect. This overlaps the layer's KV stream from HBM with the QKV
+  // projection that runs before this kernel; the real loads below then hit L2.
+  if (slot >= 0) {
+    const int pos_spec = *reinterpret_cast<const volatile int32_t*>(a.seq_len + slot);
+    int chunk_s = (pos_spec + a.n_splits - 1) / a.n_splits;
+    chunk_s = ((chunk_s + kPageTokens - 1) / kPageTokens) * kPageTokens;
+    const int tb = split * chunk_s;
+    const int te = min(pos_spec, tb + chunk_s);
+    if (sub < 2) {  // lane 0 of the group prefetches the K row, lane 1 the V row (128 B each)
+      const __nv_bfloat16* pool = sub == 0 ? a.k_pool : a.v_pool;
+      for (int tpos = tb + grp; tpos < te; tpos += kPageTokens) {
+        const int pi = tpos / kPageTokens;
+        const int page = pi < n_stage ? sm_pages[pi] : pt[pi];
+        const size_t off =
+            ((static_cast<size_t>(page) * a.n_head + h) * kPageTokens + tpos % kPageTokens) * kHeadDim;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pool + off));
+      }
+    }
+  }
+
+  B200_ATRACE(1);
   pdl_wait();
   pdl_launch_dependents();
-  const int slot = a.active_slots ? a.active_slots[b] : b;
   if (slot < 0) return;
   const int pos = a.seq_len[slot];
   const int ctx = pos + 1;
+  B200_ATRACE(2);
   const bool fin = a.finished != nullptr && a.finished[slot] != 0;
-
-  const __nv_bfloat16* row = a.qkv + static_cast<size_t>(b) * 3 * d + h * kHeadDim + sub * 8;
-  float q[8];
-  {
-    const uint4 qv = *reinterpret_cast<const uint4*>(row);
-    bf16x8_to_float(qv, q);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) q[i] *= kScaleLog2;
-  }
-  const uint4 k_new = *reinterpret_cast<const uint4*>(row + d);
-  const uint4 v_new = *reinterpret_cast<const uint4*>(row + 2 * d);
-  const int32_t* pt = a.page_table + static_cast<size_t>(slot) * a.max_pages_per_seq;
-
-  if (split == 0 && !fin && warp == 0 && lane < 8) {
-    const int page = pt[pos / kPageTokens];
-    const size_t dst =
-        ((static_cast<size_t>(page) * a.n_head + h) * kPageTokens + pos % kPageTokens) * kHeadDim +
-        sub * 8;
-    *reinterpret_cast<uint4*>(a.k_pool + dst) = k_new;
-    *reinterpret_cast<uint4*>(a.v_pool + dst) = v_new;
-  }
 
   int chunk = (ctx + a.n_splits - 1) / a.n_splits;
   chunk = ((chunk + kPageTokens - 1) / kPageTokens) * kPageTokens;
   const int t_begin = split * chunk;
   const int t_end = min(ctx, t_begin + chunk);
+
+  // Cached K/V of positions < pos never change during this step: request the first batch now,
+  // so the HBM latency overlaps the reduction of this token's own q/k/v below.
+  auto page_of = [&](int tpos) -> int {
+    const int pi = tpos / kPageTokens;
+    return pi < n_stage ? sm_pages[pi] : pt[pi];
+  };
+  auto load_batch = [&](int base, KvBatch& kb) {
+#pragma unroll
+    for (int u = 0; u < kDecUnroll; ++u) {
+      const int tpos = base + u * kPageTokens + grp;
+      kb.k[u] = make_uint4(0u, 0u, 0u, 0u);
+      kb.v[u] = make_uint4(0u, 0u, 0u, 0u);
+      if (tpos < t_end && tpos != pos) {
+        const size_t off =
+            ((static_cast<size_t>(page_of(tpos)) * a.n_head + h) * kPageTokens + tpos % kPageTokens) *
+                kHeadDim + sub * 8;
+        kb.k[u] = ld_nc_v4(a.k_pool + off);
+        kb.v[u] = ld_nc_v4(a.v_pool + off);
+      }
+    }
+  };
+  KvBatch cur;
+  load_batch(t_begin, cur);
+  B200_ATRACE(3);
+
+  // This token's q/k/v. With a split-K projection the CTA reduces the fp32 partial planes
+  // (fixed summation order -> deterministic), adds the bias, keeps q in fp32 and rounds k/v to
+  // the cache dtype; everyone then reads them from shared memory.
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int vi = threadIdx.x + r * 128;
+    if (vi < 3 * kHeadDim) {
+      const int part = vi >> 6, dim = vi & 63;
+      float val;
+      if (a.qkv_partials != nullptr) {
+        const float* src = a.qkv_partials + static_cast<size_t>(b) * 3 * d + part * d + h * kHeadDim + dim;
+        const size_t plane = static_cast<size_t>(a.partial_rows) * 3 * d;
+        val = rbias[r];
+        for (int s0 = 0; s0 < a.n_qkv_partials; s0 += 8) {
+          float x[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            x[j] = (s0 + j < a.n_qkv_partials) ? src[static_cast<size_t>(s0 + j) * plane] : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) val += x[j];
+        }
+      } else {
+        val = __bfloat162float(a.qkv[static_cast<size_t>(b) * 3 * d + part * d + h * kHeadDim + dim]);
+      }
+      if (part == 0) {
+        sm_q[dim] = val * kScaleLog2;
+      } else {
+        sm_kv[part - 1][dim] = __float2bfloat16(val);
+      }
+    }
+  }
+  __syncthreads();
+  B200_ATRACE(4);
+  float q[8];
+  {
+    const float4 q0 = *reinterpret_cast<const float4*>(&sm_q[sub * 8]);
+    const float4 q1 = *reinterpret_cast<const float4*>(&sm_q[sub * 8 + 4]);
+    q[0] = q0.x; q[1] = q0.y; q[2] = q0.z; q[3] = q0.w;
+    q[4] = q1.x; q[5] = q1.y; q[6] = q1.z; q[7] = q1.w;
+  }
+  const uint4 k_new = *reinterpret_cast<const uint4*>(&sm_kv[0][sub * 8]);
+  const uint4 v_new = *reinterpret_cast<const uint4*>(&sm_kv[1][sub * 8]);
+
+  if (split == 0 && !fin && warp == 0 && lane < 8) {
+    const size_t dst =
+        ((static_cast<size_t>(page_of(pos)) * a.n_head + h) * kPageTokens + pos % kPageTokens) * kHeadDim +
+        sub * 8;
+    *reinterpret_cast<uint4*>(a.k_pool + dst) = k_new;
+    *reinterpret_cast<uint4*>(a.v_pool + dst) = v_new;
+  }
 
   Softmax8 acc;
   acc.m = -INFINITY;
@@ -298,36 +420,24 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(DecodeAttnArgs a) {
   for (int i = 0; i < 8; ++i) acc.o[i] = 0.f;
 
   for (int base = t_begin; base < t_end; base += kPageTokens * kDecUnroll) {
-    uint4 kv[kDecUnroll], vv[kDecUnroll];
-    bool valid[kDecUnroll];
+    if (base != t_begin) load_batch(base, cur);  // the first batch is already in flight
 #pragma unroll
     for (int u = 0; u < kDecUnroll; ++u) {
       const int tpos = base + u * kPageTokens + grp;
-      valid[u] = tpos < t_end;
-      kv[u] = k_new;
-      vv[u] = v_new;
-      if (valid[u] && tpos != pos) {
-        const int page = pt[tpos / kPageTokens];
-        const size_t off =
-            ((static_cast<size_t>(page) * a.n_head + h) * kPageTokens + tpos % kPageTokens) *
-                kHeadDim + sub * 8;
-        kv[u] = ld_nc_v4(a.k_pool + off);
-        vv[u] = ld_nc_v4(a.v_pool + off);
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < kDecUnroll; ++u) {
+      const bool valid = tpos < t_end;
+      const uint4 kraw = (tpos == pos) ? k_new : cur.k[u];
+      const uint4 vraw = (tpos == pos) ? v_new : cur.v[u];
       float kf[8];
-      bf16x8_to_float(kv[u], kf);
+      bf16x8_to_float(kraw, kf);
       float s = 0.f;
 #pragma unroll
       for (int i = 0; i < 8; ++i) s = fmaf(q[i], kf[i], s);
       s += __shfl_xor_sync(0xffffffffu, s, 1);
       s += __shfl_xor_sync(0xffffffffu, s, 2);
       s += __shfl_xor_sync(0xffffffffu, s, 4);
-      if (valid[u]) {
+      if (valid) {
         float vf[8];
-        bf16x8_to_float(vv[u], vf);
+        bf16x8_to_float(vraw, vf);
         const float m = fmaxf(acc.m, s);
         const float f = (acc.m == -INFINITY) ? 0.f : exp2f(acc.m - m);
         const float p = exp2f(s - m);
@@ -339,6 +449,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(DecodeAttnArgs a) {
     }
   }
 
+  B200_ATRACE(5);
   // merge the 4 token groups of this warp (lanes differing in bits 3 and 4)
 #pragma unroll
   for (int off = 8; off <= 16; off <<= 1) {
@@ -381,6 +492,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(DecodeAttnArgs a) {
       }
     }
   }
+  B200_ATRACE(6);
 }
 
 __global__ void __launch_bounds__(64) decode_combine_kernel(DecodeAttnArgs a) {

@@ -19,7 +19,12 @@ int prefill_attention(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int b
                       int max_seq_len, int n_head, __nv_bfloat16* out, cudaStream_t stream);
 
 struct DecodeAttnArgs {
-  const __nv_bfloat16* qkv;      // [batch, 3*d] current token (bias already added)
+  const __nv_bfloat16* qkv;      // [batch, 3*d] current token (bias already added), or null when
+                                 // the projection arrives as split-K partial planes:
+  const float* qkv_partials;     // [n_qkv_partials][partial_rows, 3*d] fp32 (no bias)
+  int n_qkv_partials;
+  int partial_rows;
+  const float* qkv_bias;         // [3*d] added while reducing the partials
   const int32_t* active_slots;   // [batch] slot per row (-1 = padding)
   const int32_t* seq_len;        // [n_slots] tokens already cached == position of this token
   const int32_t* finished;       // [n_slots] or null; finished rows do not append

@@ -17,6 +17,7 @@
 //   workspace residual stream x fp32 [rows,d]; h / qkv / attn / ffn bf16; logits fp32
 //             [max_batch_rows, V]; split-K partial planes; split-KV attention scratch.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -190,6 +191,9 @@ struct b200llm_engine {
   int launches_in_capture = 0;
 
   int last_batch = 0;
+  // Profiling aid (env B200LLM_SKIP, bit mask): drop a class of kernels from the decode step to
+  // read its in-graph cost by difference. Results are garbage when set; never set in tests.
+  int skip_mask = 0;
 };
 
 namespace b200llm {
@@ -233,7 +237,9 @@ int pick_split(int features, int k, int sms, int cap) {
 struct StepPlan {
   int rows;           // activation rows fed to the GEMMs
   bool decode;        // decode step (slot-driven) or prefill
-  int split_o = 1;    // split-K of the attention out-proj
+  int split_qkv = 1;  // split-K of c_attn (partials reduced inside decode attention)
+  int split_fc = 1;   // split-K of the MLP up-proj (partials reduced by reduce_bias_gelu)
+  int split_o = 1;    // split-K of the attention out-proj (partials reduced by the next LayerNorm)
   int split_p = 1;    // split-K of the MLP down-proj
   int attn_splits = 1;
   int pdl = 0;
@@ -242,6 +248,8 @@ struct StepPlan {
   float* logits_all = nullptr;
   bool store_logits = true;  // materialise last-position logits (sampling rows / parity reads)
 };
+
+enum SkipBits { kSkipLn = 1, kSkipGemm = 2, kSkipAttn = 4, kSkipHead = 8, kSkipSelect = 16, kSkipGelu = 32 };
 
 int count(b200llm_engine* e, int rc) {
   if (rc == kOk) {
@@ -267,6 +275,7 @@ int gemm(b200llm_engine* e, const __nv_bfloat16* act, const __nv_bfloat16* w, co
   g.act_rows_alloc = e->max_rows;
   g.force_orientation = -1;
   g.pdl = pdl;
+  if (e->skip_mask & kSkipGemm) return kOk;
   return count(e, gemm_bf16(g, e->stream));
 }
 
@@ -287,6 +296,7 @@ int ln(b200llm_engine* e, const float* partials, int n_partials, int partial_row
   a.d = e->d;
   a.eps = e->cfg.ln_eps;
   a.pdl = pdl;
+  if (e->skip_mask & kSkipLn) return kOk;
   return count(e, layernorm(a, e->stream));
 }
 
@@ -310,11 +320,21 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
     pending_partials = nullptr;
     pending_n = 0;
     // c_attn (:185)
-    B200_PROPAGATE(gemm(e, e->h, w.w_qkv, w.b_qkv, e->qkv, rows, 3 * d, d, 3 * d, kEpiBiasBf16, 1, pdl));
+    const bool qkv_split = p.decode && p.split_qkv > 1;
+    if (qkv_split) {
+      B200_PROPAGATE(gemm(e, e->h, w.w_qkv, nullptr, e->partials, rows, 3 * d, d, 3 * d,
+                          kEpiPartialF32, p.split_qkv, pdl));
+    } else {
+      B200_PROPAGATE(gemm(e, e->h, w.w_qkv, w.b_qkv, e->qkv, rows, 3 * d, d, 3 * d, kEpiBiasBf16, 1, pdl));
+    }
     // attention (:186-222)
     if (p.decode) {
       DecodeAttnArgs a = {};
-      a.qkv = e->qkv;
+      a.qkv = qkv_split ? nullptr : e->qkv;
+      a.qkv_partials = qkv_split ? e->partials : nullptr;
+      a.n_qkv_partials = qkv_split ? p.split_qkv : 0;
+      a.partial_rows = rows;
+      a.qkv_bias = w.b_qkv;
       a.active_slots = e->active_dev;
       a.seq_len = e->seq_len;
       a.finished = e->finished;
@@ -328,7 +348,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       a.n_splits = p.attn_splits;
       a.scratch = e->attn_scratch;
       a.pdl = pdl;
-      B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
+      if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
       if (p.attn_splits > 1) e->launches += 1, e->launches_in_capture += 1;
     } else {
       B200_PROPAGATE(count(e, kv_scatter(e->qkv, e->row_slot, e->row_pos, e->page_table,
@@ -346,7 +366,16 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       B200_PROPAGATE(ln(e, nullptr, 0, rows, nullptr, w.ln2_g, w.ln2_b, nullptr, rows, pdl));
     }
     // mlp c_fc + gelu_new (:239-240)
-    B200_PROPAGATE(gemm(e, e->h, w.w_fc, w.b_fc, e->ffn, rows, 4 * d, d, 4 * d, kEpiBiasGeluBf16, 1, pdl));
+    if (p.decode && p.split_fc > 1) {
+      B200_PROPAGATE(gemm(e, e->h, w.w_fc, nullptr, e->partials, rows, 4 * d, d, 4 * d,
+                          kEpiPartialF32, p.split_fc, pdl));
+      if (!(e->skip_mask & kSkipGelu)) {
+        B200_PROPAGATE(count(e, reduce_bias_gelu(e->partials, p.split_fc, rows, w.b_fc, e->ffn, rows,
+                                                 4 * d, pdl, e->stream)));
+      }
+    } else {
+      B200_PROPAGATE(gemm(e, e->h, w.w_fc, w.b_fc, e->ffn, rows, 4 * d, d, 4 * d, kEpiBiasGeluBf16, 1, pdl));
+    }
     // mlp c_proj + residual (:241, :307)
     if (p.split_p > 1) {
       B200_PROPAGATE(gemm(e, e->ffn, w.w_proj, nullptr, e->partials, rows, d, 4 * d, d,
@@ -391,7 +420,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
     g.eos_logit = e->eos_logit;
     g.ld_amax = e->logits_rows;
     g.eos_id = e->cfg.eos_token_id;
-    B200_PROPAGATE(count(e, gemm_bf16(g, e->stream)));
+    if (!(e->skip_mask & kSkipHead)) B200_PROPAGATE(count(e, gemm_bf16(g, e->stream)));
   }
 
   SelectArgs s = {};
@@ -419,7 +448,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
   s.top_k = e->top_k;
   s.seed = e->seed;
   s.advance_seq = p.decode ? 1 : 0;
-  B200_PROPAGATE(count(e, select_tokens(s, e->stream)));
+  if (!(e->skip_mask & kSkipSelect)) B200_PROPAGATE(count(e, select_tokens(s, e->stream)));
   return kOk;
 }
 
@@ -474,6 +503,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
 
   std::unique_ptr<b200llm_engine> e(new b200llm_engine());
   e->cfg = *cfg;
+  if (const char* skip = std::getenv("B200LLM_SKIP")) e->skip_mask = std::atoi(skip);
   e->d = cfg->d_model;
   e->H = cfg->n_head;
   e->L = cfg->n_layer;
@@ -849,6 +879,8 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   if (bucket <= 256 && cap > 1) {
     p.split_o = pick_split(e->d, e->d, sms, cap);
     p.split_p = pick_split(e->d, 4 * e->d, sms, cap);
+    p.split_qkv = pick_split(3 * e->d, e->d, sms, cap);
+    p.split_fc = pick_split(4 * e->d, e->d, sms, cap);
   }
   // split-KV when (rows x heads) alone cannot fill the machine and contexts are long
   {
@@ -1098,6 +1130,10 @@ int b200llm_op_decode_attention(const void* qkv, const int32_t* seq_len, const i
                  "op_decode_attention: null argument");
   DecodeAttnArgs a = {};
   a.qkv = static_cast<const __nv_bfloat16*>(qkv);
+  a.qkv_partials = nullptr;
+  a.n_qkv_partials = 0;
+  a.partial_rows = 0;
+  a.qkv_bias = nullptr;
   a.active_slots = nullptr;
   a.seq_len = seq_len;
   a.finished = nullptr;

@@ -28,6 +28,20 @@
 
 #include "common.cuh"
 
+#ifdef B200_GEMM_TRACE
+// Profiling build only (profiles/gemm_trace.cu): CTA 0 records SM-clock timestamps of its
+// pipeline milestones so the per-kernel latency chain can be read without a profiler.
+__device__ unsigned long long g_gemm_trace[16];
+#define B200_TRACE(slot)                                                   \
+  do {                                                                     \
+    if (blockIdx.x == 0 && blockIdx.y == 0) g_gemm_trace[slot] = clock64(); \
+  } while (0)
+#else
+#define B200_TRACE(slot) \
+  do {                   \
+  } while (0)
+#endif
+
 namespace b200llm {
 
 namespace {
@@ -43,10 +57,13 @@ struct TileCfg {
   static constexpr int kABytes = kBlockM * kBlockK * 2;
   static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BLOCK_N >= 256) ? 4 : (BLOCK_N >= 128) ? 6 : 8;
+  static constexpr int kMaxStages = (BLOCK_N >= 256) ? 4 : (BLOCK_N >= 128) ? 6 : 8;
   static constexpr int kTmemCols = (kAccumStages * BLOCK_N < 32) ? 32 : kAccumStages * BLOCK_N;
-  // ring + barriers + tmem base slot, plus 1024 B slack for manual alignment.
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
+  // ring + barriers + tmem base slot, plus 1024 B slack for manual alignment. The ring depth
+  // is a launch-time choice: short split-K CTAs take a small ring so that two CTAs (this
+  // kernel's and the next kernel's, started early by programmatic dependent launch) fit on
+  // one SM; long weight streams take the full ring.
+  static constexpr int smem_bytes(int stages) { return stages * kStageBytes + 1024 + 256; }
 };
 
 struct KernelArgs {
@@ -63,6 +80,7 @@ struct KernelArgs {
   float* eos_logit;
   int ld_amax;
   int eos_id;
+  int stages;  // smem ring depth actually allocated (<= TileCfg::kMaxStages)
 };
 
 template <int N>
@@ -90,7 +108,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
             const KernelArgs args) {
   using Cfg = TileCfg<BLOCK_N>;
-  constexpr int kStages = Cfg::kStages;
+  const int kStages = args.stages;
   constexpr int kChunk = (BLOCK_N >= 32) ? 32 : 16;  // columns per tcgen05.ld
 
   extern __shared__ uint8_t smem_raw[];
@@ -106,6 +124,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) B200_TRACE(0);
 
   const int num_m_blocks = (args.a_rows + kBlockM - 1) / kBlockM;
   const int num_n_blocks = (args.b_rows + BLOCK_N - 1) / BLOCK_N;
@@ -142,6 +161,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   // Let the next kernel of the step start its own prologue / weight prefetch now; it still
   // waits (griddepcontrol.wait) for this grid to finish before touching activations.
   pdl_launch_dependents();
+  if (threadIdx.x == 0) B200_TRACE(1);
 
   if (warp == 0) {
     // ================= TMA producer =================
@@ -165,7 +185,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         mbar_arrive_expect_tx(&full_bar[it], Cfg::kStageBytes);
         tma_load_2d(sa, &map_a, &full_bar[it], kb * kBlockK, m_blk * kBlockM, kEvictFirst);
       }
+      B200_TRACE(2);
       pdl_wait();
+      B200_TRACE(3);
       for (int it = 0; it < pre; ++it) {
         const int tile = blockIdx.x + (it / num_kb) * gridDim.x;
         const int kb = kb_begin + it % num_kb;
@@ -203,6 +225,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(astage * BLOCK_N);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
+          if (kb == 0) B200_TRACE(4);
           tc_fence_after();
           const uint32_t sa = smem_u32(ring + stage * Cfg::kStageBytes);
           const uint32_t sb = sa + Cfg::kABytes;
@@ -222,6 +245,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           }
         }
         umma_commit(&tmem_full_bar[astage]);  // accumulator complete
+        B200_TRACE(5);
         if (++astage == kAccumStages) {
           astage = 0;
           aphase ^= 1u;
@@ -238,6 +262,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       const int m_blk = tile % num_m_blocks;
       const int n_blk = tile / num_m_blocks;
       mbar_wait(&tmem_full_bar[astage], aphase);
+      if (threadIdx.x == 128) B200_TRACE(6);
       tc_fence_after();
       const int a_row = m_blk * kBlockM + q * 32 + lane;  // row of the 128-row operand
       const bool a_ok = a_row < args.a_rows;
@@ -255,6 +280,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
                                static_cast<uint32_t>(astage * BLOCK_N + c0);
         tmem_ld_cols<kChunk>(taddr, r);
         tmem_ld_wait();
+        if (threadIdx.x == 128 && c0 == 0) B200_TRACE(9);
+        if (threadIdx.x == 128 && c0 == kChunk) B200_TRACE(10);
         const int b_row0 = n_blk * BLOCK_N + c0;  // first row of the N operand in this chunk
 
         if (TRANS && EPI == kEpiLogitsArgmax) {
@@ -302,28 +329,51 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           }
         } else if (TRANS) {
           // lane = feature (a_row), columns = tokens. For each token the warp's 32 lanes
-          // write 32 consecutive features -> coalesced.
+          // write 32 consecutive features -> one coalesced 64/128-byte store. Addresses advance
+          // by a running pointer and the tail is predicated (no per-store branches / 64-bit
+          // multiplies: that version took ~60 cycles per store).
           const int feature = a_row;
+          const int n_valid = a_ok ? (args.b_rows - b_row0) : 0;  // valid token columns here
+          const size_t ld = static_cast<size_t>(args.ld_out);
+          if (EPI == kEpiBiasBf16 || EPI == kEpiBiasGeluBf16) {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(args.out) +
+                               static_cast<size_t>(b_row0) * ld + feature;
 #pragma unroll
-          for (int j = 0; j < kChunk; ++j) {
-            const int token = b_row0 + j;
-            if (a_ok && token < args.b_rows) {
-              float v = __uint_as_float(r[j]);
-              const size_t idx = static_cast<size_t>(token) * args.ld_out + feature;
-              if (EPI == kEpiBiasBf16) {
-                reinterpret_cast<__nv_bfloat16*>(args.out)[idx] = __float2bfloat16(v + bias_lane);
-              } else if (EPI == kEpiBiasGeluBf16) {
-                reinterpret_cast<__nv_bfloat16*>(args.out)[idx] =
-                    __float2bfloat16(gelu_new(v + bias_lane));
-              } else if (EPI == kEpiBiasResidF32) {
-                float* o = reinterpret_cast<float*>(args.out);
-                o[idx] = o[idx] + (v + bias_lane);
-              } else if (EPI == kEpiF32) {
-                reinterpret_cast<float*>(args.out)[idx] = v;
-              } else {  // kEpiPartialF32
-                const size_t pidx =
-                    (static_cast<size_t>(split) * args.tokens + token) * args.ld_out + feature;
-                reinterpret_cast<float*>(args.out)[pidx] = v;
+            for (int j = 0; j < kChunk; ++j) {
+              float x = __uint_as_float(r[j]) + bias_lane;
+              if (EPI == kEpiBiasGeluBf16) x = gelu_new(x);
+              const __nv_bfloat16 y = __float2bfloat16(x);
+              if (j < n_valid) *o = y;
+              o += ld;
+            }
+          } else {
+            float* o = reinterpret_cast<float*>(args.out) + feature;
+            if (EPI == kEpiPartialF32) {
+              o += (static_cast<size_t>(split) * args.tokens + b_row0) * ld;
+            } else {
+              o += static_cast<size_t>(b_row0) * ld;
+            }
+            if (EPI == kEpiBiasResidF32) {
+              float old[kChunk];
+              {
+                const float* oi = o;
+#pragma unroll
+                for (int j = 0; j < kChunk; ++j) {
+                  old[j] = (j < n_valid) ? *oi : 0.f;
+                  oi += ld;
+                }
+              }
+#pragma unroll
+              for (int j = 0; j < kChunk; ++j) {
+                const float x = old[j] + (__uint_as_float(r[j]) + bias_lane);
+                if (j < n_valid) *o = x;
+                o += ld;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < kChunk; ++j) {
+                if (j < n_valid) *o = __uint_as_float(r[j]);
+                o += ld;
               }
             }
           }
@@ -411,6 +461,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       }
       // All TMEM reads of this accumulator stage are complete (tcgen05.wait::ld above).
       tc_fence_before();
+      if (threadIdx.x == 128) B200_TRACE(7);
       mbar_arrive(&tmem_empty_bar[astage]);
       if (++astage == kAccumStages) {
         astage = 0;
@@ -425,6 +476,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
+  if (threadIdx.x == 64) B200_TRACE(8);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -540,18 +592,23 @@ int launch(const GemmArgs& g, cudaStream_t stream) {
     if (cap < 1) cap = 1;
     if (grid_x > cap) grid_x = cap;
   }
+  // ring depth: enough for every k-block this CTA will ever load, at least 2, at most the max
+  const int iters_per_cta = ((num_tiles + grid_x - 1) / grid_x) * ka.k_blocks_per_split;
+  int stages = iters_per_cta < Cfg::kMaxStages ? iters_per_cta : Cfg::kMaxStages;
+  if (stages < 2) stages = 2;
+  ka.stages = stages;
 
   auto kernel = gemm_kernel<BLOCK_N, EPI, TRANS>;
   static bool attr_set = false;
   if (!attr_set) {
     B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      Cfg::kSmemBytes));
+                                      Cfg::smem_bytes(Cfg::kMaxStages)));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid_x, split, 1);
   cfg.blockDim = dim3(kThreads, 1, 1);
-  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.dynamicSmemBytes = Cfg::smem_bytes(stages);
   cfg.stream = stream;
   cudaLaunchAttribute attrs[1];
   attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

@@ -130,6 +130,39 @@ layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int 
 }
 
 // ---------------------------------------------------------------------------------------
+// Split-K reduce + bias + gelu_new -> bf16 (one float4 column group per thread)
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+reduce_bias_gelu_kernel(const float* __restrict__ partials, int n_partials, size_t plane_f4,
+                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int rows,
+                        int cols4) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int total = rows * cols4;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int c4 = idx % cols4;
+  if (idx < total) acc = __ldg(reinterpret_cast<const float4*>(bias) + c4);
+  pdl_wait();
+  pdl_launch_dependents();
+  if (idx >= total) return;
+  const float4* p = reinterpret_cast<const float4*>(partials) + idx;
+  int s = 0;
+  for (; s + 2 <= n_partials; s += 2) {
+    const float4 p0 = p[static_cast<size_t>(s) * plane_f4];
+    const float4 p1 = p[static_cast<size_t>(s + 1) * plane_f4];
+    acc.x += p0.x; acc.y += p0.y; acc.z += p0.z; acc.w += p0.w;
+    acc.x += p1.x; acc.y += p1.y; acc.z += p1.z; acc.w += p1.w;
+  }
+  for (; s < n_partials; ++s) {
+    const float4 p0 = p[static_cast<size_t>(s) * plane_f4];
+    acc.x += p0.x; acc.y += p0.y; acc.z += p0.z; acc.w += p0.w;
+  }
+  uint2 pk;
+  pk.x = pack_bf16x2(gelu_new(acc.x), gelu_new(acc.y));
+  pk.y = pack_bf16x2(gelu_new(acc.z), gelu_new(acc.w));
+  reinterpret_cast<uint2*>(out)[idx] = pk;
+}
+
+// ---------------------------------------------------------------------------------------
 // Token selection
 // ---------------------------------------------------------------------------------------
 struct MaxIdx {
@@ -416,6 +449,16 @@ int layernorm(const LayerNormArgs& a, cudaStream_t stream) {
   return launch_pdl(layernorm_kernel, dim3(a.rows), dim3(threads), stream, a.pdl, a.x, a.partials,
                     a.n_partials, a.add_bias, a.gamma, a.beta, a.row_index, a.out, a.d, rows_total,
                     a.eps);
+}
+
+int reduce_bias_gelu(const float* partials, int n_partials, int partial_rows, const float* bias,
+                     __nv_bfloat16* out, int rows, int cols, int pdl, cudaStream_t stream) {
+  B200_CHECK_ARG(partials && bias && out && rows > 0 && cols % 4 == 0 && n_partials > 0,
+                 "reduce_bias_gelu: bad arguments");
+  const int total = rows * (cols / 4);
+  const size_t plane_f4 = static_cast<size_t>(partial_rows > 0 ? partial_rows : rows) * cols / 4;
+  return launch_pdl(reduce_bias_gelu_kernel, dim3((total + 255) / 256), dim3(256), stream, pdl,
+                    partials, n_partials, plane_f4, bias, out, rows, cols / 4);
 }
 
 int select_tokens(const SelectArgs& a, cudaStream_t stream) {

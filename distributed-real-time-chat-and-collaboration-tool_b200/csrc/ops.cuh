@@ -75,6 +75,11 @@ struct SelectArgs {
 // finished rows emit pad (:2796-2797); EOS marks a row finished (stopping_criteria.py:450-471).
 int select_tokens(const SelectArgs& a, cudaStream_t stream);
 
+// out_bf16[r, c] = gelu_new(bias[c] + sum_s partials[s][r, c]): finishes a split-K MLP
+// up-projection (modeling_gpt2.py:239-240) so the down-projection can read it through TMA.
+int reduce_bias_gelu(const float* partials, int n_partials, int partial_rows, const float* bias,
+                     __nv_bfloat16* out, int rows, int cols, int pdl, cudaStream_t stream);
+
 // Plain row-wise argmax (unit tests / teacher-forced parity).
 int argmax_rows(const float* logits, int rows, int ld, int vocab, int32_t* out,
                 cudaStream_t stream);

@@ -1,0 +1,71 @@
+// Profiling tool (not part of the library): runs decode-shaped GEMMs with the kernel's
+// B200_GEMM_TRACE timestamps enabled and prints CTA 0's milestone timeline in SM cycles.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -DB200_GEMM_TRACE \
+//        -I<pkg>/csrc profiles/gemm_trace.cu -o profiles/gemm_trace -lcudart
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "gemm_tcgen05.cu"
+
+namespace b200llm {
+static thread_local std::string g_err;
+void set_last_error(const std::string& m) { g_err = m; }
+int fail(int code, const std::string& m) { g_err = m; return code; }
+}  // namespace b200llm
+
+using namespace b200llm;
+
+static void run(const char* name, int tokens, int features, int k, int epi, int split) {
+  __nv_bfloat16 *act, *w;
+  float *bias, *out;
+  cudaMalloc(&act, (size_t)256 * k * 2);
+  cudaMalloc(&w, (size_t)features * k * 2);
+  cudaMalloc(&bias, features * 4);
+  cudaMalloc(&out, (size_t)32 * 256 * features * 4);
+  cudaMemset(act, 0, (size_t)256 * k * 2);
+  cudaMemset(w, 0, (size_t)features * k * 2);
+  cudaMemset(bias, 0, features * 4);
+  GemmArgs g = {};
+  g.act = act; g.w = w; g.bias = bias; g.out = out; g.tokens = tokens; g.features = features; g.k = k;
+  g.ld_out = features; g.epilogue = epi; g.split_k = split; g.act_rows_alloc = 256;
+  g.force_orientation = 1; g.pdl = 0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  for (int i = 0; i < 3; ++i) {
+    if (gemm_bf16(g, 0) != 0) { printf("%s: %s\n", name, g_err.c_str()); return; }
+  }
+  cudaDeviceSynchronize();
+  // flush L2 so the weights come from HBM like in a real step
+  void* flush; cudaMalloc(&flush, 256 << 20); cudaMemset(flush, 1, 256 << 20); cudaDeviceSynchronize();
+  cudaEventRecord(e0);
+  gemm_bf16(g, 0);
+  cudaEventRecord(e1);
+  cudaDeviceSynchronize();
+  float ms; cudaEventElapsedTime(&ms, e0, e1);
+  unsigned long long t[16];
+  cudaMemcpyFromSymbol(t, g_gemm_trace, sizeof(t));
+  printf("%-28s event %.2f us | cycles from CTA start: setup %llu, A issued %llu, pdl ok %llu, first full %llu, "
+         "mma done-issue %llu, tmem_full %llu, ld0 done %llu, ld1 done %llu, epilogue end %llu, exit %llu\n",
+         name, ms * 1e3, t[1] - t[0], t[2] - t[0], t[3] - t[0], t[4] - t[0], t[5] - t[0], t[6] - t[0],
+         t[9] - t[0], t[10] - t[0], t[7] - t[0], t[8] - t[0]);
+  // warm L2 timing of 20 back-to-back launches
+  cudaEventRecord(e0);
+  for (int i = 0; i < 20; ++i) gemm_bf16(g, 0);
+  cudaEventRecord(e1);
+  cudaDeviceSynchronize();
+  cudaEventElapsedTime(&ms, e0, e1);
+  printf("%-28s back-to-back avg %.2f us\n", name, ms * 1e3 / 20);
+  cudaFree(act); cudaFree(w); cudaFree(bias); cudaFree(out); cudaFree(flush);
+}
+
+int main() {
+  run("qkv 64x2304x768 nosplit", 64, 2304, 768, kEpiBiasBf16, 1);
+  run("qkv 64x2304x768 split6", 64, 2304, 768, kEpiPartialF32, 6);
+  run("proj 64x768x768 split12", 64, 768, 768, kEpiPartialF32, 12);
+  run("fc 64x3072x768 nosplit", 64, 3072, 768, kEpiBiasGeluBf16, 1);
+  run("fc 64x3072x768 split6", 64, 3072, 768, kEpiPartialF32, 6);
+  run("proj2 64x768x3072 split24", 64, 768, 3072, kEpiPartialF32, 24);
+  run("head 64x50257x768", 64, 50257, 768, kEpiF32, 1);
+  return 0;
+}
