@@ -155,9 +155,12 @@ def run_ours(args):
     eng.set_stream(stream.cuda_stream)
     sp = [E.SamplingParams(max_new_tokens=N, min_new_tokens=N)] * B
 
-    # each rank serves its own shard of the request stream
-    rng = np.random.default_rng(1234 + rank)
-    prompts_np = rng.integers(0, shape.vocab_size - 1, size=(B, T), dtype=np.int32)
+    # one global request stream (B sequences per replica), sharded by request across the ranks
+    sharding = importlib.import_module(f"{PKG}.sharding")
+    rng = np.random.default_rng(1234)
+    stream = rng.integers(0, shape.vocab_size - 1, size=(B * world, T), dtype=np.int32)
+    prompts_np = np.ascontiguousarray(sharding.shard_requests(stream, rank, world))
+    assert prompts_np.shape[0] == B
     prompts = [row for row in prompts_np]
     ids_dev = torch.from_numpy(prompts_np.reshape(-1)).to(dev)
     chunk = max(1, min(B, 16384 // T))  # sequences per prefill call

@@ -599,11 +599,14 @@ int launch(const GemmArgs& g, cudaStream_t stream) {
   ka.stages = stages;
 
   auto kernel = gemm_kernel<BLOCK_N, EPI, TRANS>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  // the opt-in shared-memory limit is a per-device function attribute
+  static bool attr_set[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       Cfg::smem_bytes(Cfg::kMaxStages)));
-    attr_set = true;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid_x, split, 1);

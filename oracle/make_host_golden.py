@@ -28,9 +28,10 @@ def load_reference():
     stub = types.ModuleType("google.generativeai")
     stub.configure = lambda **kw: None
     stub.GenerativeModel = lambda name: object()
-    google = types.ModuleType("google")
+    import google.protobuf  # noqa: F401  (the real `google` namespace package must stay importable)
+    import google
+
     google.generativeai = stub
-    sys.modules.setdefault("google", google)
     sys.modules["google.generativeai"] = stub
     sys.path.insert(0, str(REF))
     sys.path.insert(0, str(REF / "llm_server"))

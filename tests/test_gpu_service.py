@@ -1,0 +1,106 @@
+"""The whole drop-in path on a real GPU: LLMService RPC -> LLMServicer (reference prompts and
+parsers) -> LocalGenerativeModel -> Router/worker (continuous batching) -> CUDA engine."""
+import threading
+from concurrent import futures
+
+import grpc
+import numpy as np
+import pytest
+import torch
+
+from conftest import pkg
+from oracle import gpt2_oracle as O
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+
+
+@pytest.fixture(scope="module")
+def stack(cuda):
+    E, sched, lm, tok = pkg("engine"), pkg("scheduler"), pkg("local_model"), pkg("tokenizer")
+    w = O.synthetic_weights(O.SMALL, seed=0)
+    eng = E.Engine(E.GPT2_SMALL, O.pack_blob(O.SMALL, w).numpy(), max_seqs=32, max_seq_len=1024,
+                   max_batch_tokens=8192, max_new_tokens=64)
+    worker = sched.EngineWorker(eng, decode_burst=8)
+    router = sched.Router([worker])
+    model = lm.LocalGenerativeModel(router, tok.ByteLevelTokenizer(), default_max_new_tokens=24,
+                                    max_prompt_tokens=900)
+    yield {"engine": eng, "router": router, "model": model, "weights": w, "worker": worker}
+    router.shutdown()
+    eng.close()
+
+
+def test_scheduler_tokens_equal_direct_engine_and_oracle(stack):
+    """Continuous batching must not change results: tokens from concurrent submissions equal the
+    oracle's greedy tokens wherever its margin is decisive."""
+    E = pkg("engine")
+    ids = O.synthetic_prompts(6, 40, seed=21)
+    ref, _, margins = O.greedy_generate(O.SMALL, stack["weights"], ids, 12, min_new_tokens=12)
+    sp = E.SamplingParams(max_new_tokens=12, min_new_tokens=12)
+    futs = [stack["router"].submit(ids[i].tolist(), sp) for i in range(6)]
+    got = np.array([f.result(timeout=60).tokens for f in futs])
+    ref = ref.numpy()
+    same_prefix = np.cumprod(np.concatenate([np.ones((6, 1), bool), got[:, :-1] == ref[:, :-1]], 1), 1).astype(bool)
+    decisive = margins.numpy() > 0.1
+    assert (got[same_prefix & decisive] == ref[same_prefix & decisive]).all()
+    assert (got == ref).mean() > 0.8
+
+
+def test_grpc_round_trip_all_rpcs_with_the_cuda_backend(stack):
+    server_mod, svc, pb = pkg("server"), pkg("llm_service"), pkg("llm_proto")
+    server = grpc.server(futures.ThreadPoolExecutor(max_workers=32))
+    server_mod.add_llm_service(svc.LLMServicer(stack["model"]), server)
+    port = server.add_insecure_port("127.0.0.1:0")
+    server.start()
+    launches0 = stack["engine"].kernel_launches
+    try:
+        with grpc.insecure_channel(f"127.0.0.1:{port}") as ch:
+            stub = server_mod.LLMServiceStub(ch)
+            msgs = [pb.Message(sender="alice", content="Are we still on for 3pm?"),
+                    pb.Message(sender="bob", content="Yes, room 4B.")]
+            r = stub.GetSmartReply(pb.SmartReplyRequest(request_id="s", recent_messages=msgs, user_id="bob"), timeout=20)
+            assert r.request_id == "s" and 2 <= len(r.suggestions) <= 3
+            r = stub.SummarizeConversation(pb.SummarizeRequest(request_id="m", messages=msgs, max_length=80), timeout=20)
+            assert r.request_id == "m" and len(r.summary) <= 80 and 1 <= len(r.key_points) <= 3
+            r = stub.GetLLMAnswer(pb.LLMRequest(request_id="a", query="When?", context=["alice: 3pm"]), timeout=20)
+            assert r.request_id == "a" and abs(r.confidence - 0.95) < 1e-6
+            r = stub.GetContextSuggestions(pb.ContextRequest(request_id="c", context=msgs, current_input="I"), timeout=20)
+            assert r.request_id == "c" and len(r.suggestions) >= 1 and len(r.topics) >= 1
+
+            # concurrent callers are batched by the worker
+            out = []
+            def call(i):
+                out.append(stub.GetSmartReply(pb.SmartReplyRequest(request_id=str(i), recent_messages=msgs), timeout=30))
+            ts = [threading.Thread(target=call, args=(i,)) for i in range(24)]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
+            assert sorted(int(o.request_id) for o in out) == list(range(24))
+    finally:
+        server.stop(0)
+    assert stack["engine"].kernel_launches > launches0, "the CUDA engine did not run"
+    assert stack["worker"].completed >= 28
+
+
+def test_generate_content_shape_and_finish_reasons(stack):
+    resp = stack["model"].generate_content("Hello there")
+    assert resp and len(resp.candidates) == 1 and resp.candidates[0].finish_reason in (1, 2)
+    assert isinstance(resp.text, str) and resp.usage["generated_tokens"] <= 24
+    resp = stack["model"].generate_content("Hello", generation_config={"temperature": 0.7, "max_output_tokens": 5})
+    assert resp.usage["generated_tokens"] <= 5
+    with pytest.raises(ValueError):
+        stack["model"].generate_content("")
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_two_replicas_give_the_same_tokens_as_one(stack):
+    E, sched = pkg("engine"), pkg("scheduler")
+    blob = O.pack_blob(O.SMALL, stack["weights"]).numpy()
+    engines = [E.Engine(E.GPT2_SMALL, blob, device=d, max_seqs=16, max_seq_len=256, max_batch_tokens=4096,
+                        max_new_tokens=16) for d in (0, 1)]
+    router = sched.Router([sched.EngineWorker(e) for e in engines])
+    ids = O.synthetic_prompts(16, 32, seed=3)
+    sp = E.SamplingParams(max_new_tokens=8, min_new_tokens=8)
+    two = [f.result(timeout=60).tokens for f in [router.submit(ids[i].tolist(), sp) for i in range(16)]]
+    one = [stack["router"].generate(ids[i].tolist(), sp, timeout=60).tokens for i in range(16)]
+    router.shutdown()
+    [e.close() for e in engines]
+    assert two == one
