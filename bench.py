@@ -158,8 +158,8 @@ def run_ours(args):
     # one global request stream (B sequences per replica), sharded by request across the ranks
     sharding = importlib.import_module(f"{PKG}.sharding")
     rng = np.random.default_rng(1234)
-    stream = rng.integers(0, shape.vocab_size - 1, size=(B * world, T), dtype=np.int32)
-    prompts_np = np.ascontiguousarray(sharding.shard_requests(stream, rank, world))
+    request_stream = rng.integers(0, shape.vocab_size - 1, size=(B * world, T), dtype=np.int32)
+    prompts_np = np.ascontiguousarray(sharding.shard_requests(request_stream, rank, world))
     assert prompts_np.shape[0] == B
     prompts = [row for row in prompts_np]
     ids_dev = torch.from_numpy(prompts_np.reshape(-1)).to(dev)
