@@ -13,6 +13,8 @@
 //   by warp shuffles. Optional split-KV for long contexts with a deterministic combine pass.
 #include "attention.cuh"
 
+#include <mutex>
+
 #include "common.cuh"
 #include "ops.cuh"
 
@@ -548,6 +550,47 @@ int prefill_attention(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int b
 size_t decode_attention_scratch_floats(int batch, int n_head, int n_splits) {
   if (n_splits <= 1) return 0;
   return static_cast<size_t>(batch) * n_head * n_splits * kScratchStride;
+}
+
+// Split-KV partials for callers that must not allocate. The array is part of the library's
+// device image: every GPU that loads libb200llm.so carries these 4 MiB until the process exits.
+// In host code the name below only stands for the symbol; the device address comes from
+// cudaGetSymbolAddress (done once per device, with that device current).
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchFloats];
+
+int decode_attention_noalloc(DecodeAttnArgs a, cudaStream_t stream) {
+  B200_CHECK_ARG(a.batch > 0 && a.n_head > 0 && a.n_splits >= 1, "decode_attention_noalloc: bad shape");
+  const size_t need = decode_attention_scratch_floats(a.batch, a.n_head, a.n_splits);
+  if (need > kNoAllocScratchFloats) {
+    return fail(kErrCapacity,
+                "decode_attention_noalloc: batch*n_head*n_splits*66 = " + std::to_string(need) +
+                    " floats of split-KV partials exceed the built-in scratch of " +
+                    std::to_string(kNoAllocScratchFloats) +
+                    " floats; use fewer splits or the entry point that takes a scratch buffer");
+  }
+  static std::mutex mu;
+  static float* resolved[64] = {};  // per device ordinal
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  B200_CHECK_ARG(dev >= 0 && dev < 64, "decode_attention_noalloc: unsupported device ordinal");
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (resolved[dev] == nullptr) {
+      void* p = nullptr;
+      const cudaError_t err = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+      if (err != cudaSuccess || p == nullptr) {
+        return fail(kErrCuda, std::string("decode_attention_noalloc: cudaGetSymbolAddress: ") +
+                                  cudaGetErrorString(err));
+      }
+      resolved[dev] = static_cast<float*>(p);
+    }
+    scratch = resolved[dev];
+  }
+  // Nothing in the scratch has to start at zero: every (row, head, split) slot that the
+  // combine pass reads is written by its own CTA first, empty splits included.
+  a.scratch = scratch;
+  return decode_attention(a, stream);
 }
 
 int decode_attention(const DecodeAttnArgs& a, cudaStream_t stream) {

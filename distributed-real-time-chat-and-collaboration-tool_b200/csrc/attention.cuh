@@ -46,4 +46,10 @@ int decode_attention(const DecodeAttnArgs& a, cudaStream_t stream);
 // Floats of scratch decode_attention needs for (batch, n_head, n_splits).
 size_t decode_attention_scratch_floats(int batch, int n_head, int n_splits);
 
+// Same step, but the split-KV partials live in a fixed array that is part of the loaded
+// library image instead of a caller-provided buffer (a.scratch is ignored). See the comment
+// on b200llm_op_decode_attention_noalloc in include/b200llm.h for who needs this and its rules.
+constexpr size_t kNoAllocScratchFloats = 1u << 20;  // 4 MiB per GPU that loads the library
+int decode_attention_noalloc(DecodeAttnArgs a, cudaStream_t stream);
+
 }  // namespace b200llm

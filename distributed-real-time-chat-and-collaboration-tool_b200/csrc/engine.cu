@@ -1150,6 +1150,26 @@ int b200llm_op_decode_attention(const void* qkv, const int32_t* seq_len, const i
   return decode_attention(a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int b200llm_op_decode_attention_noalloc(const void* qkv, const int32_t* seq_len,
+                                        const int32_t* page_table, int32_t max_pages_per_seq,
+                                        void* k_pool, void* v_pool, void* out, int32_t batch,
+                                        int32_t n_head, int32_t n_splits, void* stream) {
+  B200_CHECK_ARG(qkv && seq_len && page_table && k_pool && v_pool && out,
+                 "op_decode_attention_noalloc: null argument");
+  DecodeAttnArgs a = {};
+  a.qkv = static_cast<const __nv_bfloat16*>(qkv);
+  a.seq_len = seq_len;
+  a.page_table = page_table;
+  a.max_pages_per_seq = max_pages_per_seq;
+  a.k_pool = static_cast<__nv_bfloat16*>(k_pool);
+  a.v_pool = static_cast<__nv_bfloat16*>(v_pool);
+  a.out = static_cast<__nv_bfloat16*>(out);
+  a.batch = batch;
+  a.n_head = n_head;
+  a.n_splits = n_splits;
+  return decode_attention_noalloc(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
 size_t b200llm_decode_attention_scratch_floats(int32_t batch, int32_t n_head, int32_t n_splits) {
   return decode_attention_scratch_floats(batch, n_head, n_splits);
 }

@@ -206,6 +206,38 @@ int b200llm_op_decode_attention(const void* qkv_dev, const int32_t* seq_len_dev,
                                 int32_t n_head, int32_t n_splits, float* scratch_dev, void* stream);
 size_t b200llm_decode_attention_scratch_floats(int32_t batch, int32_t n_head, int32_t n_splits);
 
+/*
+ * b200llm_op_decode_attention without a scratch argument. (No counterpart in the reference: it
+ * has no attention code at all; this exists only for embedders of this library.)
+ *
+ * Who it is for: a host that cannot obtain device memory at the moment it wants to run a
+ * split-KV decode step -- for example a serving loop whose memory was handed out once at start-up
+ * to its own pool so that a later cudaMalloc would fail or would stall every stream of the device
+ * while the driver serves it, or a plug-in that is only given input and output buffers by its
+ * caller and has nowhere to keep a workspace of its own. Such a caller still passes the inputs and
+ * the output exactly as above; the partial results of the KV splits go to a fixed array inside the
+ * library image instead.
+ *
+ * Rules
+ *   - Limit: batch * n_head * n_splits * 66 floats must not exceed
+ *     B200LLM_NOALLOC_SCRATCH_FLOATS (4 MiB). Larger requests return B200LLM_ERR_CAPACITY with an
+ *     explanatory b200llm_last_error(); nothing is launched.
+ *   - Cost: every GPU on which the library is loaded holds those 4 MiB until the process exits.
+ *   - The call performs no cudaMalloc / cudaFree and uses no allocating library routine.
+ *   - The first call on each device looks up the array's device address (with that device
+ *     current). Make that first call before starting any stream capture on the device.
+ *   - All calls on a device share the one array, which keeps whatever the previous call left in
+ *     it. Nothing in it needs clearing (each slot is written before it is read within a call),
+ *     but two calls whose kernels can run at the same time on the GPU -- different streams without
+ *     an ordering between them -- race on it. Order them.
+ */
+#define B200LLM_NOALLOC_SCRATCH_FLOATS (1u << 20)
+int b200llm_op_decode_attention_noalloc(const void* qkv_dev, const int32_t* seq_len_dev,
+                                        const int32_t* page_table_dev, int32_t max_pages_per_seq,
+                                        void* k_pool_dev, void* v_pool_dev, void* out_dev,
+                                        int32_t batch, int32_t n_head, int32_t n_splits,
+                                        void* stream);
+
 /* Row-wise argmax of fp32 logits, ties to the lowest index ($TF/generation/utils.py:2793). */
 int b200llm_op_argmax(const float* logits_dev, int32_t rows, int32_t ld, int32_t vocab,
                       int32_t* out_dev, void* stream);
