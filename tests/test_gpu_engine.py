@@ -189,3 +189,36 @@ def test_temperature_topk_sampling_is_seeded_and_in_topk(cuda):
     logits[TINY.eos_token_id] = -float("inf")
     assert a[0][0] in logits.topk(8).indices.tolist()
     eng.close()
+
+
+@pytest.mark.parametrize("name", ["medium", "large"])
+def test_medium_and_large_teacher_forced_logits(cuda, name):
+    """The other BASELINE model sizes (d = 1024 / 1280, 16 / 20 heads): all-position logits of
+    prompt + oracle continuation within LOGIT_TOL, argmax agreement where the margin is decisive."""
+    shape = O.SHAPES[name]
+    w = O.synthetic_weights(shape, seed=0)
+    B, T, N = 2, 24, 8
+    ids = O.synthetic_prompts(B, T, seed=9)
+    ref_tok, ref_logits, margins = O.greedy_generate(shape, w, ids, N, min_new_tokens=N)
+    eng, E = _engine(shape, w, max_seqs=4, max_seq_len=64, max_batch_tokens=128, max_new_tokens=N + 1)
+    full = torch.cat([ids, ref_tok[:, :-1]], 1)
+    logits = torch.zeros(full.numel(), shape.vocab_size, device=cuda)
+    slots = [eng.seq_alloc(64) for _ in range(B)]
+    eng.prefill(full.tolist(), slots, logits_all_ptr=logits.data_ptr())
+    eng.sync()
+    got = logits.view(B, full.shape[1], -1)[:, T - 1:, :].cpu()
+    err = (got - ref_logits).abs().max().item()
+    print(f"{name}: teacher-forced max |dlogit| = {err:.4f}")
+    assert err <= LOGIT_TOL
+    got[:, :, shape.eos_token_id] = -float("inf")
+    agree = got.argmax(-1) == ref_tok
+    assert agree[margins > 2 * err].all()
+    for s in slots:
+        eng.seq_free(s)
+    # and the decode path (graphs + PDL + split-K) on the same model
+    sp = E.SamplingParams(max_new_tokens=N, min_new_tokens=N)
+    out = np.array(eng.generate(ids.tolist(), sp))
+    ref = ref_tok.numpy()
+    same_prefix = np.cumprod(np.concatenate([np.ones((B, 1), bool), out[:, :-1] == ref[:, :-1]], 1), 1).astype(bool)
+    assert (out[same_prefix & (margins.numpy() > 2 * LOGIT_TOL)] == ref[same_prefix & (margins.numpy() > 2 * LOGIT_TOL)]).all()
+    eng.close()
