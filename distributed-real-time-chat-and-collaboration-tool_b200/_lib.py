@@ -44,6 +44,7 @@ class Config(C.Structure):
         ("use_pdl", C.c_int32),
         ("decode_split_k", C.c_int32),
         ("keep_logits", C.c_int32),
+        ("decode_reduce", C.c_int32),
     ]
 
 

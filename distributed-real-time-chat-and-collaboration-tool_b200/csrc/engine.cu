@@ -223,6 +223,17 @@ int bucket_for(int batch) {
   return (batch + 255) / 256 * 256;
 }
 
+// Cluster split: largest divisor s <= 8 of k_blocks with tiles * s <= sms.
+int pick_cluster(int features, int k, int sms) {
+  const int tiles = (features + 127) / 128;
+  const int kb = k / 64;
+  int best = 1;
+  for (int s = 1; s <= 8; ++s) {
+    if (kb % s == 0 && tiles * s <= sms) best = s;
+  }
+  return best;
+}
+
 // Largest divisor s of k_blocks with tiles * s <= sms and s <= cap.
 int pick_split(int features, int k, int sms, int cap) {
   const int tiles = (features + 127) / 128;
@@ -241,6 +252,8 @@ struct StepPlan {
   int split_fc = 1;   // split-K of the MLP up-proj (partials reduced by reduce_bias_gelu)
   int split_o = 1;    // split-K of the attention out-proj (partials reduced by the next LayerNorm)
   int split_p = 1;    // split-K of the MLP down-proj
+  // cluster (DSMEM) split-K factors; when > 1 they take precedence over the plane splits
+  int cl_qkv = 1, cl_o = 1, cl_fc = 1, cl_p = 1;
   int attn_splits = 1;
   int pdl = 0;
   int batch = 0;       // sequences (prefill) / bucket rows (decode)
@@ -260,8 +273,10 @@ int count(b200llm_engine* e, int rc) {
 }
 
 int gemm(b200llm_engine* e, const __nv_bfloat16* act, const __nv_bfloat16* w, const float* bias,
-         void* out, int tokens, int features, int k, int ld_out, int epi, int split, int pdl) {
+         void* out, int tokens, int features, int k, int ld_out, int epi, int split, int pdl,
+         int cluster_split = 0) {
   GemmArgs g = {};
+  g.cluster_split = cluster_split;
   g.act = act;
   g.w = w;
   g.bias = bias;
@@ -320,8 +335,10 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
     pending_partials = nullptr;
     pending_n = 0;
     // c_attn (:185)
-    const bool qkv_split = p.decode && p.split_qkv > 1;
-    if (qkv_split) {
+    const bool qkv_split = p.decode && p.split_qkv > 1 && p.cl_qkv <= 1;
+    if (p.decode && p.cl_qkv > 1) {
+      B200_PROPAGATE(gemm(e, e->h, w.w_qkv, w.b_qkv, e->qkv, rows, 3 * d, d, 3 * d, kEpiBiasBf16, 1, pdl, p.cl_qkv));
+    } else if (qkv_split) {
       B200_PROPAGATE(gemm(e, e->h, w.w_qkv, nullptr, e->partials, rows, 3 * d, d, 3 * d,
                           kEpiPartialF32, p.split_qkv, pdl));
     } else {
@@ -357,7 +374,10 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
                                                 e->attn, e->stream)));
     }
     // attn c_proj + residual (:223, :282)
-    if (p.split_o > 1) {
+    if (p.decode && p.cl_o > 1) {
+      B200_PROPAGATE(gemm(e, e->attn, w.w_o, w.b_o, e->x, rows, d, d, d, kEpiBiasResidF32, 1, pdl, p.cl_o));
+      B200_PROPAGATE(ln(e, nullptr, 0, rows, nullptr, w.ln2_g, w.ln2_b, nullptr, rows, pdl));
+    } else if (p.split_o > 1) {
       B200_PROPAGATE(gemm(e, e->attn, w.w_o, nullptr, e->partials, rows, d, d, d, kEpiPartialF32,
                           p.split_o, pdl));
       B200_PROPAGATE(ln(e, e->partials, p.split_o, rows, w.b_o, w.ln2_g, w.ln2_b, nullptr, rows, pdl));
@@ -366,7 +386,9 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       B200_PROPAGATE(ln(e, nullptr, 0, rows, nullptr, w.ln2_g, w.ln2_b, nullptr, rows, pdl));
     }
     // mlp c_fc + gelu_new (:239-240)
-    if (p.decode && p.split_fc > 1) {
+    if (p.decode && p.cl_fc > 1) {
+      B200_PROPAGATE(gemm(e, e->h, w.w_fc, w.b_fc, e->ffn, rows, 4 * d, d, 4 * d, kEpiBiasGeluBf16, 1, pdl, p.cl_fc));
+    } else if (p.decode && p.split_fc > 1) {
       B200_PROPAGATE(gemm(e, e->h, w.w_fc, nullptr, e->partials, rows, 4 * d, d, 4 * d,
                           kEpiPartialF32, p.split_fc, pdl));
       if (!(e->skip_mask & kSkipGelu)) {
@@ -377,7 +399,9 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       B200_PROPAGATE(gemm(e, e->h, w.w_fc, w.b_fc, e->ffn, rows, 4 * d, d, 4 * d, kEpiBiasGeluBf16, 1, pdl));
     }
     // mlp c_proj + residual (:241, :307)
-    if (p.split_p > 1) {
+    if (p.decode && p.cl_p > 1) {
+      B200_PROPAGATE(gemm(e, e->ffn, w.w_proj, w.b_proj, e->x, rows, d, 4 * d, d, kEpiBiasResidF32, 1, pdl, p.cl_p));
+    } else if (p.split_p > 1) {
       B200_PROPAGATE(gemm(e, e->ffn, w.w_proj, nullptr, e->partials, rows, d, 4 * d, d,
                           kEpiPartialF32, p.split_p, pdl));
       pending_partials = e->partials;
@@ -876,7 +900,12 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.device);
   const int cap = e->cfg.decode_split_k == 0 ? 32 : std::min(e->cfg.decode_split_k, 32);
-  if (bucket <= 256 && cap > 1) {
+  if (bucket <= 256 && cap > 1 && e->cfg.decode_reduce == 2) {
+    p.cl_qkv = pick_cluster(3 * e->d, e->d, sms);
+    p.cl_o = pick_cluster(e->d, e->d, sms);
+    p.cl_fc = pick_cluster(4 * e->d, e->d, sms);
+    p.cl_p = pick_cluster(e->d, 4 * e->d, sms);
+  } else if (bucket <= 256 && cap > 1) {
     p.split_o = pick_split(e->d, e->d, sms, cap);
     p.split_p = pick_split(e->d, 4 * e->d, sms, cap);
     p.split_qkv = pick_split(3 * e->d, e->d, sms, cap);
@@ -1078,7 +1107,8 @@ int b200llm_op_gemm(const void* act, const void* w, const float* bias, void* out
   g.k = k;
   g.ld_out = ld_out;
   g.epilogue = epilogue;
-  g.split_k = split_k;
+  g.split_k = split_k > 0 ? split_k : 1;
+  g.cluster_split = split_k < 0 ? -split_k : 0;  // negative split_k selects the cluster (DSMEM) reduction
   g.act_rows_alloc = tokens;
   g.force_orientation = orientation;
   g.pdl = 0;

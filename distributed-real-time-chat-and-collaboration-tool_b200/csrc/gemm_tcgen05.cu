@@ -479,6 +479,233 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   if (threadIdx.x == 64) B200_TRACE(8);
 }
 
+
+// ---------------------------------------------------------------------------------------
+// Cluster split-K variant (swap-AB orientation, one 128-feature tile per cluster).
+//
+// Decode GEMMs have only 6..40 weight tiles, far fewer than 148 SMs, and one SM can ingest only
+// ~56 B/clk through TMA, so K is split over the CTAs of a thread-block cluster: CTA `rank`
+// multiplies its K slice into TMEM, spills the fp32 partial tile to its own shared memory, and
+// after a cluster barrier CTA `rank` reduces token columns [rank*cpr, (rank+1)*cpr) of ALL ranks
+// through distributed shared memory (fixed rank order -> deterministic) and applies the final
+// epilogue (bias / gelu / residual). No global partial planes, no consumer-side reduction.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
+}
+__device__ __forceinline__ float4 ld_dsmem_f4(uint32_t local_addr, uint32_t rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(remote)
+               : "memory");
+  return v;
+}
+
+template <int BLOCK_N, int EPI>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_cluster_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    const KernelArgs args) {
+  using Cfg = TileCfg<BLOCK_N>;
+  const int kStages = args.stages;
+  constexpr int kChunk = (BLOCK_N >= 32) ? 32 : 16;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~static_cast<uintptr_t>(1023u));
+  uint8_t* ring = smem;
+  // barriers live after max(ring, staging) so the staging tile never overwrites them
+  const int ring_bytes = kStages * Cfg::kStageBytes;
+  const int stage_tile_bytes = BLOCK_N * kBlockM * 4;
+  const int body_bytes = ring_bytes > stage_tile_bytes ? ring_bytes : stage_tile_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + body_bytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full_bar = empty_bar + kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  float* stage_tile = reinterpret_cast<float*>(ring);  // [BLOCK_N tokens][128 features] fp32
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) B200_TRACE(0);
+  const uint32_t rank = cluster_ctarank();
+  const uint32_t csize = cluster_nctarank();
+  const int m_blk = blockIdx.x;
+  const int kb_begin = static_cast<int>(rank) * args.k_blocks_per_split;
+  int kb_end = kb_begin + args.k_blocks_per_split;
+  if (kb_end > args.k_blocks_total) kb_end = args.k_blocks_total;
+  const int num_kb = kb_end - kb_begin;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  if (threadIdx.x == 0) B200_TRACE(1);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // weights first (independent of the upstream kernel), activations after the dependency
+      const int pre = num_kb < kStages ? num_kb : kStages;
+      for (int it = 0; it < pre; ++it) {
+        uint8_t* sa = ring + it * Cfg::kStageBytes;
+        mbar_arrive_expect_tx(&full_bar[it], Cfg::kStageBytes);
+        tma_load_2d(sa, &map_a, &full_bar[it], (kb_begin + it) * kBlockK, m_blk * kBlockM, kEvictFirst);
+      }
+      pdl_wait();
+      for (int it = 0; it < pre; ++it) {
+        uint8_t* sb = ring + it * Cfg::kStageBytes + Cfg::kABytes;
+        tma_load_2d(sb, &map_b, &full_bar[it], (kb_begin + it) * kBlockK, 0, kEvictLast);
+      }
+      for (int it = pre; it < num_kb; ++it) {
+        const int stage = it % kStages;
+        const uint32_t phase = static_cast<uint32_t>(it / kStages) & 1u;
+        mbar_wait(&empty_bar[stage], phase ^ 1u);
+        uint8_t* sa = ring + stage * Cfg::kStageBytes;
+        mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        tma_load_2d(sa, &map_a, &full_bar[stage], (kb_begin + it) * kBlockK, m_blk * kBlockM, kEvictFirst);
+        tma_load_2d(sa + Cfg::kABytes, &map_b, &full_bar[stage], (kb_begin + it) * kBlockK, 0, kEvictLast);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int stage = kb % kStages;
+        const uint32_t phase = static_cast<uint32_t>(kb / kStages) & 1u;
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(ring + stage * Cfg::kStageBytes);
+        const uint64_t desc_a = umma_desc_k_sw128(sa);
+        const uint64_t desc_b = umma_desc_k_sw128(sa + Cfg::kABytes);
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          umma_bf16_ss(tmem_base, desc_a + static_cast<uint64_t>(k * 2), desc_b + static_cast<uint64_t>(k * 2),
+                       idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[stage]);
+      }
+      umma_commit(tmem_full_bar);
+      B200_TRACE(5);
+    }
+  } else if (warp >= 4) {
+    // phase A: this CTA's partial tile TMEM -> own shared memory, [token][feature] fp32
+    const int q = warp - 4;
+    mbar_wait(tmem_full_bar, 0);
+    if (threadIdx.x == 128) B200_TRACE(6);
+    tc_fence_after();
+    const int f_local = q * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BLOCK_N; c0 += kChunk) {
+      uint32_t r[32];
+      tmem_ld_cols<kChunk>(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0), r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < kChunk; ++j) {
+        stage_tile[(c0 + j) * kBlockM + f_local] = (num_kb > 0) ? __uint_as_float(r[j]) : 0.f;
+      }
+    }
+    tc_fence_before();
+    if (threadIdx.x == 128) B200_TRACE(9);
+  }
+
+  cluster_sync_all();  // every rank's partial tile is visible cluster-wide
+  if (threadIdx.x == 128) B200_TRACE(10);
+
+  if (warp >= 4) {
+    // phase B: reduce my token columns over all ranks through DSMEM and finish the epilogue
+    const int q = warp - 4;
+    const int cpr = (BLOCK_N + static_cast<int>(csize) - 1) / static_cast<int>(csize);
+    const int t_begin = static_cast<int>(rank) * cpr;
+    int t_end = t_begin + cpr;
+    if (t_end > BLOCK_N) t_end = BLOCK_N;
+    if (t_end > args.b_rows) t_end = args.b_rows;
+    const int fb = m_blk * kBlockM + lane * 4;  // first of this lane's 4 features
+    const bool f_ok = fb < args.a_rows;         // a_rows % 4 == 0 is checked on the host
+    float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (f_ok && args.bias != nullptr) bias4 = __ldg(reinterpret_cast<const float4*>(args.bias + fb));
+    const uint32_t tile_addr = smem_u32(stage_tile);
+    pdl_wait();
+    for (int t = t_begin + q; t < t_end; t += 4) {
+      const uint32_t laddr = tile_addr + static_cast<uint32_t>((t * kBlockM + lane * 4) * 4);
+      // all remote loads of this column in flight together; summed in rank order (deterministic)
+      float4 v[8];
+#pragma unroll
+      for (uint32_t s = 0; s < 8; ++s) {
+        v[s] = (s < csize) ? ld_dsmem_f4(laddr, s) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      float4 acc = v[0];
+#pragma unroll
+      for (uint32_t s = 1; s < 8; ++s) {
+        acc.x += v[s].x;
+        acc.y += v[s].y;
+        acc.z += v[s].z;
+        acc.w += v[s].w;
+      }
+      if (!f_ok) continue;
+      acc.x += bias4.x;
+      acc.y += bias4.y;
+      acc.z += bias4.z;
+      acc.w += bias4.w;
+      const size_t idx = static_cast<size_t>(t) * args.ld_out + fb;
+      if (EPI == kEpiBiasBf16 || EPI == kEpiBiasGeluBf16) {
+        if (EPI == kEpiBiasGeluBf16) {
+          acc.x = gelu_new(acc.x);
+          acc.y = gelu_new(acc.y);
+          acc.z = gelu_new(acc.z);
+          acc.w = gelu_new(acc.w);
+        }
+        uint2 pk;
+        pk.x = pack_bf16x2(acc.x, acc.y);
+        pk.y = pack_bf16x2(acc.z, acc.w);
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(args.out) + idx) = pk;
+      } else {  // kEpiBiasResidF32
+        float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(args.out) + idx);
+        const float4 old = *o;
+        *o = make_float4(old.x + acc.x, old.y + acc.y, old.z + acc.z, old.w + acc.w);
+      }
+    }
+  }
+
+  if (threadIdx.x == 128) B200_TRACE(7);
+  cluster_sync_all();  // nobody leaves while a peer may still read its shared memory
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+  if (threadIdx.x == 64) B200_TRACE(8);
+}
+
 // ---------------------------------------------------------------------------------------
 // Host side: tensor maps + dispatch
 // ---------------------------------------------------------------------------------------
@@ -646,6 +873,72 @@ int dispatch_epi(const GemmArgs& g, cudaStream_t stream) {
   }
 }
 
+
+template <int BLOCK_N, int EPI>
+int launch_cluster(const GemmArgs& g, cudaStream_t stream) {
+  using Cfg = TileCfg<BLOCK_N>;
+  CUtensorMap map_a, map_b;
+  const int act_rows = g.act_rows_alloc > 0 ? g.act_rows_alloc : g.tokens;
+  B200_PROPAGATE(get_tensor_map(g.w, g.features, g.k, kBlockM, &map_a));
+  B200_PROPAGATE(get_tensor_map(g.act, act_rows, g.k, BLOCK_N, &map_b));
+  const int split = g.cluster_split;
+  KernelArgs ka = {};
+  ka.bias = g.bias;
+  ka.out = g.out;
+  ka.a_rows = g.features;
+  ka.b_rows = g.tokens;
+  ka.k_blocks_total = g.k / kBlockK;
+  ka.k_blocks_per_split = ka.k_blocks_total / split;
+  ka.ld_out = g.ld_out;
+  ka.tokens = g.tokens;
+  int stages = ka.k_blocks_per_split < Cfg::kMaxStages ? ka.k_blocks_per_split : Cfg::kMaxStages;
+  if (stages < 2) stages = 2;
+  ka.stages = stages;
+  const int ring_bytes = stages * Cfg::kStageBytes;
+  const int tile_bytes = BLOCK_N * kBlockM * 4;
+  const int smem_bytes = (ring_bytes > tile_bytes ? ring_bytes : tile_bytes) + 1024 + 256;
+  const int max_bytes = (Cfg::kMaxStages * Cfg::kStageBytes > tile_bytes ? Cfg::kMaxStages * Cfg::kStageBytes : tile_bytes) + 1024 + 256;
+
+  auto kernel = gemm_cluster_kernel<BLOCK_N, EPI>;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_bytes));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((g.features + kBlockM - 1) / kBlockM, split, 1);
+  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[2];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = 1;
+  attrs[0].val.clusterDim.y = split;
+  attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[1].val.programmaticStreamSerializationAllowed = g.pdl ? 1 : 0;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 2;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, ka));
+  return kOk;
+}
+
+template <int BLOCK_N>
+int dispatch_cluster(const GemmArgs& g, cudaStream_t stream) {
+  switch (g.epilogue) {
+    case kEpiBiasBf16:
+      return launch_cluster<BLOCK_N, kEpiBiasBf16>(g, stream);
+    case kEpiBiasGeluBf16:
+      return launch_cluster<BLOCK_N, kEpiBiasGeluBf16>(g, stream);
+    case kEpiBiasResidF32:
+      return launch_cluster<BLOCK_N, kEpiBiasResidF32>(g, stream);
+    default:
+      return fail(kErrUnsupported, "gemm: the cluster split-K path supports the bias / gelu / residual epilogues");
+  }
+}
+
 }  // namespace
 
 void gemm_clear_tensor_map_cache() {
@@ -663,6 +956,19 @@ int gemm_bf16(const GemmArgs& g, cudaStream_t stream) {
                  "gemm: split_k > 1 requires the partial epilogue");
   B200_CHECK_ARG(g.split_k <= 1 || (g.k / kBlockK) % g.split_k == 0,
                  "gemm: split_k must divide the number of 64-wide k blocks");
+
+  if (g.cluster_split > 1) {
+    // split-K across a thread-block cluster with an on-chip (DSMEM) reduction
+    B200_CHECK_ARG(g.cluster_split <= 8, "gemm: cluster split-K is limited to the portable cluster size 8");
+    B200_CHECK_ARG((g.k / kBlockK) % g.cluster_split == 0, "gemm: cluster_split must divide the k blocks");
+    B200_CHECK_ARG(g.tokens <= 256 && g.features % 4 == 0 && g.ld_out % 4 == 0 && g.split_k <= 1,
+                   "gemm: cluster split-K needs <= 256 tokens and 4-aligned features");
+    if (g.tokens <= 16) return dispatch_cluster<16>(g, stream);
+    if (g.tokens <= 32) return dispatch_cluster<32>(g, stream);
+    if (g.tokens <= 64) return dispatch_cluster<64>(g, stream);
+    if (g.tokens <= 128) return dispatch_cluster<128>(g, stream);
+    return dispatch_cluster<256>(g, stream);
+  }
 
   bool trans;
   if (g.force_orientation == 0) {

@@ -41,6 +41,9 @@ struct GemmArgs {
   float* eos_logit;
   int ld_amax;
   int eos_id;
+  // > 1: swap-AB split-K over a thread-block cluster of this many CTAs, reduced through
+  // distributed shared memory inside the kernel (deterministic; final epilogue applied)
+  int cluster_split;
 };
 
 // Enqueue one GEMM on `stream`. Returns 0 or an error code (see common.cuh Status).

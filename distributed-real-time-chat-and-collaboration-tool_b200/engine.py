@@ -54,7 +54,7 @@ class Engine:
                  max_seqs: int = 64, max_seq_len: int = 256, max_batch_tokens: int = 8192,
                  max_new_tokens: int = 256, kv_pool_tokens: int = 0, use_cuda_graphs: bool = True,
                  use_pdl: bool = True, decode_split_k: int = 0, keep_logits: bool = False,
-                 pad_token_id: int | None = None):
+                 decode_reduce: int = 0, pad_token_id: int | None = None):
         blob = np.ascontiguousarray(weights_blob, dtype=np.float32).reshape(-1)
         self.shape = shape
         self.cfg = Config(
@@ -65,7 +65,7 @@ class Engine:
             max_seqs=max_seqs, max_seq_len=max_seq_len, max_batch_tokens=max_batch_tokens,
             max_new_tokens=max_new_tokens, kv_pool_tokens=kv_pool_tokens, device=device,
             use_cuda_graphs=int(use_cuda_graphs), use_pdl=int(use_pdl), decode_split_k=decode_split_k,
-            keep_logits=int(keep_logits))
+            keep_logits=int(keep_logits), decode_reduce=decode_reduce)
         expect = lib.b200llm_weight_blob_floats(C.byref(self.cfg))
         if blob.size != expect:
             raise ValueError(f"weight blob has {blob.size} floats, config needs {expect}")

@@ -72,6 +72,10 @@ typedef struct b200llm_config {
   int32_t decode_split_k;   /* 0 = auto; 1 = off; >1 = split-K factor cap for decode GEMMs */
   int32_t keep_logits;      /* 1 = decode steps also store the fp32 logits (greedy rows do not
                                need them: the LM-head GEMM fuses the argmax)                 */
+  int32_t decode_reduce;    /* how decode GEMMs combine their K splits: 0/1 = fp32 partial planes in L2
+                               reduced by the consumer kernel (default; measured faster);
+                               2 = inside the GEMM, over a thread-block cluster through distributed
+                               shared memory (fewer kernels, but DSMEM moves ~20 B/clk per SM)    */
 } b200llm_config;
 
 /* Number of fp32 values in the weight blob for `cfg` (layout below). */
@@ -175,7 +179,10 @@ int64_t b200llm_kernel_launches(const b200llm_engine* engine);
 
 /* out[token, feature] = sum_k act[token,k] * w[feature,k] (+ epilogue).  act [tokens,k] bf16,
  * w [features,k] bf16 (K-major), bias [features] fp32 or NULL. Conv1D: $TF/pytorch_utils.py:119-122.
- * orientation: -1 auto, 0 tokens on UMMA-M, 1 weights on UMMA-M (swap-AB, small batches). */
+ * orientation: -1 auto, 0 tokens on UMMA-M, 1 weights on UMMA-M (swap-AB, small batches).
+ * split_k: 1 = none; n > 1 = n partial planes (B200LLM_EPI_PARTIAL_F32 only, the consumer reduces);
+ *          -n = split K over a thread-block cluster of n CTAs (n <= 8) reduced on chip through
+ *          distributed shared memory, with the normal bias / gelu / residual epilogue. */
 int b200llm_op_gemm(const void* act_dev, const void* w_dev, const float* bias_dev, void* out_dev,
                     int32_t tokens, int32_t features, int32_t k, int32_t ld_out, int32_t epilogue,
                     int32_t split_k, int32_t orientation, void* stream);

@@ -16,7 +16,7 @@ int fail(int code, const std::string& m) { g_err = m; return code; }
 
 using namespace b200llm;
 
-static void run(const char* name, int tokens, int features, int k, int epi, int split) {
+static void run(const char* name, int tokens, int features, int k, int epi, int split, int cluster = 0) {
   __nv_bfloat16 *act, *w;
   float *bias, *out;
   cudaMalloc(&act, (size_t)256 * k * 2);
@@ -29,7 +29,7 @@ static void run(const char* name, int tokens, int features, int k, int epi, int 
   GemmArgs g = {};
   g.act = act; g.w = w; g.bias = bias; g.out = out; g.tokens = tokens; g.features = features; g.k = k;
   g.ld_out = features; g.epilogue = epi; g.split_k = split; g.act_rows_alloc = 256;
-  g.force_orientation = 1; g.pdl = 0;
+  g.force_orientation = 1; g.pdl = 0; g.cluster_split = cluster;
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   for (int i = 0; i < 3; ++i) {
@@ -67,5 +67,11 @@ int main() {
   run("fc 64x3072x768 split6", 64, 3072, 768, kEpiPartialF32, 6);
   run("proj2 64x768x3072 split24", 64, 768, 3072, kEpiPartialF32, 24);
   run("head 64x50257x768", 64, 50257, 768, kEpiF32, 1);
+  printf("-- cluster (DSMEM) split-K: ld0=staged in smem, ld1=after cluster barrier 1, epilogue end=before barrier 2\n");
+  run("qkv cluster6", 64, 2304, 768, kEpiBiasBf16, 1, 6);
+  run("proj cluster6", 64, 768, 768, kEpiBiasResidF32, 1, 6);
+  run("fc cluster6", 64, 3072, 768, kEpiBiasGeluBf16, 1, 6);
+  run("proj2 cluster8", 64, 768, 3072, kEpiBiasResidF32, 1, 8);
+  run("proj2 cluster4", 64, 768, 3072, kEpiBiasResidF32, 1, 4);
   return 0;
 }

@@ -28,9 +28,10 @@ prompts = rng.integers(0, shape.vocab_size - 1, size=(B, T), dtype=np.int32)
 stream = torch.cuda.Stream()
 chunk = max(1, min(B, 16384 // T))
 
-for graphs, pdl, split in [(False, False, 1), (True, False, 1), (True, False, 0), (True, True, 0), (False, True, 0)]:
+for graphs, pdl, split, reduce in [(True, False, 1, 0), (True, False, 0, 0), (True, True, 0, 0), (True, True, 0, 2)]:
     eng = E.Engine(shape, blob, max_seqs=B, max_seq_len=T + N, max_batch_tokens=min(B * T, 16384),
-                   max_new_tokens=N, use_cuda_graphs=graphs, use_pdl=pdl, decode_split_k=split)
+                   max_new_tokens=N, use_cuda_graphs=graphs, use_pdl=pdl, decode_split_k=split,
+                   decode_reduce=reduce)
     eng.set_stream(stream.cuda_stream)
     best = 1e9
     pf = 1e9
@@ -49,5 +50,5 @@ for graphs, pdl, split in [(False, False, 1), (True, False, 1), (True, False, 0)
         pf = min(pf, e0.elapsed_time(e1))
         for s in slots:
             eng.seq_free(s)
-    print(f"graphs={graphs!s:5} pdl={pdl!s:5} split={split}: decode {best * 1e3:8.1f} us/step   prefill {pf:7.3f} ms")
+    print(f"graphs={graphs!s:5} pdl={pdl!s:5} split={split} reduce={reduce}: decode {best * 1e3:8.1f} us/step   prefill {pf:7.3f} ms")
     eng.close()

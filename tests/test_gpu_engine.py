@@ -59,13 +59,15 @@ def test_tiny_model_all_position_logits(cuda):
     eng.close()
 
 
-@pytest.mark.parametrize("graphs,pdl,split", [(False, False, 1), (True, False, 0), (True, True, 0)])
-def test_small_greedy_generation_margin_aware(cuda, small_weights, graphs, pdl, split):
+@pytest.mark.parametrize("graphs,pdl,split,reduce", [(False, False, 1, 0), (True, False, 0, 0), (True, True, 0, 0),
+                                                     (True, True, 0, 2)])
+def test_small_greedy_generation_margin_aware(cuda, small_weights, graphs, pdl, split, reduce):
     B, T, N = 8, 64, 32
     ids = O.synthetic_prompts(B, T)
     ref_tok, ref_logits, margins = O.greedy_generate(O.SMALL, small_weights, ids, N, min_new_tokens=N)
     eng, E = _engine(O.SMALL, small_weights, max_seqs=16, max_seq_len=128, max_batch_tokens=1024,
-                     max_new_tokens=N, use_cuda_graphs=graphs, use_pdl=pdl, decode_split_k=split)
+                     max_new_tokens=N, use_cuda_graphs=graphs, use_pdl=pdl, decode_split_k=split,
+                     decode_reduce=reduce)
     sp = E.SamplingParams(max_new_tokens=N, min_new_tokens=N)
     got = np.array(eng.generate(ids.tolist(), sp))
     assert got.shape == (B, N)

@@ -101,6 +101,43 @@ def test_gemm_split_k_partials_then_layernorm(ops, cuda, split):
     assert (h.float() - ref_h).abs().max().item() <= 3e-2
 
 
+@pytest.mark.parametrize("tokens,features,k,cluster,epi", [
+    (64, 2304, 768, 6, "bias"),      # decode QKV: 18 tiles x cluster of 6
+    (64, 3072, 768, 6, "gelu"),      # MLP up
+    (64, 768, 768, 6, "resid"),      # attention out-proj, uneven token split (64 / 6)
+    (64, 768, 3072, 8, "resid"),     # MLP down: 6 k-blocks per CTA
+    (13, 1024, 1024, 4, "bias"),     # ragged batch on a 16-wide tile
+    (200, 1280, 5120, 8, "resid"),   # 256-wide tile, 10 k-blocks per CTA (> ring depth)
+    (1, 768, 768, 2, "gelu"),
+])
+def test_gemm_cluster_split_k_dsmem_reduce(ops, cuda, tokens, features, k, cluster, epi):
+    """K split over a thread-block cluster, reduced through distributed shared memory."""
+    act, w, bias = _gemm_inputs(tokens, features, k, cuda, seed=6)
+    ref = act.float() @ w.float().t() + bias
+    if epi == "resid":
+        resid = torch.randn(tokens, features, device=cuda)
+        out = resid.clone()
+        ops.gemm(act, w, bias, out, ops.EPI_BIAS_RESID_F32, split_k=-cluster, orientation=1)
+        ref = ref + resid
+        got = out
+    else:
+        out = torch.zeros(tokens, features, dtype=torch.bfloat16, device=cuda)
+        code = ops.EPI_BIAS_GELU_BF16 if epi == "gelu" else ops.EPI_BIAS_BF16
+        ops.gemm(act, w, bias, out, code, split_k=-cluster, orientation=1)
+        if epi == "gelu":
+            ref = gelu_new(ref)
+        got = out.float()
+    torch.cuda.synchronize()
+    scale = max(1.0, ref.abs().max().item())
+    assert (got - ref).abs().max().item() <= 1e-2 * scale
+    # deterministic: a second run is bit-identical
+    if epi != "resid":
+        out2 = torch.zeros_like(out)
+        ops.gemm(act, w, bias, out2, code, split_k=-cluster, orientation=1)
+        torch.cuda.synchronize()
+        assert torch.equal(out, out2)
+
+
 @pytest.mark.parametrize("rows,d", [(1, 768), (64, 768), (257, 1024), (33, 1280), (5, 128)])
 def test_layernorm(ops, cuda, rows, d):
     x = torch.randn(rows, d, device=cuda) * 3 + 0.7
