@@ -11,7 +11,10 @@ import re
 from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
-LIB_PATH = HERE / "libb200llm.so"
+import os as _os
+
+# B200LLM_LIB selects another build of the same library (profiling variants); default in-tree.
+LIB_PATH = Path(_os.environ["B200LLM_LIB"]) if _os.environ.get("B200LLM_LIB") else HERE / "libb200llm.so"
 HEADER_PATH = HERE.parent / "include" / "b200llm.h"
 
 

@@ -46,6 +46,18 @@ def _compile(src: Path, obj: Path) -> str:
     return log
 
 
+def build_trace_variant() -> Path:
+    """Profiling-only library with the kernels' clock64 milestone traces compiled in."""
+    out = HERE / "libb200llm_trace.so"
+    srcs = [str(CSRC / n) for n in SOURCES]
+    flags = [f for f in FLAGS if f not in ("-Xptxas", "-v")]
+    cmd = [NVCC, *flags, "-DB200_ATTN_TRACE", "-shared", "-o", str(out), *srcs, "-lcudart"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(r.stdout + r.stderr)
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
     BUILD.mkdir(exist_ok=True)
     headers = sorted(CSRC.glob("*.cuh")) + [HERE.parent / "include" / "b200llm.h"]
@@ -70,5 +82,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
 
 if __name__ == "__main__":
+    if "--trace" in sys.argv:
+        print(build_trace_variant())
+        sys.exit(0)
     lib = build(force="--force" in sys.argv, verbose="-v" in sys.argv)
     print(lib)

@@ -258,18 +258,85 @@ __device__ __forceinline__ void bf16x8_to_float(const uint4& v, float (&f)[8]) {
 constexpr int kDecUnroll = 3;
 constexpr int kScratchStride = kHeadDim + 2;  // o[64], m, l
 constexpr int kMaxSmemPages = 256;            // page ids staged in smem (4096 tokens)
+constexpr int kStageTokens = 128;             // cached tokens staged in smem per CTA (32 KB)
 
 struct KvBatch {
   uint4 k[kDecUnroll];
   uint4 v[kDecUnroll];
 };
 
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_wait_all() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+// Online-softmax update with N cached tokens at once: the N dot products, their shuffle
+// reductions and exponentials are independent, so one pass through the dependent chain
+// (max -> rescale -> accumulate) serves N tokens instead of one.
+template <int N>
+__device__ __forceinline__ void attend_tokens(Softmax8& acc, const float (&q)[8], const uint4 (&kraw)[N],
+                                              const uint4 (&vraw)[N], const bool (&valid)[N]) {
+  float s[N];
+#pragma unroll
+  for (int n = 0; n < N; ++n) {
+    float kf[8];
+    bf16x8_to_float(kraw[n], kf);
+    float d = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) d = fmaf(q[i], kf[i], d);
+    s[n] = d;
+  }
+#pragma unroll
+  for (int o = 1; o <= 4; o <<= 1) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) s[n] += __shfl_xor_sync(0xffffffffu, s[n], o);
+  }
+  float m = acc.m;
+#pragma unroll
+  for (int n = 0; n < N; ++n) m = valid[n] ? fmaxf(m, s[n]) : m;
+  if (m == -INFINITY) return;  // nothing valid yet (uniform within the 8-lane group)
+  const float f = (acc.m == -INFINITY) ? 0.f : exp2f(acc.m - m);
+  float p[N];
+  float psum = 0.f;
+#pragma unroll
+  for (int n = 0; n < N; ++n) {
+    p[n] = valid[n] ? exp2f(s[n] - m) : 0.f;
+    psum += p[n];
+  }
+  acc.l = acc.l * f + psum;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc.o[i] *= f;
+#pragma unroll
+  for (int n = 0; n < N; ++n) {
+    float vf[8];
+    bf16x8_to_float(vraw[n], vf);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc.o[i] = fmaf(p[n], vf[i], acc.o[i]);
+  }
+  acc.m = m;
+}
+
+// Ordering argument for everything this kernel does BEFORE griddepcontrol.wait.
+// In a decode step only the GEMM kernels signal launch_dependents before their own wait; every
+// other kernel (embed, LayerNorm, this one, gelu-reduce, select) signals after its wait has
+// returned, i.e. after its predecessor has completely finished. This kernel's predecessor is the
+// QKV GEMM, whose predecessor is a LayerNorm: by the time a CTA of this kernel runs at all, that
+// LayerNorm has passed its wait, so everything up to the kernel before it -- in particular the
+// previous step's selector (seq_len, finished) and the previous step's attention kernels (KV
+// positions < seq_len) -- is complete and visible. Only the QKV projection of THIS step is not.
+// So the whole cached KV stream is fetched before the wait and overlaps the QKV GEMM.
 __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   __shared__ float sm_o[4][kHeadDim];
   __shared__ float sm_ml[4][2];
   __shared__ int32_t sm_pages[kMaxSmemPages];
-  __shared__ __align__(16) float sm_q[kHeadDim];          // this token's q (pre-scaled)
+  __shared__ __align__(16) float sm_q[kHeadDim];              // this token's q (pre-scaled)
   __shared__ __align__(16) __nv_bfloat16 sm_kv[2][kHeadDim];  // this token's k, v (cache dtype)
+  __shared__ __align__(16) uint4 sm_k[kStageTokens][8];       // staged cached K rows
+  __shared__ __align__(16) uint4 sm_v[kStageTokens][8];       // staged cached V rows
 
   const int bh = blockIdx.x;
   const int b = bh / a.n_head;
@@ -282,15 +349,18 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   const int d = a.n_head * kHeadDim;
   B200_ATRACE(0);
 
-  // ---- before the grid dependency resolves: only data no kernel of a decode step writes ----
-  // (active set and page table are written by the host between steps, never by the step).
   const int slot = a.active_slots ? a.active_slots[b] : b;
-  const int32_t* pt = a.page_table + static_cast<size_t>(slot < 0 ? 0 : slot) * a.max_pages_per_seq;
-  const int n_stage = a.max_pages_per_seq < kMaxSmemPages ? a.max_pages_per_seq : kMaxSmemPages;
-  if (slot >= 0) {
-    for (int i = threadIdx.x; i < n_stage; i += blockDim.x) sm_pages[i] = pt[i];
+  if (slot < 0) {
+    pdl_wait();
+    pdl_launch_dependents();
+    return;
   }
-  // Each thread owns one or two of the 192 values (q|k|v x 64 dims) of this token's projection.
+  const int32_t* pt = a.page_table + static_cast<size_t>(slot) * a.max_pages_per_seq;
+  const int n_stage_pages = a.max_pages_per_seq < kMaxSmemPages ? a.max_pages_per_seq : kMaxSmemPages;
+  for (int i = threadIdx.x; i < n_stage_pages; i += blockDim.x) sm_pages[i] = pt[i];
+  const int pos = a.seq_len[slot];
+  const int ctx = pos + 1;
+  const bool fin = a.finished != nullptr && a.finished[slot] != 0;
   float rbias[2] = {0.f, 0.f};
   if (a.qkv_partials != nullptr) {
 #pragma unroll
@@ -301,100 +371,112 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   }
   __syncthreads();
 
-  // Speculative KV prefetch into L2. seq_len is written by the selector of the PREVIOUS step,
-  // so a read here (before the dependency wait) may be stale -- but a stale value is only ever
-  // smaller, positions below it are cached and immutable for the whole step, and a prefetch
-  // has no architectural effect. This overlaps the layer's KV stream from HBM with the QKV
-  // projection that runs before this kernel; the real loads below then hit L2.
-  if (slot >= 0) {
-    const int pos_spec = *reinterpret_cast<const volatile int32_t*>(a.seq_len + slot);
-    int chunk_s = (pos_spec + a.n_splits - 1) / a.n_splits;
-    chunk_s = ((chunk_s + kPageTokens - 1) / kPageTokens) * kPageTokens;
-    const int tb = split * chunk_s;
-    const int te = min(pos_spec, tb + chunk_s);
-    if (sub < 2) {  // lane 0 of the group prefetches the K row, lane 1 the V row (128 B each)
-      const __nv_bfloat16* pool = sub == 0 ? a.k_pool : a.v_pool;
-      for (int tpos = tb + grp; tpos < te; tpos += kPageTokens) {
-        const int pi = tpos / kPageTokens;
-        const int page = pi < n_stage ? sm_pages[pi] : pt[pi];
-        const size_t off =
-            ((static_cast<size_t>(page) * a.n_head + h) * kPageTokens + tpos % kPageTokens) * kHeadDim;
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(pool + off));
-      }
-    }
-  }
-
-  B200_ATRACE(1);
-  pdl_wait();
-  pdl_launch_dependents();
-  if (slot < 0) return;
-  const int pos = a.seq_len[slot];
-  const int ctx = pos + 1;
-  B200_ATRACE(2);
-  const bool fin = a.finished != nullptr && a.finished[slot] != 0;
-
   int chunk = (ctx + a.n_splits - 1) / a.n_splits;
   chunk = ((chunk + kPageTokens - 1) / kPageTokens) * kPageTokens;
   const int t_begin = split * chunk;
-  const int t_end = min(ctx, t_begin + chunk);
+  const int t_end = min(ctx, t_begin + chunk);        // may include `pos` (the new token)
+  const int t_cached_end = min(t_end, pos);           // cached tokens only
+  const int n_staged = max(0, min(t_cached_end - t_begin, kStageTokens));
 
-  // Cached K/V of positions < pos never change during this step: request the first batch now,
-  // so the HBM latency overlaps the reduction of this token's own q/k/v below.
   auto page_of = [&](int tpos) -> int {
     const int pi = tpos / kPageTokens;
-    return pi < n_stage ? sm_pages[pi] : pt[pi];
+    return pi < n_stage_pages ? sm_pages[pi] : pt[pi];
   };
+  auto kv_offset = [&](int tpos) -> size_t {
+    return ((static_cast<size_t>(page_of(tpos)) * a.n_head + h) * kPageTokens + tpos % kPageTokens) * kHeadDim;
+  };
+  // (1) the first kStageTokens cached tokens: global -> shared with cp.async, no registers held
+  for (int i = threadIdx.x; i < n_staged * 16; i += blockDim.x) {
+    const int tok = i >> 4, part = i & 15;
+    const size_t off = kv_offset(t_begin + tok) + (part & 7) * 8;
+    if (part < 8) {
+      cp_async_16(&sm_k[tok][part], a.k_pool + off);
+    } else {
+      cp_async_16(&sm_v[tok][part - 8], a.v_pool + off);
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  // (2) the remaining tokens stream through registers; their first batch is requested now and
+  //     the rest is pulled into L2
+  const int t_rest = t_begin + n_staged;
   auto load_batch = [&](int base, KvBatch& kb) {
 #pragma unroll
     for (int u = 0; u < kDecUnroll; ++u) {
       const int tpos = base + u * kPageTokens + grp;
       kb.k[u] = make_uint4(0u, 0u, 0u, 0u);
       kb.v[u] = make_uint4(0u, 0u, 0u, 0u);
-      if (tpos < t_end && tpos != pos) {
-        const size_t off =
-            ((static_cast<size_t>(page_of(tpos)) * a.n_head + h) * kPageTokens + tpos % kPageTokens) *
-                kHeadDim + sub * 8;
+      if (tpos < t_cached_end) {
+        const size_t off = kv_offset(tpos) + sub * 8;
         kb.k[u] = ld_nc_v4(a.k_pool + off);
         kb.v[u] = ld_nc_v4(a.v_pool + off);
       }
     }
   };
   KvBatch cur;
-  load_batch(t_begin, cur);
-  B200_ATRACE(3);
+  load_batch(t_rest, cur);
+  if (sub < 2) {
+    const __nv_bfloat16* pool = sub == 0 ? a.k_pool : a.v_pool;
+    for (int tpos = t_rest + kPageTokens * kDecUnroll + grp; tpos < t_cached_end; tpos += kPageTokens) {
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(pool + kv_offset(tpos)));
+    }
+  }
+
+  B200_ATRACE(1);
+  pdl_wait();
+  pdl_launch_dependents();
+  B200_ATRACE(2);
 
   // This token's q/k/v. With a split-K projection the CTA reduces the fp32 partial planes
   // (fixed summation order -> deterministic), adds the bias, keeps q in fp32 and rounds k/v to
   // the cache dtype; everyone then reads them from shared memory.
+  {
+    float val[2] = {rbias[0], rbias[1]};
+    if (a.qkv_partials != nullptr) {
+      const size_t plane = static_cast<size_t>(a.partial_rows) * 3 * d;
+      for (int s0 = 0; s0 < a.n_qkv_partials; s0 += 8) {
+        float x[2][8];
 #pragma unroll
-  for (int r = 0; r < 2; ++r) {
-    const int vi = threadIdx.x + r * 128;
-    if (vi < 3 * kHeadDim) {
-      const int part = vi >> 6, dim = vi & 63;
-      float val;
-      if (a.qkv_partials != nullptr) {
-        const float* src = a.qkv_partials + static_cast<size_t>(b) * 3 * d + part * d + h * kHeadDim + dim;
-        const size_t plane = static_cast<size_t>(a.partial_rows) * 3 * d;
-        val = rbias[r];
-        for (int s0 = 0; s0 < a.n_qkv_partials; s0 += 8) {
-          float x[8];
+        for (int r = 0; r < 2; ++r) {  // both values' planes requested before anything is summed
+          const int vi = threadIdx.x + r * 128;
+          const float* src = a.qkv_partials + static_cast<size_t>(b) * 3 * d + (vi >> 6) * d + h * kHeadDim + (vi & 63);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            x[j] = (s0 + j < a.n_qkv_partials) ? src[static_cast<size_t>(s0 + j) * plane] : 0.f;
+            x[r][j] = (vi < 3 * kHeadDim && s0 + j < a.n_qkv_partials)
+                          ? __ldcg(src + static_cast<size_t>(s0 + j) * plane)
+                          : 0.f;
           }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) val += x[j];
         }
-      } else {
-        val = __bfloat162float(a.qkv[static_cast<size_t>(b) * 3 * d + part * d + h * kHeadDim + dim]);
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) val[r] += x[r][j];
+        }
       }
-      if (part == 0) {
-        sm_q[dim] = val * kScaleLog2;
-      } else {
-        sm_kv[part - 1][dim] = __float2bfloat16(val);
+    } else {
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int vi = threadIdx.x + r * 128;
+        if (vi < 3 * kHeadDim) {
+          val[r] = __bfloat162float(a.qkv[static_cast<size_t>(b) * 3 * d + (vi >> 6) * d + h * kHeadDim + (vi & 63)]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int vi = threadIdx.x + r * 128;
+      if (vi < 3 * kHeadDim) {
+        const int part = vi >> 6, dim = vi & 63;
+        if (part == 0) {
+          sm_q[dim] = val[r] * kScaleLog2;
+        } else {
+          sm_kv[part - 1][dim] = __float2bfloat16(val[r]);
+        }
       }
     }
   }
+  B200_ATRACE(7);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  B200_ATRACE(8);
   __syncthreads();
   B200_ATRACE(4);
   float q[8];
@@ -407,10 +489,9 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   const uint4 k_new = *reinterpret_cast<const uint4*>(&sm_kv[0][sub * 8]);
   const uint4 v_new = *reinterpret_cast<const uint4*>(&sm_kv[1][sub * 8]);
 
-  if (split == 0 && !fin && warp == 0 && lane < 8) {
-    const size_t dst =
-        ((static_cast<size_t>(page_of(pos)) * a.n_head + h) * kPageTokens + pos % kPageTokens) * kHeadDim +
-        sub * 8;
+  // append this token to its page (the split that owns position `pos` does it)
+  if (pos >= t_begin && pos < t_end && !fin && warp == 0 && lane < 8) {
+    const size_t dst = kv_offset(pos) + sub * 8;
     *reinterpret_cast<uint4*>(a.k_pool + dst) = k_new;
     *reinterpret_cast<uint4*>(a.v_pool + dst) = v_new;
   }
@@ -421,34 +502,40 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
 #pragma unroll
   for (int i = 0; i < 8; ++i) acc.o[i] = 0.f;
 
-  for (int base = t_begin; base < t_end; base += kPageTokens * kDecUnroll) {
-    if (base != t_begin) load_batch(base, cur);  // the first batch is already in flight
+  // staged tokens (shared memory; a warp's 4 groups read 4 consecutive 128-byte rows), 4 at a time
+  // (trip count is CTA-uniform: the shuffles inside need every lane of the warp)
+  for (int it0 = 0; it0 < n_staged; it0 += 4 * kPageTokens) {
+    uint4 kk[4], vv[4];
+    bool ok[4];
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+      const int i = it0 + grp + n * kPageTokens;
+      ok[n] = i < n_staged;
+      const int ii = ok[n] ? i : 0;
+      kk[n] = sm_k[ii][sub];
+      vv[n] = sm_v[ii][sub];
+    }
+    attend_tokens<4>(acc, q, kk, vv, ok);
+  }
+  // streamed tokens; the new token rides along with the last batch
+  const bool own_new = pos >= t_begin && pos < t_end;
+  bool new_done = !own_new;
+  for (int base = t_rest; base < t_cached_end || !new_done; base += kPageTokens * kDecUnroll) {
+    if (base != t_rest && base < t_cached_end) load_batch(base, cur);
+    uint4 kk[kDecUnroll + 1], vv[kDecUnroll + 1];
+    bool ok[kDecUnroll + 1];
 #pragma unroll
     for (int u = 0; u < kDecUnroll; ++u) {
-      const int tpos = base + u * kPageTokens + grp;
-      const bool valid = tpos < t_end;
-      const uint4 kraw = (tpos == pos) ? k_new : cur.k[u];
-      const uint4 vraw = (tpos == pos) ? v_new : cur.v[u];
-      float kf[8];
-      bf16x8_to_float(kraw, kf);
-      float s = 0.f;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) s = fmaf(q[i], kf[i], s);
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      s += __shfl_xor_sync(0xffffffffu, s, 2);
-      s += __shfl_xor_sync(0xffffffffu, s, 4);
-      if (valid) {
-        float vf[8];
-        bf16x8_to_float(vraw, vf);
-        const float m = fmaxf(acc.m, s);
-        const float f = (acc.m == -INFINITY) ? 0.f : exp2f(acc.m - m);
-        const float p = exp2f(s - m);
-        acc.l = acc.l * f + p;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) acc.o[i] = fmaf(p, vf[i], acc.o[i] * f);
-        acc.m = m;
-      }
+      kk[u] = cur.k[u];
+      vv[u] = cur.v[u];
+      ok[u] = base + u * kPageTokens + grp < t_cached_end;
     }
+    const bool last = base + kPageTokens * kDecUnroll >= t_cached_end;
+    kk[kDecUnroll] = k_new;
+    vv[kDecUnroll] = v_new;
+    ok[kDecUnroll] = last && own_new && grp == 0;
+    attend_tokens<kDecUnroll + 1>(acc, q, kk, vv, ok);
+    if (last) new_done = true;
   }
 
   B200_ATRACE(5);
@@ -592,6 +679,15 @@ int decode_attention_noalloc(DecodeAttnArgs a, cudaStream_t stream) {
   a.scratch = scratch;
   return decode_attention(a, stream);
 }
+
+#ifdef B200_ATTN_TRACE
+}  // namespace b200llm
+// Profiling builds only: read CTA 0's milestone timestamps of the last decode_attn_kernel launch.
+extern "C" int b200llm_debug_attn_trace(unsigned long long* out16) {
+  return cudaMemcpyFromSymbol(out16, g_attn_trace, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : 2;
+}
+namespace b200llm {
+#endif
 
 int decode_attention(const DecodeAttnArgs& a, cudaStream_t stream) {
   B200_CHECK_ARG(a.batch > 0 && a.n_head > 0 && a.n_splits >= 1, "decode_attention: bad shape");

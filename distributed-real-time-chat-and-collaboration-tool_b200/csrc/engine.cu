@@ -478,7 +478,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
 
 int decode_step_launches(b200llm_engine* e, const StepPlan& p) {
   B200_PROPAGATE(count(e, embed_decode(e->wte_f32, e->wpe, e->active_dev, e->last_tok, e->seq_len,
-                                       e->x, p.rows, e->d, e->V, e->P, e->stream)));
+                                       e->x, p.rows, e->d, e->V, e->P, e->stream, p.pdl)));
   return run_stack(e, p);
 }
 

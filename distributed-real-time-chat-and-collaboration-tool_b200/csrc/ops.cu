@@ -433,12 +433,11 @@ int embed_tokens(const float* wte, const float* wpe, const int32_t* ids, const i
 
 int embed_decode(const float* wte, const float* wpe, const int32_t* active_slots,
                  const int32_t* last_tok, const int32_t* seq_len, float* x, int batch, int d,
-                 int vocab, int n_positions, cudaStream_t stream) {
+                 int vocab, int n_positions, cudaStream_t stream, int pdl) {
   B200_CHECK_ARG(batch > 0 && d % 4 == 0, "embed: bad shape");
-  embed_kernel<<<batch, 128, 0, stream>>>(wte, wpe, nullptr, nullptr, active_slots, last_tok,
-                                          seq_len, x, batch, d, vocab, n_positions);
-  B200_CUDA_OK(cudaGetLastError());
-  return kOk;
+  const int32_t* no_ids = nullptr;
+  return launch_pdl(embed_kernel, dim3(batch), dim3(128), stream, pdl, wte, wpe, no_ids, no_ids,
+                    active_slots, last_tok, seq_len, x, batch, d, vocab, n_positions);
 }
 
 int layernorm(const LayerNormArgs& a, cudaStream_t stream) {

@@ -20,7 +20,7 @@ int embed_tokens(const float* wte, const float* wpe, const int32_t* ids, const i
 // Decode form: row b reads its token and position from per-slot generation state.
 int embed_decode(const float* wte, const float* wpe, const int32_t* active_slots,
                  const int32_t* last_tok, const int32_t* seq_len, float* x, int batch, int d,
-                 int vocab, int n_positions, cudaStream_t stream);
+                 int vocab, int n_positions, cudaStream_t stream, int pdl = 0);
 
 struct LayerNormArgs {
   float* x;                  // [rows, d] fp32 residual stream (updated in place if partials)
