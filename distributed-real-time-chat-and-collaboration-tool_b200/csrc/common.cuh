@@ -109,6 +109,18 @@ __device__ __forceinline__ float gelu_new(float x) {
   return 0.5f * x * (1.0f + t);
 }
 
+// Same function through the hardware tanh (MUFU.TANH, rel. error 2^-11): used where the result is
+// rounded to bf16 anyway (2^-9) and the exact version made the epilogue issue-bound.
+__device__ __forceinline__ float gelu_new_fast(float x) {
+  const float k0 = 0.7978845608028654f;
+  const float k1 = 0.044715f * 0.7978845608028654f;
+  const float u = x * fmaf(k1, x * x, k0);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  const float hx = 0.5f * x;
+  return fmaf(hx, t, hx);
+}
+
 // Streaming 16-byte global load that does not allocate in L1 (KV pages, weights read once).
 __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
   uint4 r;

@@ -103,10 +103,17 @@ __device__ __forceinline__ void tmem_ld_cols<16>(uint32_t taddr, uint32_t (&r)[3
       : "memory");
 }
 
-template <int BLOCK_N, int EPI, bool TRANS>
+// TMA_EPI (tokens-on-M orientation only): the epilogue stages 128-row x 128-byte boxes of the
+// output tile in shared memory (SWIZZLE_128B) and hands them to the TMA store unit --
+// cp.async.bulk.tensor for bf16 outputs, cp.reduce.async.bulk.tensor ... .add for the fp32
+// residual stream (x += tile, performed in L2). Direct per-thread stores from a 128-lane TMEM
+// tile hit 32 different cache lines per instruction and made the prefill GEMMs epilogue-bound.
+constexpr int kEpiBoxBytes = kBlockM * 128;  // one staging box: 128 rows x 128 B
+
+template <int BLOCK_N, int EPI, bool TRANS, bool TMA_EPI>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-            const KernelArgs args) {
+            const __grid_constant__ CUtensorMap map_out, const KernelArgs args) {
   using Cfg = TileCfg<BLOCK_N>;
   const int kStages = args.stages;
   constexpr int kChunk = (BLOCK_N >= 32) ? 32 : 16;  // columns per tcgen05.ld
@@ -116,7 +123,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   uint8_t* smem = reinterpret_cast<uint8_t*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~static_cast<uintptr_t>(1023u));
   uint8_t* ring = smem;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint8_t* epi_stage = smem + kStages * Cfg::kStageBytes;  // 2 boxes, 1024 B aligned (TMA_EPI only)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_stage + (TMA_EPI ? 2 * kEpiBoxBytes : 0));
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full_bar = empty_bar + kStages;
   uint64_t* tmem_empty_bar = tmem_full_bar + kAccumStages;
@@ -257,6 +265,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     const int q = warp - 4;  // == warp % 4: TMEM lane quarter this warp may access
     int astage = 0;
     uint32_t aphase = 0;
+    int epi_box = 0;  // staging-buffer rotation (TMA_EPI)
     pdl_wait();  // residual / output buffers may be read by the upstream kernel
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile % num_m_blocks;
@@ -273,6 +282,91 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         bias_lane = args.bias[a_row];
       }
 
+      if constexpr (TMA_EPI) {
+        // ---- staged epilogue: TMEM -> registers -> swizzled smem box -> TMA store / reduce-add
+        constexpr bool kF32Out = (EPI == kEpiBiasResidF32);
+        constexpr int kBoxCols = kF32Out ? 32 : 64;  // 128 bytes per row either way
+        const int row_in_tile = q * 32 + lane;
+        const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BLOCK_N; c0 += kBoxCols) {
+          const int f_box = n_blk * BLOCK_N + c0;
+          if (f_box >= args.b_rows) break;  // uniform across the epilogue warps
+          uint8_t* box = epi_stage + (epi_box & 1) * kEpiBoxBytes;
+          // the TMA store issued two boxes ago must have finished reading this buffer
+          if (threadIdx.x == 128) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          uint8_t* row_ptr = box + row_in_tile * 128;
+#pragma unroll
+          for (int cc = 0; cc < kBoxCols; cc += 32) {
+            uint32_t r[32];
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                   static_cast<uint32_t>(astage * BLOCK_N + c0 + cc);
+            tmem_ld_cols<32>(taddr, r);
+            tmem_ld_wait();
+            if (threadIdx.x == 128 && c0 == 0 && cc == 0) B200_TRACE(9);
+            const int f0 = f_box + cc;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              float v[8];
+              float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+              if (args.bias != nullptr && f0 + j + 7 < args.b_rows) {
+                b0 = __ldg(reinterpret_cast<const float4*>(args.bias + f0 + j));
+                b1 = __ldg(reinterpret_cast<const float4*>(args.bias + f0 + j + 4));
+              }
+              v[0] = __uint_as_float(r[j + 0]) + b0.x;
+              v[1] = __uint_as_float(r[j + 1]) + b0.y;
+              v[2] = __uint_as_float(r[j + 2]) + b0.z;
+              v[3] = __uint_as_float(r[j + 3]) + b0.w;
+              v[4] = __uint_as_float(r[j + 4]) + b1.x;
+              v[5] = __uint_as_float(r[j + 5]) + b1.y;
+              v[6] = __uint_as_float(r[j + 6]) + b1.z;
+              v[7] = __uint_as_float(r[j + 7]) + b1.w;
+              if (EPI == kEpiBiasGeluBf16) {
+#pragma unroll
+                for (int t = 0; t < 8; ++t) v[t] = gelu_new_fast(v[t]);
+              }
+              if (kF32Out) {
+                // 8 floats = two 16-byte chunks of the 128-byte row (chunk index = col / 4)
+                const uint32_t ch = static_cast<uint32_t>((cc + j) >> 2);
+                *reinterpret_cast<float4*>(row_ptr + (((ch + 0) ^ sw) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4*>(row_ptr + (((ch + 1) ^ sw) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
+              } else {
+                // 8 bf16 = one 16-byte chunk (chunk index = col / 8)
+                const uint32_t ch = static_cast<uint32_t>((cc + j) >> 3);
+                uint4 pk;
+                pk.x = pack_bf16x2(v[0], v[1]);
+                pk.y = pack_bf16x2(v[2], v[3]);
+                pk.z = pack_bf16x2(v[4], v[5]);
+                pk.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(row_ptr + ((ch ^ sw) << 4)) = pk;
+              }
+            }
+          }
+          fence_proxy_async();  // make the generic-proxy smem writes visible to the TMA unit
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (threadIdx.x == 128) {
+            const uint64_t desc = reinterpret_cast<uint64_t>(&map_out);
+            const uint32_t src = smem_u32(box);
+            const int crd0 = f_box, crd1 = m_blk * kBlockM;
+            if (kF32Out) {
+              asm volatile(
+                  "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];"
+                  :
+                  : "l"(desc), "r"(src), "r"(crd0), "r"(crd1)
+                  : "memory");
+            } else {
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                           :
+                           : "l"(desc), "r"(src), "r"(crd0), "r"(crd1)
+                           : "memory");
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          ++epi_box;
+        }
+        if (threadIdx.x == 128) B200_TRACE(7);
+      } else {
 #pragma unroll 1
       for (int c0 = 0; c0 < BLOCK_N; c0 += kChunk) {
         uint32_t r[32];
@@ -459,15 +553,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           }
         }
       }
+      }  // !TMA_EPI
       // All TMEM reads of this accumulator stage are complete (tcgen05.wait::ld above).
       tc_fence_before();
-      if (threadIdx.x == 128) B200_TRACE(7);
+      if (!TMA_EPI && threadIdx.x == 128) B200_TRACE(7);
       mbar_arrive(&tmem_empty_bar[astage]);
       if (++astage == kAccumStages) {
         astage = 0;
         aphase ^= 1u;
       }
     }
+    // every bulk store / reduction of this CTA must be complete before it exits
+    if (TMA_EPI && threadIdx.x == 128) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    (void)epi_box;
   }
 
   tc_fence_before();
@@ -729,7 +827,7 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-using MapKey = std::tuple<const void*, int, int, int>;  // ptr, rows, cols, box_rows
+using MapKey = std::tuple<const void*, int, int, int, int>;  // ptr, rows, cols, box_rows, elem bytes
 std::map<MapKey, CUtensorMap>& map_cache() {
   static std::map<MapKey, CUtensorMap> cache;
   return cache;
@@ -740,9 +838,11 @@ std::mutex& map_mutex() {
 }
 
 // Row-major bf16 [rows, cols] matrix; box = [box_rows, 64 cols] with 128 B swizzle.
-int get_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+// elem_bytes 2: bf16 operand / output (box 64 columns); 4: fp32 output (box 32 columns). Either
+// way a box row is 128 bytes, the SWIZZLE_128B span.
+int get_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out, int elem_bytes = 2) {
   std::lock_guard<std::mutex> lock(map_mutex());
-  MapKey key{ptr, rows, cols, box_rows};
+  MapKey key{ptr, rows, cols, box_rows, elem_bytes};
   auto it = map_cache().find(key);
   if (it != map_cache().end()) {
     *out = it->second;
@@ -755,10 +855,11 @@ int get_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMa
   }
   CUtensorMap map;
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
-  cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 2};
-  cuuint32_t box[2] = {static_cast<cuuint32_t>(kBlockK), static_cast<cuuint32_t>(box_rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * elem_bytes};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / elem_bytes), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t elem_strides[2] = {1, 1};
-  CUresult r = encode(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
+  CUresult r = encode(&map, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                      2, const_cast<void*>(ptr), dims,
                       strides, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE,
                       CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -781,7 +882,7 @@ int num_sms() {
   return n;
 }
 
-template <int BLOCK_N, int EPI, bool TRANS>
+template <int BLOCK_N, int EPI, bool TRANS, bool TMA_EPI = false>
 int launch(const GemmArgs& g, cudaStream_t stream) {
   using Cfg = TileCfg<BLOCK_N>;
   const int a_rows = TRANS ? g.features : g.tokens;
@@ -792,9 +893,15 @@ int launch(const GemmArgs& g, cudaStream_t stream) {
   const int a_rows_map = TRANS ? g.features : act_rows;
   const int b_rows_map = TRANS ? act_rows : g.features;
 
-  CUtensorMap map_a, map_b;
+  CUtensorMap map_a, map_b, map_out;
   B200_PROPAGATE(get_tensor_map(a_ptr, a_rows_map, g.k, kBlockM, &map_a));
   B200_PROPAGATE(get_tensor_map(b_ptr, b_rows_map, g.k, BLOCK_N, &map_b));
+  if (TMA_EPI) {
+    B200_PROPAGATE(get_tensor_map(g.out, g.tokens, g.ld_out, kBlockM, &map_out,
+                                  EPI == kEpiBiasResidF32 ? 4 : 2));
+  } else {
+    map_out = map_a;  // unused
+  }
 
   KernelArgs ka;
   ka.bias = g.bias;
@@ -825,32 +932,52 @@ int launch(const GemmArgs& g, cudaStream_t stream) {
   if (stages < 2) stages = 2;
   ka.stages = stages;
 
-  auto kernel = gemm_kernel<BLOCK_N, EPI, TRANS>;
+  auto kernel = gemm_kernel<BLOCK_N, EPI, TRANS, TMA_EPI>;
+  constexpr int kEpiBytes = TMA_EPI ? 2 * kEpiBoxBytes : 0;
   // the opt-in shared-memory limit is a per-device function attribute
   static bool attr_set[64] = {};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      Cfg::smem_bytes(Cfg::kMaxStages)));
+                                      Cfg::smem_bytes(Cfg::kMaxStages) + kEpiBytes));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid_x, split, 1);
   cfg.blockDim = dim3(kThreads, 1, 1);
-  cfg.dynamicSmemBytes = Cfg::smem_bytes(stages);
+  cfg.dynamicSmemBytes = Cfg::smem_bytes(stages) + kEpiBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attrs[1];
   attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attrs[0].val.programmaticStreamSerializationAllowed = g.pdl ? 1 : 0;
   cfg.attrs = attrs;
   cfg.numAttrs = 1;
-  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, ka));
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, map_out, ka));
   return kOk;
 }
 
 template <int BLOCK_N, bool TRANS>
 int dispatch_epi(const GemmArgs& g, cudaStream_t stream) {
+  if constexpr (!TRANS) {
+    // staged TMA-store epilogue when the output satisfies TMA's alignment rules
+    const int eb = g.epilogue == kEpiBiasResidF32 ? 4 : 2;
+    const bool tma_ok = (reinterpret_cast<uintptr_t>(g.out) & 15u) == 0 &&
+                        (static_cast<size_t>(g.ld_out) * eb) % 16 == 0 && g.features % 8 == 0 &&
+                        (g.bias == nullptr || (reinterpret_cast<uintptr_t>(g.bias) & 15u) == 0);
+    if (tma_ok) {
+      switch (g.epilogue) {
+        case kEpiBiasBf16:
+          return launch<BLOCK_N, kEpiBiasBf16, false, true>(g, stream);
+        case kEpiBiasGeluBf16:
+          return launch<BLOCK_N, kEpiBiasGeluBf16, false, true>(g, stream);
+        case kEpiBiasResidF32:
+          return launch<BLOCK_N, kEpiBiasResidF32, false, true>(g, stream);
+        default:
+          break;
+      }
+    }
+  }
   switch (g.epilogue) {
     case kEpiBiasBf16:
       return launch<BLOCK_N, kEpiBiasBf16, TRANS>(g, stream);

@@ -16,20 +16,21 @@ int fail(int code, const std::string& m) { g_err = m; return code; }
 
 using namespace b200llm;
 
-static void run(const char* name, int tokens, int features, int k, int epi, int split, int cluster = 0) {
+static void run(const char* name, int tokens, int features, int k, int epi, int split, int cluster = 0, int orient = 1) {
   __nv_bfloat16 *act, *w;
   float *bias, *out;
-  cudaMalloc(&act, (size_t)256 * k * 2);
+  const int act_rows = tokens > 256 ? tokens : 256;
+  cudaMalloc(&act, (size_t)act_rows * k * 2);
   cudaMalloc(&w, (size_t)features * k * 2);
   cudaMalloc(&bias, features * 4);
-  cudaMalloc(&out, (size_t)32 * 256 * features * 4);
-  cudaMemset(act, 0, (size_t)256 * k * 2);
+  cudaMalloc(&out, (size_t)(tokens > 256 ? tokens : 32 * 256) * features * 4);
+  cudaMemset(act, 0, (size_t)act_rows * k * 2);
   cudaMemset(w, 0, (size_t)features * k * 2);
   cudaMemset(bias, 0, features * 4);
   GemmArgs g = {};
   g.act = act; g.w = w; g.bias = bias; g.out = out; g.tokens = tokens; g.features = features; g.k = k;
-  g.ld_out = features; g.epilogue = epi; g.split_k = split; g.act_rows_alloc = 256;
-  g.force_orientation = 1; g.pdl = 0; g.cluster_split = cluster;
+  g.ld_out = features; g.epilogue = epi; g.split_k = split; g.act_rows_alloc = act_rows;
+  g.force_orientation = orient; g.pdl = 0; g.cluster_split = cluster;
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   for (int i = 0; i < 3; ++i) {
@@ -55,7 +56,8 @@ static void run(const char* name, int tokens, int features, int k, int epi, int 
   cudaEventRecord(e1);
   cudaDeviceSynchronize();
   cudaEventElapsedTime(&ms, e0, e1);
-  printf("%-28s back-to-back avg %.2f us\n", name, ms * 1e3 / 20);
+  printf("%-28s back-to-back avg %.2f us  (%.0f TFLOP/s)\n", name, ms * 1e3 / 20,
+         2.0 * tokens * features * k / (ms * 1e-3 / 20) / 1e12);
   cudaFree(act); cudaFree(w); cudaFree(bias); cudaFree(out); cudaFree(flush);
 }
 
@@ -67,6 +69,11 @@ int main() {
   run("fc 64x3072x768 split6", 64, 3072, 768, kEpiPartialF32, 6);
   run("proj2 64x768x3072 split24", 64, 768, 3072, kEpiPartialF32, 24);
   run("head 64x50257x768", 64, 50257, 768, kEpiF32, 1);
+  printf("-- prefill orientation, 8192 tokens (first tile of CTA 0; flops in TF/s from back-to-back)\n");
+  run("pf qkv 8192x2304x768", 8192, 2304, 768, kEpiBiasBf16, 1, 0, 0);
+  run("pf fc 8192x3072x768 gelu", 8192, 3072, 768, kEpiBiasGeluBf16, 1, 0, 0);
+  run("pf proj 8192x768x768 resid", 8192, 768, 768, kEpiBiasResidF32, 1, 0, 0);
+  run("pf proj2 8192x768x3072 resid", 8192, 768, 3072, kEpiBiasResidF32, 1, 0, 0);
   printf("-- cluster (DSMEM) split-K: ld0=staged in smem, ld1=after cluster barrier 1, epilogue end=before barrier 2\n");
   run("qkv cluster6", 64, 2304, 768, kEpiBiasBf16, 1, 6);
   run("proj cluster6", 64, 768, 768, kEpiBiasResidF32, 1, 6);
