@@ -385,41 +385,76 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           // the 32 results leave as one coalesced store. EOS is excluded from the candidates
           // and reported separately so the selector can apply min_new_tokens exactly.
           const int feature = a_row;
-          float keep_v = -INFINITY;
-          int keep_i = 0x7fffffff;
+          const int n_valid = args.b_rows - b_row0;  // token columns of this chunk that exist
+          float v[kChunk];
 #pragma unroll
           for (int j = 0; j < kChunk; ++j) {
-            const int token = b_row0 + j;
-            float v = a_ok ? __uint_as_float(r[j]) : -INFINITY;
-            int idx = feature;
-            if (a_ok && token < args.b_rows) {
-              if (args.out != nullptr) {
-                reinterpret_cast<float*>(args.out)[static_cast<size_t>(token) * args.ld_out + feature] = v;
-              }
-              if (feature == args.eos_id) {
-                args.eos_logit[token] = v;
-                v = -INFINITY;
-              }
-            }
+            v[j] = a_ok ? __uint_as_float(r[j]) : -INFINITY;
+          }
+          if (a_ok && args.out != nullptr) {
+            float* o = reinterpret_cast<float*>(args.out) + static_cast<size_t>(b_row0) * args.ld_out + feature;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-              const float ov = __shfl_xor_sync(0xffffffffu, v, o);
-              const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
-              if (ov > v || (ov == v && oi < idx)) {
-                v = ov;
-                idx = oi;
-              }
-            }
-            if (lane == j) {
-              keep_v = v;
-              keep_i = idx;
+            for (int j = 0; j < kChunk; ++j) {
+              if (j < n_valid) *o = v[j];
+              o += args.ld_out;
             }
           }
-          const int token = b_row0 + lane;
-          if (lane < kChunk && token < args.b_rows) {
+          if (a_ok && feature == args.eos_id) {
+#pragma unroll
+            for (int j = 0; j < kChunk; ++j) {
+              if (j < n_valid) args.eos_logit[b_row0 + j] = v[j];
+              v[j] = -INFINITY;
+            }
+          }
+          // Butterfly transpose-reduce over the warp's 32 vocabulary entries: at each level a
+          // lane keeps half of its columns and trades the other half with lane^offset, so 31
+          // (value, index) exchanges finish all kChunk columns and lane j ends with column j.
+          int idx[kChunk / 2];
+          {
+            constexpr int n = kChunk / 2;
+            const bool upper = (lane & n) != 0;  // offset == n at the first level (kChunk 32 or 16)
+#pragma unroll
+            for (int j = 0; j < n; ++j) {
+              const float send = upper ? v[j] : v[j + n];
+              const float keep = upper ? v[j + n] : v[j];
+              const float recv = __shfl_xor_sync(0xffffffffu, send, n);
+              const int other = feature ^ n;  // partner lane's feature (32-aligned groups)
+              const bool take = recv > keep || (recv == keep && other < feature);
+              v[j] = take ? recv : keep;
+              idx[j] = take ? other : feature;
+            }
+          }
+#pragma unroll
+          for (int n = kChunk / 4; n >= 1; n >>= 1) {
+            const bool upper = (lane & n) != 0;
+#pragma unroll
+            for (int j = 0; j < n; ++j) {
+              const float send_v = upper ? v[j] : v[j + n];
+              const int send_i = upper ? idx[j] : idx[j + n];
+              const float keep_v = upper ? v[j + n] : v[j];
+              const int keep_i = upper ? idx[j + n] : idx[j];
+              const float recv_v = __shfl_xor_sync(0xffffffffu, send_v, n);
+              const int recv_i = __shfl_xor_sync(0xffffffffu, send_i, n);
+              const bool take = recv_v > keep_v || (recv_v == keep_v && recv_i < keep_i);
+              v[j] = take ? recv_v : keep_v;
+              idx[j] = take ? recv_i : keep_i;
+            }
+          }
+          if (kChunk == 16) {
+            // 16 columns leave one column per lane PAIR (lane, lane^16), each reduced over its
+            // own 16 lanes: one plain exchange merges the two halves.
+            const float recv_v = __shfl_xor_sync(0xffffffffu, v[0], 16);
+            const int recv_i = __shfl_xor_sync(0xffffffffu, idx[0], 16);
+            const bool take = recv_v > v[0] || (recv_v == v[0] && recv_i < idx[0]);
+            v[0] = take ? recv_v : v[0];
+            idx[0] = take ? recv_i : idx[0];
+          }
+          const int col = (kChunk == 32) ? lane : (lane & 15);
+          const int token = b_row0 + col;
+          if ((kChunk == 32 || lane < 16) && token < args.b_rows) {
             const size_t pidx = static_cast<size_t>(m_blk * 4 + q) * args.ld_amax + token;
-            args.amax_val[pidx] = keep_v;
-            args.amax_idx[pidx] = keep_i;
+            args.amax_val[pidx] = v[0];
+            args.amax_idx[pidx] = idx[0];
           }
         } else if (TRANS) {
           // lane = feature (a_row), columns = tokens. For each token the warp's 32 lanes

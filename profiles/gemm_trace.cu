@@ -31,6 +31,12 @@ static void run(const char* name, int tokens, int features, int k, int epi, int 
   g.act = act; g.w = w; g.bias = bias; g.out = out; g.tokens = tokens; g.features = features; g.k = k;
   g.ld_out = features; g.epilogue = epi; g.split_k = split; g.act_rows_alloc = act_rows;
   g.force_orientation = orient; g.pdl = 0; g.cluster_split = cluster;
+  float* amv = nullptr; int* ami = nullptr; float* eosl = nullptr;
+  if (epi == kEpiLogitsArgmax) {
+    const int groups = ((features + 127) / 128) * 4;
+    cudaMalloc(&amv, (size_t)groups * 256 * 4); cudaMalloc(&ami, (size_t)groups * 256 * 4); cudaMalloc(&eosl, 256 * 4);
+    g.amax_val = amv; g.amax_idx = ami; g.eos_logit = eosl; g.ld_amax = 256; g.eos_id = 50256; g.out = nullptr;
+  }
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   for (int i = 0; i < 3; ++i) {
@@ -69,6 +75,7 @@ int main() {
   run("fc 64x3072x768 split6", 64, 3072, 768, kEpiPartialF32, 6);
   run("proj2 64x768x3072 split24", 64, 768, 3072, kEpiPartialF32, 24);
   run("head 64x50257x768", 64, 50257, 768, kEpiF32, 1);
+  run("head fused argmax", 64, 50257, 768, kEpiLogitsArgmax, 1);
   printf("-- prefill orientation, 8192 tokens (first tile of CTA 0; flops in TF/s from back-to-back)\n");
   run("pf qkv 8192x2304x768", 8192, 2304, 768, kEpiBiasBf16, 1, 0, 0);
   run("pf fc 8192x3072x768 gelu", 8192, 3072, 768, kEpiBiasGeluBf16, 1, 0, 0);
