@@ -141,6 +141,8 @@ struct b200llm_engine {
   std::vector<char> slot_used;
   std::vector<int32_t> slot_capacity;
   std::vector<int32_t> slot_len_host;  // host mirror of seq_len upper bound
+  std::vector<int32_t> page_table_host;  // host mirror [max_seqs][max_pages_per_seq]
+  std::vector<char> slot_pt_dirty;       // row not yet uploaded (uploaded in bulk at prefill)
 
   // slot state (device)
   int32_t *seq_len = nullptr, *last_tok = nullptr, *finished = nullptr, *n_gen = nullptr;
@@ -171,6 +173,8 @@ struct b200llm_engine {
   int32_t* pin_i32 = nullptr;
   size_t pin_i32_count = 0;
   SlotInit* pin_init = nullptr;
+  int32_t* pin_pt = nullptr;    // pinned mirror of the page table (bulk uploads)
+  int32_t* pin_tok = nullptr;   // pinned landing zone for generated tokens [max_seqs][max_new]
 
   // decode graphs
   struct GraphKey {
@@ -627,6 +631,8 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   e->slot_used.assign(cfg->max_seqs, 0);
   e->slot_capacity.assign(cfg->max_seqs, 0);
   e->slot_len_host.assign(cfg->max_seqs, 0);
+  e->page_table_host.assign(static_cast<size_t>(cfg->max_seqs) * e->max_pages_per_seq, 0);
+  e->slot_pt_dirty.assign(cfg->max_seqs, 0);
 
   // ---- slot state -------------------------------------------------------------------------
   const size_t S = cfg->max_seqs;
@@ -682,6 +688,8 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   E_TRY(dev_alloc_t(e.get(), &e->status_dev, 2 * S));
   E_TRY(dev_alloc_t(e.get(), &e->init_dev, S));
   E_CUDA(cudaMallocHost(reinterpret_cast<void**>(&e->pin_init), S * sizeof(SlotInit)));
+  E_CUDA(cudaMallocHost(reinterpret_cast<void**>(&e->pin_pt), S * e->max_pages_per_seq * sizeof(int32_t)));
+  E_CUDA(cudaMallocHost(reinterpret_cast<void**>(&e->pin_tok), S * cfg->max_new_tokens * sizeof(int32_t)));
   E_TRY(ensure_pinned(e.get(), R + 4 * S + 16));
   E_CUDA(cudaStreamSynchronize(st));
 #undef E_TRY
@@ -701,6 +709,8 @@ int b200llm_engine_destroy(b200llm_engine* e) {
   for (void* p : e->allocations) cudaFree(p);
   if (e->pin_i32) cudaFreeHost(e->pin_i32);
   if (e->pin_init) cudaFreeHost(e->pin_init);
+  if (e->pin_pt) cudaFreeHost(e->pin_pt);
+  if (e->pin_tok) cudaFreeHost(e->pin_tok);
   if (e->own_stream) cudaStreamDestroy(e->own_stream);
   gemm_clear_tensor_map_cache();
   delete e;
@@ -737,16 +747,11 @@ int b200llm_seq_alloc(b200llm_engine* e, int32_t capacity_tokens, int32_t* out_s
     pages.push_back(e->free_pages.back());
     e->free_pages.pop_back();
   }
-  // The page-table row is uploaded from pageable memory: cudaMemcpyAsync stages it before
-  // returning, so `pages` may change afterwards.
-  cudaError_t err = cudaMemcpyAsync(e->page_table + static_cast<size_t>(slot) * e->max_pages_per_seq,
-                                    pages.data(), need * sizeof(int32_t), cudaMemcpyHostToDevice,
-                                    e->stream);
-  if (err != cudaSuccess) {
-    for (int32_t p : pages) e->free_pages.push_back(p);
-    pages.clear();
-    return fail(kErrCuda, std::string("seq_alloc: page table upload: ") + cudaGetErrorString(err));
-  }
+  // The row goes to the device in bulk with the next prefill that uses the slot (one copy per
+  // run of consecutive slots instead of one per sequence).
+  std::copy(pages.begin(), pages.end(),
+            e->page_table_host.begin() + static_cast<size_t>(slot) * e->max_pages_per_seq);
+  e->slot_pt_dirty[slot] = 1;
   e->slot_used[slot] = 1;
   e->slot_capacity[slot] = capacity_tokens;
   e->slot_len_host[slot] = 0;
@@ -806,6 +811,29 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   B200_CUDA_OK(cudaMemcpyAsync(e->cu_dev, pin, (batch + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   B200_CUDA_OK(cudaMemcpyAsync(e->slots_dev, pin + batch + 1, batch * sizeof(int32_t),
                                cudaMemcpyHostToDevice, st));
+  // page-table rows of freshly allocated slots: stage in pinned memory, one copy per run of
+  // consecutive slots
+  {
+    std::vector<int32_t> dirty;
+    for (int b = 0; b < batch; ++b) {
+      if (e->slot_pt_dirty[slots[b]]) dirty.push_back(slots[b]);
+    }
+    std::sort(dirty.begin(), dirty.end());
+    dirty.erase(std::unique(dirty.begin(), dirty.end()), dirty.end());
+    const size_t mp = e->max_pages_per_seq;
+    size_t i = 0;
+    int32_t* pt_pin = e->pin_pt;
+    while (i < dirty.size()) {
+      size_t j = i + 1;
+      while (j < dirty.size() && dirty[j] == dirty[j - 1] + 1) ++j;
+      const size_t first = dirty[i], n_rows = j - i;
+      std::memcpy(pt_pin + first * mp, e->page_table_host.data() + first * mp, n_rows * mp * sizeof(int32_t));
+      B200_CUDA_OK(cudaMemcpyAsync(e->page_table + first * mp, pt_pin + first * mp,
+                                   n_rows * mp * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+      i = j;
+    }
+    for (int32_t sidx : dirty) e->slot_pt_dirty[sidx] = 0;
+  }
   const int32_t* ids_dev = ids;
   if (!ids_on_device) {
     for (int i = 0; i < n_tok; ++i) {
@@ -1067,26 +1095,31 @@ int b200llm_generate(b200llm_engine* e, const int32_t* ids_host, const int32_t* 
   }
   rc = b200llm_read_status(e, slots.data(), batch, counts.data(), fin.data());
   if (rc != kOk) return release(rc);
-  // one strided device->host copy of every row, then trim on the host
-  std::vector<int32_t> rows(static_cast<size_t>(batch) * e->cfg.max_new_tokens);
-  for (int b = 0; b < batch; ++b) {
-    const int n = std::min(counts[b], out_stride);
-    if (n > 0) {
-      cudaError_t err = cudaMemcpyAsync(rows.data() + static_cast<size_t>(b) * e->cfg.max_new_tokens,
-                                        e->out_tokens + static_cast<size_t>(slots[b]) * e->cfg.max_new_tokens,
-                                        n * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream);
+  // generated tokens: one device->host copy per run of consecutive slots into pinned memory
+  {
+    const size_t mn = e->cfg.max_new_tokens;
+    std::vector<int32_t> order(slots);
+    std::sort(order.begin(), order.end());
+    size_t i = 0;
+    while (i < order.size()) {
+      size_t j = i + 1;
+      while (j < order.size() && order[j] == order[j - 1] + 1) ++j;
+      const size_t first = order[i], n_rows = j - i;
+      cudaError_t err = cudaMemcpyAsync(e->pin_tok + first * mn, e->out_tokens + first * mn,
+                                        n_rows * mn * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream);
       if (err != cudaSuccess) return release(fail(kErrCuda, cudaGetErrorString(err)));
+      i = j;
     }
-  }
-  cudaError_t err = cudaStreamSynchronize(e->stream);
-  if (err != cudaSuccess) return release(fail(kErrCuda, cudaGetErrorString(err)));
-  for (int b = 0; b < batch; ++b) {
-    const int n = std::min(counts[b], out_stride);
-    for (int i = 0; i < out_stride; ++i) {
-      out_tokens[static_cast<size_t>(b) * out_stride + i] =
-          i < n ? rows[static_cast<size_t>(b) * e->cfg.max_new_tokens + i] : e->cfg.pad_token_id;
+    cudaError_t err = cudaStreamSynchronize(e->stream);
+    if (err != cudaSuccess) return release(fail(kErrCuda, cudaGetErrorString(err)));
+    for (int b = 0; b < batch; ++b) {
+      const int n = std::min(counts[b], out_stride);
+      const int32_t* row = e->pin_tok + static_cast<size_t>(slots[b]) * mn;
+      for (int t = 0; t < out_stride; ++t) {
+        out_tokens[static_cast<size_t>(b) * out_stride + t] = t < n ? row[t] : e->cfg.pad_token_id;
+      }
+      out_counts[b] = n;
     }
-    out_counts[b] = n;
   }
   return release(kOk);
 }
