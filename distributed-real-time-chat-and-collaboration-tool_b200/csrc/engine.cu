@@ -927,7 +927,9 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   p.store_logits = need_logits;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.device);
-  const int cap = e->cfg.decode_split_k == 0 ? 32 : std::min(e->cfg.decode_split_k, 32);
+  // auto: 12 planes at most -- measured optimum (more planes cost the reducing kernel more than
+  // the extra CTAs save the GEMM; profiles/split_sweep.py)
+  const int cap = e->cfg.decode_split_k == 0 ? 12 : std::min(e->cfg.decode_split_k, 32);
   if (bucket <= 256 && cap > 1 && e->cfg.decode_reduce == 2) {
     p.cl_qkv = pick_cluster(3 * e->d, e->d, sms);
     p.cl_o = pick_cluster(e->d, e->d, sms);
