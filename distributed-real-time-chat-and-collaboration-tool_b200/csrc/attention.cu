@@ -80,7 +80,7 @@ __device__ __forceinline__ void load_tile_64x64(__nv_bfloat16 (*dst)[kLds],
 
 __global__ void __launch_bounds__(128)
 prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ cu_seqlens,
-                    int n_head, __nv_bfloat16* __restrict__ out) {
+                    int n_head, __nv_bfloat16* __restrict__ out, PrefillCache cache) {
   __shared__ __align__(16) __nv_bfloat16 sQ[kBQ][kLds];
   __shared__ __align__(16) __nv_bfloat16 sK[kBKV][kLds];
   __shared__ __align__(16) __nv_bfloat16 sV[kBKV][kLds];
@@ -127,6 +127,24 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
     load_tile_64x64(sK, k_base, ld, len - kt * kBKV);
     load_tile_64x64(sV, k_base + d, ld, len - kt * kBKV);
     __syncthreads();
+    if (kt == qt && cache.slots != nullptr) {
+      // diagonal tile: this CTA is the only one that loads exactly this K/V tile last -> it
+      // fills the KV pages ([page][head][16 tokens][64]) straight from shared memory
+      const int32_t* pt = cache.page_table + static_cast<size_t>(cache.slots[b]) * cache.max_pages_per_seq;
+      const int valid = min(kBKV, len - kt * kBKV);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int c = threadIdx.x + 128 * i;
+        const int row = c >> 3, col = (c & 7) * 8;
+        if (row < valid) {
+          const int pos = kt * kBKV + row;
+          const size_t dst = ((static_cast<size_t>(pt[pos / kPageTokens]) * n_head + h) * kPageTokens +
+                              pos % kPageTokens) * kHeadDim + col;
+          *reinterpret_cast<uint4*>(cache.k_pool + dst) = *reinterpret_cast<const uint4*>(&sK[row][col]);
+          *reinterpret_cast<uint4*>(cache.v_pool + dst) = *reinterpret_cast<const uint4*>(&sV[row][col]);
+        }
+      }
+    }
 
     float s[8][4];
 #pragma unroll
@@ -626,10 +644,12 @@ int launch_with_pdl(void (*kernel)(DecodeAttnArgs), dim3 grid, dim3 block, cudaS
 }  // namespace
 
 int prefill_attention(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int batch,
-                      int max_seq_len, int n_head, __nv_bfloat16* out, cudaStream_t stream) {
+                      int max_seq_len, int n_head, __nv_bfloat16* out, cudaStream_t stream,
+                      const PrefillCache* cache) {
   B200_CHECK_ARG(batch > 0 && max_seq_len > 0 && n_head > 0, "prefill_attention: bad shape");
   dim3 grid((max_seq_len + kBQ - 1) / kBQ, n_head, batch);
-  prefill_attn_kernel<<<grid, 128, 0, stream>>>(qkv, cu_seqlens, n_head, out);
+  prefill_attn_kernel<<<grid, 128, 0, stream>>>(qkv, cu_seqlens, n_head, out,
+                                                cache ? *cache : PrefillCache{});
   B200_CUDA_OK(cudaGetLastError());
   return kOk;
 }

@@ -15,8 +15,18 @@ namespace b200llm {
 // Prefill: qkv is the packed [n_tok, 3*d] bf16 output of the QKV GEMM (q | k | v along the
 // feature axis, each [n_head, 64]); sequence b owns rows [cu_seqlens[b], cu_seqlens[b+1]).
 // out is [n_tok, d] bf16 with heads merged (modeling_gpt2.py:222).
+// When `cache` is given, the CTA on the diagonal (query tile == key tile) also writes that
+// K/V tile into the sequence's KV pages, so prefill needs no separate scatter pass.
+struct PrefillCache {
+  const int32_t* slots = nullptr;       // [batch] slot per sequence; null = do not fill pages
+  const int32_t* page_table = nullptr;  // [n_slots, max_pages_per_seq]
+  int max_pages_per_seq = 0;
+  __nv_bfloat16* k_pool = nullptr;
+  __nv_bfloat16* v_pool = nullptr;
+};
 int prefill_attention(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int batch,
-                      int max_seq_len, int n_head, __nv_bfloat16* out, cudaStream_t stream);
+                      int max_seq_len, int n_head, __nv_bfloat16* out, cudaStream_t stream,
+                      const PrefillCache* cache = nullptr);
 
 struct DecodeAttnArgs {
   const __nv_bfloat16* qkv;      // [batch, 3*d] current token (bias already added), or null when

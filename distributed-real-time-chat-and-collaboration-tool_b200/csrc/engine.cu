@@ -372,10 +372,14 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
       if (p.attn_splits > 1) e->launches += 1, e->launches_in_capture += 1;
     } else {
-      B200_PROPAGATE(count(e, kv_scatter(e->qkv, e->row_slot, e->row_pos, e->page_table,
-                                         e->max_pages_per_seq, kp, vp, rows, e->H, e->stream)));
+      PrefillCache pc;
+      pc.slots = e->slots_dev;
+      pc.page_table = e->page_table;
+      pc.max_pages_per_seq = e->max_pages_per_seq;
+      pc.k_pool = kp;
+      pc.v_pool = vp;
       B200_PROPAGATE(count(e, prefill_attention(e->qkv, e->cu_dev, p.batch, p.max_len, e->H,
-                                                e->attn, e->stream)));
+                                                e->attn, e->stream, &pc)));
     }
     // attn c_proj + residual (:223, :282)
     if (p.decode && p.cl_o > 1) {

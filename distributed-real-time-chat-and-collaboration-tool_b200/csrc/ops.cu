@@ -129,6 +129,47 @@ layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int 
   }
 }
 
+// Many rows, no partial planes (prefill): one warp per row, 8 rows per CTA, the whole row in
+// registers (VEC float4 per lane) -- one CTA per row is launch-bound at thousands of rows.
+template <int VEC>  // d = VEC * 128
+__global__ void __launch_bounds__(256)
+layernorm_rows_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                      const float* __restrict__ beta, const int32_t* __restrict__ row_index,
+                      __nv_bfloat16* __restrict__ out, int rows, float eps) {
+  constexpr int D = VEC * 128;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int orow = blockIdx.x * 8 + warp;
+  pdl_wait();
+  pdl_launch_dependents();
+  if (orow >= rows) return;
+  const int irow = row_index ? row_index[orow] : orow;
+  const float4* xr = reinterpret_cast<const float4*>(x + static_cast<size_t>(irow) * D);
+  float4 v[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) v[i] = xr[lane + 32 * i];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  const float mean = warp_sum(sum) * (1.0f / D);
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) {
+    const float a0 = v[i].x - mean, a1 = v[i].y - mean, a2 = v[i].z - mean, a3 = v[i].w - mean;
+    sq += (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
+  }
+  const float rstd = 1.0f / sqrtf(warp_sum(sq) * (1.0f / D) + eps);
+  uint2* o = reinterpret_cast<uint2*>(out + static_cast<size_t>(orow) * D);
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) {
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + lane + 32 * i);
+    uint2 pk;
+    pk.x = pack_bf16x2((v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y);
+    pk.y = pack_bf16x2((v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w);
+    o[lane + 32 * i] = pk;
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // Split-K reduce + bias + gelu_new -> bf16 (one float4 column group per thread)
 // ---------------------------------------------------------------------------------------
@@ -443,6 +484,25 @@ int embed_decode(const float* wte, const float* wpe, const int32_t* active_slots
 int layernorm(const LayerNormArgs& a, cudaStream_t stream) {
   B200_CHECK_ARG(a.rows > 0 && a.d % 4 == 0 && a.d / 4 <= 512,
                  "layernorm: d must be a multiple of 4 and at most 2048");
+  if (a.n_partials == 0 && a.rows >= 512 && a.d % 128 == 0) {
+    const dim3 grid((a.rows + 7) / 8), block(256);
+    const float* xc = a.x;
+#define B200_LN_ROWS(V)                                                                          \
+  case V:                                                                                        \
+    return launch_pdl(layernorm_rows_kernel<V>, grid, block, stream, a.pdl, xc, a.gamma, a.beta, \
+                      a.row_index, a.out, a.rows, a.eps);
+    switch (a.d / 128) {
+      B200_LN_ROWS(1)
+      B200_LN_ROWS(2)
+      B200_LN_ROWS(4)
+      B200_LN_ROWS(6)
+      B200_LN_ROWS(8)
+      B200_LN_ROWS(10)
+      default:
+        break;  // fall through to the generic kernel
+    }
+#undef B200_LN_ROWS
+  }
   const int threads = ((a.d / 4 + 31) / 32) * 32;
   const int rows_total = a.partial_rows > 0 ? a.partial_rows : a.rows;
   return launch_pdl(layernorm_kernel, dim3(a.rows), dim3(threads), stream, a.pdl, a.x, a.partials,
