@@ -64,17 +64,21 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-__device__ __forceinline__ void load_tile_64x64(__nv_bfloat16 (*dst)[kLds],
-                                                const __nv_bfloat16* src, int ld, int rows_valid) {
-  // 64 rows x 8 chunks of 16 B; 128 threads -> 4 chunks each
+// 64 rows x 8 chunks of 16 B, 128 threads -> 4 cp.async each; rows beyond `rows_valid` are
+// zero-filled (src-size 0), so the copy never reads outside the sequence.
+__device__ __forceinline__ void load_tile_64x64_async(__nv_bfloat16 (*dst)[kLds], const __nv_bfloat16* src,
+                                                      int ld, int rows_valid) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int c = threadIdx.x + 128 * i;
     const int row = c >> 3;
     const int col = (c & 7) * 8;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (row < rows_valid) v = *reinterpret_cast<const uint4*>(src + static_cast<size_t>(row) * ld + col);
-    *reinterpret_cast<uint4*>(&dst[row][col]) = v;
+    const bool ok = row < rows_valid;
+    const __nv_bfloat16* g = src + static_cast<size_t>(ok ? row : 0) * ld + col;
+    const int bytes = ok ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(&dst[row][col])), "l"(g),
+                 "r"(bytes)
+                 : "memory");
   }
 }
 
@@ -82,8 +86,8 @@ __global__ void __launch_bounds__(128)
 prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ cu_seqlens,
                     int n_head, __nv_bfloat16* __restrict__ out, PrefillCache cache) {
   __shared__ __align__(16) __nv_bfloat16 sQ[kBQ][kLds];
-  __shared__ __align__(16) __nv_bfloat16 sK[kBKV][kLds];
-  __shared__ __align__(16) __nv_bfloat16 sV[kBKV][kLds];
+  __shared__ __align__(16) __nv_bfloat16 sKb[2][kBKV][kLds];  // double-buffered K/V tiles
+  __shared__ __align__(16) __nv_bfloat16 sVb[2][kBKV][kLds];
 
   const int b = blockIdx.z;
   const int h = blockIdx.y;
@@ -99,17 +103,14 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
   const int t = lane & 3;   // column pair
 
   const __nv_bfloat16* q_base = qkv + static_cast<size_t>(row0 + qt * kBQ) * ld + h * kHeadDim;
-  load_tile_64x64(sQ, q_base, ld, len - qt * kBQ);
-  __syncthreads();
+  const __nv_bfloat16* kv_base = qkv + static_cast<size_t>(row0) * ld + d + h * kHeadDim;
+  // Q and the first K/V tile in one cp.async group
+  load_tile_64x64_async(sQ, q_base, ld, len - qt * kBQ);
+  load_tile_64x64_async(sKb[0], kv_base, ld, len);
+  load_tile_64x64_async(sVb[0], kv_base + d, ld, len);
+  asm volatile("cp.async.commit_group;" ::: "memory");
 
   uint32_t qf[4][4];
-  {
-    const int i = lane >> 3, r = lane & 7;
-#pragma unroll
-    for (int ks = 0; ks < 4; ++ks) {
-      ldmatrix_x4(qf[ks], &sQ[warp * 16 + (i & 1) * 8 + r][ks * 16 + (i >> 1) * 8]);
-    }
-  }
 
   float o[8][4];
 #pragma unroll
@@ -121,15 +122,29 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
   const int qrow_lo = qt * kBQ + warp * 16 + g;  // this thread's rows: qrow_lo, qrow_lo + 8
 
   for (int kt = 0; kt <= qt; ++kt) {
-    __syncthreads();  // previous tile fully consumed
-    const __nv_bfloat16* k_base =
-        qkv + static_cast<size_t>(row0 + kt * kBKV) * ld + d + h * kHeadDim;
-    load_tile_64x64(sK, k_base, ld, len - kt * kBKV);
-    load_tile_64x64(sV, k_base + d, ld, len - kt * kBKV);
+    __nv_bfloat16 (*sK)[kLds] = sKb[kt & 1];
+    __nv_bfloat16 (*sV)[kLds] = sVb[kt & 1];
+    // prefetch the next tile into the other buffer (its last readers finished at the barrier
+    // that closed the previous iteration), then wait for the current one
+    if (kt + 1 <= qt) {
+      const __nv_bfloat16* nk = kv_base + static_cast<size_t>((kt + 1) * kBKV) * ld;
+      load_tile_64x64_async(sKb[(kt + 1) & 1], nk, ld, len - (kt + 1) * kBKV);
+      load_tile_64x64_async(sVb[(kt + 1) & 1], nk + d, ld, len - (kt + 1) * kBKV);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
     __syncthreads();
+    if (kt == 0) {
+      const int i = lane >> 3, r = lane & 7;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        ldmatrix_x4(qf[ks], &sQ[warp * 16 + (i & 1) * 8 + r][ks * 16 + (i >> 1) * 8]);
+      }
+    }
     if (kt == qt && cache.slots != nullptr) {
-      // diagonal tile: this CTA is the only one that loads exactly this K/V tile last -> it
-      // fills the KV pages ([page][head][16 tokens][64]) straight from shared memory
+      // diagonal tile: this CTA fills the KV pages ([page][head][16 tokens][64]) from smem
       const int32_t* pt = cache.page_table + static_cast<size_t>(cache.slots[b]) * cache.max_pages_per_seq;
       const int valid = min(kBKV, len - kt * kBKV);
 #pragma unroll
@@ -165,15 +180,18 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
       }
     }
 
-    // causal + length mask, row maxima
+    // causal + length mask (only the diagonal tile and a ragged last tile need it), row maxima
+    const bool need_mask = (kt == qt) || ((kt + 1) * kBKV > len);
     float mx[2] = {-INFINITY, -INFINITY};
 #pragma unroll
     for (int n = 0; n < 8; ++n) {
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        const int col = kt * kBKV + n * 8 + 2 * t + (c & 1);
-        const int row = qrow_lo + (c >> 1) * 8;
-        if (col > row || col >= len) s[n][c] = -INFINITY;
+        if (need_mask) {
+          const int col = kt * kBKV + n * 8 + 2 * t + (c & 1);
+          const int row = qrow_lo + (c >> 1) * 8;
+          if (col > row || col >= len) s[n][c] = -INFINITY;
+        }
         mx[c >> 1] = fmaxf(mx[c >> 1], s[n][c]);
       }
     }
@@ -224,6 +242,7 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
         }
       }
     }
+    __syncthreads();  // this tile's buffer may be overwritten by the prefetch two tiles ahead
   }
 
   // finalize
