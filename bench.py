@@ -112,6 +112,24 @@ def measured_peaks() -> tuple[dict, str]:
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
+def lmhead_traffic_from_profile() -> float | None:
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the LM-head GEMM, from the
+    committed `ncu --set full` capture (profiles/r1_lmhead_ncu_full.csv)."""
+    import csv
+
+    path = os.path.join(ROOT, "profiles", "r1_lmhead_ncu_full.csv")
+    if not os.path.exists(path):
+        return None
+    rows = list(csv.reader(open(path)))
+    hdr = rows[0]
+    try:
+        ri, wi = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        vals = [(float(r[ri]) + float(r[wi])) * 1e6 for r in rows[2:] if len(r) > max(ri, wi)]
+        return sum(vals) / len(vals) if vals else None
+    except (ValueError, IndexError):
+        return None
+
+
 def decode_step_bytes(shape, batch: int, ctx: int) -> int:
     """Algorithmic HBM bytes of one decode step: bf16 weights streamed once +
     KV read for `ctx` cached tokens + KV written for one token, per sequence."""
@@ -309,7 +327,8 @@ def run_ours(args):
             "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
             "bytes_per_launch": head_bytes,
             "us_per_launch": head_ms * 1e3,
-            "traffic": None,
+            "traffic": lmhead_traffic_from_profile(),
+            "traffic_source": "profiles/r1_lmhead_ncu_full.csv (ncu --set full, B = 64)",
         },
         "decode_step_roofline": {
             "bound": "hbm",
