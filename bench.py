@@ -141,6 +141,79 @@ def decode_step_bytes(shape, batch: int, ctx: int) -> int:
 
 
 # ------------------------------------------------------------------------------------------
+# p50 SmartReply (second half of BASELINE.json's metric)
+# ------------------------------------------------------------------------------------------
+SMART_REPLY_CONVERSATION = [
+    ("alice", "Are we still on for the design review at 3pm?"),
+    ("bob", "Yes, I booked room 4B. Bring the latency numbers."),
+    ("charlie", "I can't make it before 3:30, start without me."),
+    ("alice", "OK. Bob, can you share the doc beforehand?"),
+    ("bob", "Sure, sending it now."),
+]
+
+
+def smart_reply_latency(E, shape, blob, device: int, n_calls: int = 200, cpu_calls: int = 3) -> dict:
+    """LLMServiceStub.GetSmartReply round trips on 127.0.0.1 through the whole drop-in stack
+    (gRPC -> LLMServicer prompts/parsers -> LocalGenerativeModel -> scheduler -> CUDA engine),
+    sequential calls, fixed five-message conversation, 32 new tokens."""
+    from concurrent import futures as _f
+
+    import grpc
+
+    server_mod = importlib.import_module(f"{PKG}.server")
+    svc = importlib.import_module(f"{PKG}.llm_service")
+    pb = importlib.import_module(f"{PKG}.llm_proto")
+    sched = importlib.import_module(f"{PKG}.scheduler")
+    lm = importlib.import_module(f"{PKG}.local_model")
+    tok = importlib.import_module(f"{PKG}.tokenizer")
+
+    eng = E.Engine(shape, blob, device=device, max_seqs=8, max_seq_len=1024, max_batch_tokens=4096,
+                   max_new_tokens=64)
+    router = sched.Router([sched.EngineWorker(eng, decode_burst=31)])
+    tokenizer = tok.ByteLevelTokenizer()
+    model = lm.LocalGenerativeModel(router, tokenizer, default_max_new_tokens=32, max_prompt_tokens=900)
+    server = grpc.server(_f.ThreadPoolExecutor(max_workers=8))
+    server_mod.add_llm_service(svc.LLMServicer(model), server)
+    port = server.add_insecure_port("127.0.0.1:0")
+    server.start()
+    msgs = [pb.Message(sender=a, content=b) for a, b in SMART_REPLY_CONVERSATION]
+    prompt = svc.PROMPTS["smart_reply"].format(conversation="\n".join(f"{a}: {b}" for a, b in SMART_REPLY_CONVERSATION))
+    prompt_tokens = len(tokenizer.encode(prompt))
+    lat = []
+    try:
+        with grpc.insecure_channel(f"127.0.0.1:{port}") as ch:
+            stub = server_mod.LLMServiceStub(ch)
+            req = pb.SmartReplyRequest(request_id="bench", recent_messages=msgs, user_id="bob")
+            for _ in range(10):
+                stub.GetSmartReply(req, timeout=20)
+            for _ in range(n_calls):
+                t0 = time.perf_counter()
+                r = stub.GetSmartReply(req, timeout=20)
+                lat.append((time.perf_counter() - t0) * 1e3)
+            assert len(r.suggestions) >= 2
+    finally:
+        server.stop(0)
+        router.shutdown()
+        eng.close()
+    out = {"p50_ms": float(np.percentile(lat, 50)), "p95_ms": float(np.percentile(lat, 95)), "calls": n_calls,
+           "prompt_tokens": prompt_tokens, "new_tokens": 32,
+           "path": "gRPC 127.0.0.1 -> LLMServicer -> LocalGenerativeModel -> scheduler -> CUDA engine"}
+    if cpu_calls > 0:
+        torch, H, hf, _, _ = _cpu_setup("smart_reply_b1")
+        torch.set_num_threads(os.cpu_count() or 1)
+        ids = torch.tensor([tokenizer.encode(prompt)])
+        cpu = []
+        for i in range(cpu_calls + 1):
+            t0 = time.perf_counter()
+            H.hf_generate(hf, ids, 32, min_new_tokens=32)
+            if i:
+                cpu.append((time.perf_counter() - t0) * 1e3)
+        out["cpu_p50_ms"] = float(np.percentile(cpu, 50))
+        out["cpu_note"] = "transformers generate on the host cores, same prompt tokens, direct call (no gRPC)"
+    return out
+
+
+# ------------------------------------------------------------------------------------------
 # Our arm
 # ------------------------------------------------------------------------------------------
 def run_ours(args):
@@ -168,7 +241,6 @@ def run_ours(args):
     blob = W.synthetic_blob(shape, seed=0, hf_like=True)
     eng = E.Engine(shape, blob, device=local, max_seqs=B, max_seq_len=T + N,
                    max_batch_tokens=min(B * T, 16384), max_new_tokens=N)
-    del blob
     stream = torch.cuda.Stream(device=dev)
     eng.set_stream(stream.cuda_stream)
     sp = [E.SamplingParams(max_new_tokens=N, min_new_tokens=N)] * B
@@ -287,7 +359,7 @@ def run_ours(args):
     step_bytes = decode_step_bytes(shape, B, int(round(avg_ctx)))
     decode_step_ms = decode_ms / (N - 1)
     result = {
-        "metric": "generated tokens/sec (GPT-2 small, batch 64) at 1/2/4/8 B200",
+        "metric": "generated tokens/sec (GPT-2 small, batch 64) at 1/2/4/8 B200; p50 SmartReply ms",
         "value": value,
         "unit": "tokens/s",
         "n_gpus": world,
@@ -340,9 +412,12 @@ def run_ours(args):
             "frac": step_bytes / (decode_step_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
         },
     }
+    eng.close()
+    if rank == 0 and model == "small" and not args.no_smart_reply:
+        result["smart_reply"] = smart_reply_latency(E, shape, blob, local,
+                                                    cpu_calls=0 if (args.no_cpu_baseline or world > 1) else 3)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         result["cpu_baseline"] = cpu_baseline(args.workload, budget_s=25.0)
-    eng.close()
     if rank == 0:
         print(json.dumps(result))
     if dist is not None:
@@ -414,7 +489,7 @@ def run_reference(args):
             f"{T}-token prompts, {N} new tokens")
     print(json.dumps({
         "impl": "reference",
-        "metric": "generated tokens/sec (GPT-2 small, batch 64) at 1/2/4/8 B200",
+        "metric": "generated tokens/sec (GPT-2 small, batch 64) at 1/2/4/8 B200; p50 SmartReply ms",
         "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -434,6 +509,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="smart_reply_b64", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-smart-reply", action="store_true", help="skip the p50 SmartReply gRPC measurement")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
