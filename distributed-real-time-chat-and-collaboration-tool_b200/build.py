@@ -51,7 +51,7 @@ def build_trace_variant() -> Path:
     out = HERE / "libb200llm_trace.so"
     srcs = [str(CSRC / n) for n in SOURCES]
     flags = [f for f in FLAGS if f not in ("-Xptxas", "-v")]
-    cmd = [NVCC, *flags, "-DB200_ATTN_TRACE", "-shared", "-o", str(out), *srcs, "-lcudart"]
+    cmd = [NVCC, *flags, "-DB200_ATTN_TRACE", "-DB200_STEP_TRACE", "-shared", "-o", str(out), *srcs, "-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(r.stdout + r.stderr)

@@ -358,14 +358,14 @@ __device__ __forceinline__ void attend_tokens(Softmax8& acc, const float (&q)[8]
 }
 
 // Ordering argument for everything this kernel does BEFORE griddepcontrol.wait.
-// In a decode step only the GEMM kernels signal launch_dependents before their own wait; every
-// other kernel (embed, LayerNorm, this one, gelu-reduce, select) signals after its wait has
-// returned, i.e. after its predecessor has completely finished. This kernel's predecessor is the
-// QKV GEMM, whose predecessor is a LayerNorm: by the time a CTA of this kernel runs at all, that
-// LayerNorm has passed its wait, so everything up to the kernel before it -- in particular the
-// previous step's selector (seq_len, finished) and the previous step's attention kernels (KV
-// positions < seq_len) -- is complete and visible. Only the QKV projection of THIS step is not.
-// So the whole cached KV stream is fetched before the wait and overlaps the QKV GEMM.
+// In a decode step the GEMM, LayerNorm and gelu-reduce kernels signal launch_dependents at entry;
+// the embed kernel (first of every step), this kernel and the selector signal only AFTER their own
+// wait has returned, i.e. after their predecessor has completely finished. A CTA of this kernel
+// can therefore only be running if this step's embed kernel has passed its wait, which means the
+// previous step's selector -- and with it the whole previous step -- is complete and visible:
+// seq_len / finished are final, and KV positions < seq_len (written by earlier steps) are
+// immutable. Only the QKV projection of THIS step is not ready. So the whole cached KV stream is
+// fetched before the wait and overlaps the QKV GEMM.
 __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   __shared__ float sm_o[4][kHeadDim];
   __shared__ float sm_ml[4][2];
@@ -385,6 +385,7 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   const int grp = warp * 4 + (lane >> 3);  // 0..15: token within the 16-token page
   const int d = a.n_head * kHeadDim;
   B200_ATRACE(0);
+  B200_STEP_BEGIN(5);
 
   const int slot = a.active_slots ? a.active_slots[b] : b;
   if (slot < 0) {
@@ -619,6 +620,7 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
     }
   }
   B200_ATRACE(6);
+  B200_STEP_END();
 }
 
 __global__ void __launch_bounds__(64) decode_combine_kernel(DecodeAttnArgs a) {
@@ -718,6 +720,8 @@ int decode_attention_noalloc(DecodeAttnArgs a, cudaStream_t stream) {
   a.scratch = scratch;
   return decode_attention(a, stream);
 }
+
+B200_DEFINE_STEP_TRACE_SETTER(step_trace_set_attention)
 
 #ifdef B200_ATTN_TRACE
 }  // namespace b200llm

@@ -297,6 +297,46 @@ __device__ __forceinline__ void pdl_launch_dependents() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
+// ---------------------------------------------------------------------------------------
+// Profiling builds only (-DB200_STEP_TRACE, build.py --trace): block 0 / thread 0 of every
+// kernel records %globaltimer at entry and exit into a shared buffer, in launch order, so
+// the real timeline of a CUDA-graph + PDL decode step can be read back without a profiler.
+// ---------------------------------------------------------------------------------------
+#ifdef B200_STEP_TRACE
+struct StepTraceSink {
+  unsigned long long* buf;  // [2 * capacity]: begin, end
+  unsigned int* idx;
+  unsigned int capacity;
+};
+static __device__ StepTraceSink g_step_trace;  // one copy per translation unit, same target
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define B200_STEP_BEGIN(tag)                                                                  \
+  unsigned int _st_slot = 0xffffffffu;                                                        \
+  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 &&            \
+      g_step_trace.buf != nullptr) {                                                          \
+    _st_slot = atomicAdd(g_step_trace.idx, 1u);                                               \
+    if (_st_slot < g_step_trace.capacity) {                                                   \
+      g_step_trace.buf[3 * _st_slot] = global_timer_ns();                                     \
+      g_step_trace.buf[3 * _st_slot + 2] = (tag);                                             \
+    }                                                                                         \
+  }
+#define B200_STEP_END()                                                                       \
+  if (_st_slot < g_step_trace.capacity) g_step_trace.buf[3 * _st_slot + 1] = global_timer_ns();
+#define B200_DEFINE_STEP_TRACE_SETTER(fn)                                                     \
+  void fn(unsigned long long* buf, unsigned int* idx, unsigned int capacity) {                \
+    StepTraceSink s{buf, idx, capacity};                                                      \
+    cudaMemcpyToSymbol(g_step_trace, &s, sizeof(s));                                          \
+  }
+#else
+#define B200_STEP_BEGIN(tag)
+#define B200_STEP_END()
+#define B200_DEFINE_STEP_TRACE_SETTER(fn)
+#endif
+
 #endif  // __CUDACC__
 
 }  // namespace b200llm

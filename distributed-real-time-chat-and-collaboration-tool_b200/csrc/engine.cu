@@ -503,6 +503,14 @@ int ensure_pinned(b200llm_engine* e, size_t count_i32) {
 }  // namespace
 }  // namespace b200llm
 
+#ifdef B200_STEP_TRACE
+namespace b200llm {
+void step_trace_set_gemm(unsigned long long*, unsigned int*, unsigned int);
+void step_trace_set_ops(unsigned long long*, unsigned int*, unsigned int);
+void step_trace_set_attention(unsigned long long*, unsigned int*, unsigned int);
+}  // namespace b200llm
+#endif
+
 // =========================================================================================
 // C ABI
 // =========================================================================================
@@ -1131,6 +1139,35 @@ int b200llm_generate(b200llm_engine* e, const int32_t* ids_host, const int32_t* 
 }
 
 int64_t b200llm_kernel_launches(const b200llm_engine* e) { return e ? e->launches : 0; }
+
+#ifdef B200_STEP_TRACE
+// Profiling builds only. op 0: arm (allocates a buffer of `capacity` records, resets the counter);
+// op 1: read back up to `capacity` records of (begin ns, end ns, tag) and return the count.
+int b200llm_debug_step_trace(int op, unsigned long long* out, int capacity) {
+  static unsigned long long* buf = nullptr;
+  static unsigned int* idx = nullptr;
+  static int cap = 0;
+  if (op == 0) {
+    if (buf == nullptr) {
+      cap = capacity;
+      cudaMalloc(&buf, static_cast<size_t>(cap) * 3 * sizeof(unsigned long long));
+      cudaMalloc(&idx, sizeof(unsigned int));
+    }
+    cudaMemset(idx, 0, sizeof(unsigned int));
+    cudaMemset(buf, 0, static_cast<size_t>(cap) * 3 * sizeof(unsigned long long));
+    b200llm::step_trace_set_gemm(buf, idx, cap);
+    b200llm::step_trace_set_ops(buf, idx, cap);
+    b200llm::step_trace_set_attention(buf, idx, cap);
+    return cudaDeviceSynchronize() == cudaSuccess ? 0 : 2;
+  }
+  unsigned int n = 0;
+  cudaMemcpy(&n, idx, sizeof(n), cudaMemcpyDeviceToHost);
+  if (static_cast<int>(n) > capacity) n = capacity;
+  if (static_cast<int>(n) > cap) n = cap;
+  cudaMemcpy(out, buf, static_cast<size_t>(n) * 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+  return static_cast<int>(n);
+}
+#endif
 
 // ---- operator-level entry points ----------------------------------------------------------
 int b200llm_op_gemm(const void* act, const void* w, const float* bias, void* out, int32_t tokens,

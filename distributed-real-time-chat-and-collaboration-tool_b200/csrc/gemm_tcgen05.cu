@@ -133,6 +133,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   if (threadIdx.x == 0) B200_TRACE(0);
+  B200_STEP_BEGIN(100 + EPI);
 
   const int num_m_blocks = (args.a_rows + kBlockM - 1) / kBlockM;
   const int num_n_blocks = (args.b_rows + BLOCK_N - 1) / BLOCK_N;
@@ -1102,6 +1103,8 @@ int dispatch_cluster(const GemmArgs& g, cudaStream_t stream) {
 }
 
 }  // namespace
+
+B200_DEFINE_STEP_TRACE_SETTER(step_trace_set_gemm)
 
 void gemm_clear_tensor_map_cache() {
   std::lock_guard<std::mutex> lock(map_mutex());

@@ -73,6 +73,12 @@ layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int 
                  const float* __restrict__ beta, const int32_t* __restrict__ row_index,
                  __nv_bfloat16* __restrict__ out, int d, int rows_total, float eps) {
   __shared__ float red[32];
+  B200_STEP_BEGIN(1);
+  // This kernel reads nothing mutable before its dependency wait, so the next kernel (a GEMM
+  // that starts by prefetching weights) may be launched as soon as this one is resident.
+  // (embed / attention / select signal only AFTER their wait: they are the ordering fences the
+  // attention kernel's early KV reads rely on, see attention.cu.)
+  pdl_launch_dependents();
   const int orow = blockIdx.x;
   const int c = threadIdx.x;  // float4 column
   const int ncol = d >> 2;
@@ -85,7 +91,6 @@ layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int 
     if (n_partials > 0 && add_bias != nullptr) ab = __ldg(reinterpret_cast<const float4*>(add_bias) + c);
   }
   pdl_wait();
-  pdl_launch_dependents();
   const int irow = row_index ? row_index[orow] : orow;
   float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
   float4* xr = reinterpret_cast<float4*>(x + static_cast<size_t>(irow) * d);
@@ -127,6 +132,7 @@ layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int 
     pk.y = pack_bf16x2((v.z - mean) * rstd * g.z + b.z, (v.w - mean) * rstd * g.w + b.w);
     reinterpret_cast<uint2*>(out + static_cast<size_t>(orow) * d)[c] = pk;
   }
+  B200_STEP_END();
 }
 
 // Many rows, no partial planes (prefill): one warp per row, 8 rows per CTA, the whole row in
@@ -177,14 +183,18 @@ __global__ void __launch_bounds__(256)
 reduce_bias_gelu_kernel(const float* __restrict__ partials, int n_partials, size_t plane_f4,
                         const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int rows,
                         int cols4) {
+  B200_STEP_BEGIN(2);
+  pdl_launch_dependents();  // nothing mutable is read before the wait (see layernorm_kernel)
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int total = rows * cols4;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   const int c4 = idx % cols4;
   if (idx < total) acc = __ldg(reinterpret_cast<const float4*>(bias) + c4);
   pdl_wait();
-  pdl_launch_dependents();
-  if (idx >= total) return;
+  if (idx >= total) {
+    B200_STEP_END();
+    return;
+  }
   const float4* p = reinterpret_cast<const float4*>(partials) + idx;
   int s = 0;
   for (; s + 2 <= n_partials; s += 2) {
@@ -201,6 +211,7 @@ reduce_bias_gelu_kernel(const float* __restrict__ partials, int n_partials, size
   pk.x = pack_bf16x2(gelu_new(acc.x), gelu_new(acc.y));
   pk.y = pack_bf16x2(gelu_new(acc.z), gelu_new(acc.w));
   reinterpret_cast<uint2*>(out)[idx] = pk;
+  B200_STEP_END();
 }
 
 // ---------------------------------------------------------------------------------------
@@ -262,6 +273,7 @@ __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
   __shared__ MaxIdx red[32];
   __shared__ float top_v[kMaxTopK];
   __shared__ int top_i[kMaxTopK];
+  B200_STEP_BEGIN(3);
   pdl_wait();
   pdl_launch_dependents();
   const int row = blockIdx.x;
@@ -369,6 +381,7 @@ __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
     a.last_tok[slot] = tok;
     if (!was_finished && (tok == a.eos_id || g + 1 >= cap)) a.finished[slot] = 1;
     if (a.advance_seq && !was_finished) a.seq_len[slot] = a.seq_len[slot] + 1;
+    B200_STEP_END();
   }
   pdl_launch_dependents();
 }
@@ -462,6 +475,8 @@ int launch_pdl(Kernel kernel, dim3 grid, dim3 block, cudaStream_t stream, int pd
 }
 
 }  // namespace
+
+B200_DEFINE_STEP_TRACE_SETTER(step_trace_set_ops)
 
 int embed_tokens(const float* wte, const float* wpe, const int32_t* ids, const int32_t* pos,
                  float* x, int n_tok, int d, int vocab, int n_positions, cudaStream_t stream) {
