@@ -198,6 +198,7 @@ struct b200llm_engine {
   // Profiling aid (env B200LLM_SKIP, bit mask): drop a class of kernels from the decode step to
   // read its in-graph cost by difference. Results are garbage when set; never set in tests.
   int skip_mask = 0;
+  int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
 };
 
 namespace b200llm {
@@ -281,6 +282,7 @@ int gemm(b200llm_engine* e, const __nv_bfloat16* act, const __nv_bfloat16* w, co
          int cluster_split = 0) {
   GemmArgs g = {};
   g.cluster_split = cluster_split;
+  g.use_pair = e->pair_mode;
   g.act = act;
   g.w = w;
   g.bias = bias;
@@ -544,6 +546,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   std::unique_ptr<b200llm_engine> e(new b200llm_engine());
   e->cfg = *cfg;
   if (const char* skip = std::getenv("B200LLM_SKIP")) e->skip_mask = std::atoi(skip);
+  if (const char* pair = std::getenv("B200LLM_PAIR")) e->pair_mode = std::atoi(pair);
   e->d = cfg->d_model;
   e->H = cfg->n_head;
   e->L = cfg->n_layer;
@@ -1186,7 +1189,8 @@ int b200llm_op_gemm(const void* act, const void* w, const float* bias, void* out
   g.split_k = split_k > 0 ? split_k : 1;
   g.cluster_split = split_k < 0 ? -split_k : 0;  // negative split_k selects the cluster (DSMEM) reduction
   g.act_rows_alloc = tokens;
-  g.force_orientation = orientation;
+  g.force_orientation = orientation == 2 ? 0 : orientation;
+  g.use_pair = orientation == 2 ? 1 : (orientation == 0 ? 0 : -1);  // 2: CTA pairs, 0: single-CTA tiles
   g.pdl = 0;
   return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
 }

@@ -840,6 +840,282 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   if (threadIdx.x == 64) B200_TRACE(8);
 }
 
+
+// ---------------------------------------------------------------------------------------
+// CTA-pair variant for prefill (tokens on UMMA-M): tcgen05.mma.cta_group::2, M = 256.
+//
+// Two CTAs of a cluster (one TPC) own a 256 x 256 output tile: CTA `rank` loads its own 128
+// token rows of A and HALF of the weight tile (128 of the 256 feature rows), the leader issues
+// one UMMA that reads both halves, and each CTA's TMEM receives its 128 rows x 256 columns.
+// Per SM that is 32 KB of operands per 64-deep k block instead of 48 KB, which matters because
+// these GEMMs are bound by per-SM operand ingest through TMA, not by the tensor pipe.
+// Barriers: TMA of both CTAs completes on the LEADER's full barrier; the leader's
+// tcgen05.commit multicasts to the empty / tmem_full barriers of both CTAs; both epilogues
+// arrive (locally / remotely) on the leader's tmem_empty barrier.
+// ---------------------------------------------------------------------------------------
+constexpr int kPairStageBytes = 2 * kBlockM * kBlockK * 2;  // A 16 KB + half of B 16 KB
+constexpr int kPairStages = 6;
+constexpr int kPairN = 256;
+constexpr int kPairSmemBytes = kPairStages * kPairStageBytes + 2 * kEpiBoxBytes + 1024 + 256;
+
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* desc, uint32_t leader_bar,
+                                                 int32_t c0, int32_t c1, uint64_t cache_hint) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;"
+      :
+      : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(leader_bar), "r"(c0), "r"(c1),
+        "l"(cache_hint)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ss_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                                  uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n"
+      :
+      : "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive (once the leader's previously issued MMAs retire) on the barrier at this smem offset in
+// BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  const uint16_t mask = 0x3;
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta_rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(cta_rank));
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const __grid_constant__ CUtensorMap map_out, const KernelArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~static_cast<uintptr_t>(1023u));
+  uint8_t* ring = smem;
+  uint8_t* epi_stage = smem + kPairStages * kPairStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_stage + 2 * kEpiBoxBytes);
+  uint64_t* empty_bar = full_bar + kPairStages;
+  uint64_t* tmem_full_bar = empty_bar + kPairStages;
+  uint64_t* tmem_empty_bar = tmem_full_bar + kAccumStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + kAccumStages);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int n_clusters = gridDim.x >> 1;
+  const int num_m2 = (args.a_rows + 2 * kBlockM - 1) / (2 * kBlockM);
+  const int num_n = (args.b_rows + kPairN - 1) / kPairN;
+  const int num_tiles = num_m2 * num_n;
+  const int num_kb = args.k_blocks_total;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_out);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kPairStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < kAccumStages; ++s) {
+      mbar_init(&tmem_full_bar[s], 1);
+      mbar_init(&tmem_empty_bar[s], 8);  // 4 epilogue warps of each CTA
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // both CTAs' barriers exist before anyone signals across the pair
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      pdl_wait();
+      int it = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += n_clusters) {
+        const int m2 = tile % num_m2, n_blk = tile / num_m2;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int stage = it % kPairStages;
+          const uint32_t phase = static_cast<uint32_t>(it / kPairStages) & 1u;
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          uint8_t* sa = ring + stage * kPairStageBytes;
+          uint8_t* sb = sa + kBlockM * kBlockK * 2;
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * kPairStageBytes);
+          // completion bytes of BOTH CTAs go to the leader's barrier (peer bit cleared)
+          const uint32_t leader_bar = smem_u32(&full_bar[stage]) & 0xFEFFFFFFu;
+          tma_load_2d_pair(sa, &map_a, leader_bar, kb * kBlockK, m2 * 2 * kBlockM + static_cast<int>(rank) * kBlockM,
+                           kEvictNormal);
+          tma_load_2d_pair(sb, &map_b, leader_bar, kb * kBlockK, n_blk * kPairN + static_cast<int>(rank) * kBlockM,
+                           kEvictLast);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * kBlockM, kPairN);
+      int it = 0, astage = 0;
+      uint32_t aphase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += n_clusters) {
+        mbar_wait(&tmem_empty_bar[astage], aphase ^ 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(astage * kPairN);
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int stage = it % kPairStages;
+          const uint32_t phase = static_cast<uint32_t>(it / kPairStages) & 1u;
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(ring + stage * kPairStageBytes);
+          const uint64_t desc_a = umma_desc_k_sw128(sa);
+          const uint64_t desc_b = umma_desc_k_sw128(sa + kBlockM * kBlockK * 2);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            umma_bf16_ss_pair(tmem_d, desc_a + static_cast<uint64_t>(k * 2), desc_b + static_cast<uint64_t>(k * 2),
+                              idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_pair(&empty_bar[stage]);
+        }
+        umma_commit_pair(&tmem_full_bar[astage]);
+        if (++astage == kAccumStages) {
+          astage = 0;
+          aphase ^= 1u;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp - 4;
+    constexpr bool kF32Out = (EPI == kEpiBiasResidF32);
+    constexpr int kBoxCols = kF32Out ? 32 : 64;
+    const int row_in_tile = q * 32 + lane;
+    const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
+    int astage = 0, epi_box = 0;
+    uint32_t aphase = 0;
+    pdl_wait();
+    for (int tile = cluster_id; tile < num_tiles; tile += n_clusters) {
+      const int m2 = tile % num_m2, n_blk = tile / num_m2;
+      mbar_wait(&tmem_full_bar[astage], aphase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c0 = 0; c0 < kPairN; c0 += kBoxCols) {
+        const int f_box = n_blk * kPairN + c0;
+        if (f_box >= args.b_rows) break;
+        uint8_t* box = epi_stage + (epi_box & 1) * kEpiBoxBytes;
+        if (threadIdx.x == 128) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        uint8_t* row_ptr = box + row_in_tile * 128;
+#pragma unroll
+        for (int cc = 0; cc < kBoxCols; cc += 32) {
+          uint32_t r[32];
+          tmem_ld_cols<32>(tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                               static_cast<uint32_t>(astage * kPairN + c0 + cc), r);
+          tmem_ld_wait();
+          const int f0 = f_box + cc;
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            float v[8];
+            float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+            if (args.bias != nullptr && f0 + j + 7 < args.b_rows) {
+              b0 = __ldg(reinterpret_cast<const float4*>(args.bias + f0 + j));
+              b1 = __ldg(reinterpret_cast<const float4*>(args.bias + f0 + j + 4));
+            }
+            v[0] = __uint_as_float(r[j + 0]) + b0.x;
+            v[1] = __uint_as_float(r[j + 1]) + b0.y;
+            v[2] = __uint_as_float(r[j + 2]) + b0.z;
+            v[3] = __uint_as_float(r[j + 3]) + b0.w;
+            v[4] = __uint_as_float(r[j + 4]) + b1.x;
+            v[5] = __uint_as_float(r[j + 5]) + b1.y;
+            v[6] = __uint_as_float(r[j + 6]) + b1.z;
+            v[7] = __uint_as_float(r[j + 7]) + b1.w;
+            if (EPI == kEpiBiasGeluBf16) {
+#pragma unroll
+              for (int t = 0; t < 8; ++t) v[t] = gelu_new_fast(v[t]);
+            }
+            if (kF32Out) {
+              const uint32_t ch = static_cast<uint32_t>((cc + j) >> 2);
+              *reinterpret_cast<float4*>(row_ptr + (((ch + 0) ^ sw) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
+              *reinterpret_cast<float4*>(row_ptr + (((ch + 1) ^ sw) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
+            } else {
+              const uint32_t ch = static_cast<uint32_t>((cc + j) >> 3);
+              uint4 pk;
+              pk.x = pack_bf16x2(v[0], v[1]);
+              pk.y = pack_bf16x2(v[2], v[3]);
+              pk.z = pack_bf16x2(v[4], v[5]);
+              pk.w = pack_bf16x2(v[6], v[7]);
+              *reinterpret_cast<uint4*>(row_ptr + ((ch ^ sw) << 4)) = pk;
+            }
+          }
+        }
+        fence_proxy_async();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 128) {
+          const uint64_t desc = reinterpret_cast<uint64_t>(&map_out);
+          const uint32_t src = smem_u32(box);
+          const int crd0 = f_box, crd1 = m2 * 2 * kBlockM + static_cast<int>(rank) * kBlockM;
+          if (kF32Out) {
+            asm volatile(
+                "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];"
+                :
+                : "l"(desc), "r"(src), "r"(crd0), "r"(crd1)
+                : "memory");
+          } else {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                         :
+                         : "l"(desc), "r"(src), "r"(crd0), "r"(crd1)
+                         : "memory");
+          }
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        ++epi_box;
+      }
+      // this CTA's half of the accumulator is drained: tell the leader's MMA thread
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (leader) {
+          mbar_arrive(&tmem_empty_bar[astage]);
+        } else {
+          mbar_arrive_remote(&tmem_empty_bar[astage], 0);
+        }
+      }
+      if (++astage == kAccumStages) {
+        astage = 0;
+        aphase ^= 1u;
+      }
+    }
+    if (threadIdx.x == 128) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer may still be signalling into this CTA's barriers / reading TMEM
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // Host side: tensor maps + dispatch
 // ---------------------------------------------------------------------------------------
@@ -1102,6 +1378,50 @@ int dispatch_cluster(const GemmArgs& g, cudaStream_t stream) {
   }
 }
 
+
+template <int EPI>
+int launch_pair(const GemmArgs& g, cudaStream_t stream) {
+  CUtensorMap map_a, map_b, map_out;
+  const int act_rows = g.act_rows_alloc > 0 ? g.act_rows_alloc : g.tokens;
+  B200_PROPAGATE(get_tensor_map(g.act, act_rows, g.k, kBlockM, &map_a));
+  B200_PROPAGATE(get_tensor_map(g.w, g.features, g.k, kBlockM, &map_b));
+  B200_PROPAGATE(get_tensor_map(g.out, g.tokens, g.ld_out, kBlockM, &map_out, EPI == kEpiBiasResidF32 ? 4 : 2));
+  KernelArgs ka = {};
+  ka.bias = g.bias;
+  ka.out = g.out;
+  ka.a_rows = g.tokens;
+  ka.b_rows = g.features;
+  ka.k_blocks_total = g.k / kBlockK;
+  ka.k_blocks_per_split = ka.k_blocks_total;
+  ka.ld_out = g.ld_out;
+  ka.tokens = g.tokens;
+  ka.stages = kPairStages;
+  const int num_tiles = ((g.tokens + 2 * kBlockM - 1) / (2 * kBlockM)) * ((g.features + kPairN - 1) / kPairN);
+  const int max_clusters = num_sms() / 2;
+  const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
+
+  auto kernel = gemm_pair_kernel<EPI>;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPairSmemBytes));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * clusters, 1, 1);
+  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.dynamicSmemBytes = kPairSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = g.pdl ? 1 : 0;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, map_a, map_b, map_out, ka));
+  return kOk;
+}
+
 }  // namespace
 
 B200_DEFINE_STEP_TRACE_SETTER(step_trace_set_gemm)
@@ -1152,7 +1472,28 @@ int gemm_bf16(const GemmArgs& g, cudaStream_t stream) {
     if (g.tokens <= 128) return dispatch_epi<128, true>(g, stream);
     return dispatch_epi<256, true>(g, stream);
   }
-  // tokens on M. Wide N tiles when there is enough work to fill the machine.
+  // tokens on M. Large problems whose output can go through TMA use CTA pairs (UMMA M = 256).
+  {
+    const int eb = g.epilogue == kEpiBiasResidF32 ? 4 : 2;
+    const bool tma_ok = (reinterpret_cast<uintptr_t>(g.out) & 15u) == 0 &&
+                        (static_cast<size_t>(g.ld_out) * eb) % 16 == 0 &&
+                        (g.bias == nullptr || (reinterpret_cast<uintptr_t>(g.bias) & 15u) == 0);
+    const long pair_tiles = static_cast<long>((g.tokens + 255) / 256) * (g.features / 256);
+    const bool pair_epi = g.epilogue == kEpiBiasBf16 || g.epilogue == kEpiBiasGeluBf16 ||
+                          g.epilogue == kEpiBiasResidF32;
+    if (g.use_pair != 0 && tma_ok && pair_epi && g.features % 256 == 0 && g.split_k <= 1 &&
+        (g.use_pair > 0 || pair_tiles >= num_sms() / 2)) {
+      switch (g.epilogue) {
+        case kEpiBiasBf16:
+          return launch_pair<kEpiBiasBf16>(g, stream);
+        case kEpiBiasGeluBf16:
+          return launch_pair<kEpiBiasGeluBf16>(g, stream);
+        default:
+          return launch_pair<kEpiBiasResidF32>(g, stream);
+      }
+    }
+  }
+  // Otherwise single-CTA tiles; wide N tiles when there is enough work to fill the machine.
   const long tiles256 = static_cast<long>((g.tokens + 127) / 128) * ((g.features + 255) / 256);
   if (g.features % 256 == 0 && tiles256 >= num_sms()) return dispatch_epi<256, false>(g, stream);
   return dispatch_epi<128, false>(g, stream);

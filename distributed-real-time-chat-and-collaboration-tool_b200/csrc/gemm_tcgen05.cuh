@@ -44,6 +44,10 @@ struct GemmArgs {
   // > 1: swap-AB split-K over a thread-block cluster of this many CTAs, reduced through
   // distributed shared memory inside the kernel (deterministic; final epilogue applied)
   int cluster_split;
+  // tokens-on-M orientation: -1 = CTA pairs (cta_group::2, 256 x 256 tiles) when the problem is
+  // large enough, 0 = never, 1 = always when legal. Zero-initialised structs get "never"; the
+  // engine and the op-level ABI pass -1.
+  int use_pair;
 };
 
 // Enqueue one GEMM on `stream`. Returns 0 or an error code (see common.cuh Status).

@@ -179,7 +179,8 @@ int64_t b200llm_kernel_launches(const b200llm_engine* engine);
 
 /* out[token, feature] = sum_k act[token,k] * w[feature,k] (+ epilogue).  act [tokens,k] bf16,
  * w [features,k] bf16 (K-major), bias [features] fp32 or NULL. Conv1D: $TF/pytorch_utils.py:119-122.
- * orientation: -1 auto, 0 tokens on UMMA-M, 1 weights on UMMA-M (swap-AB, small batches).
+ * orientation: -1 auto, 0 tokens on UMMA-M with single-CTA tiles, 1 weights on UMMA-M (swap-AB,
+ *          small batches), 2 tokens on UMMA-M with CTA pairs (tcgen05 cta_group::2, 256x256 tiles).
  * split_k: 1 = none; n > 1 = n partial planes (B200LLM_EPI_PARTIAL_F32 only, the consumer reduces);
  *          -n = split K over a thread-block cluster of n CTAs (n <= 8) reduced on chip through
  *          distributed shared memory, with the normal bias / gelu / residual epilogue. */

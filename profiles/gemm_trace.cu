@@ -30,7 +30,7 @@ static void run(const char* name, int tokens, int features, int k, int epi, int 
   GemmArgs g = {};
   g.act = act; g.w = w; g.bias = bias; g.out = out; g.tokens = tokens; g.features = features; g.k = k;
   g.ld_out = features; g.epilogue = epi; g.split_k = split; g.act_rows_alloc = act_rows;
-  g.force_orientation = orient; g.pdl = 0; g.cluster_split = cluster;
+  g.force_orientation = orient == 2 ? 0 : orient; g.use_pair = orient == 2 ? 1 : 0; g.pdl = 0; g.cluster_split = cluster;
   float* amv = nullptr; int* ami = nullptr; float* eosl = nullptr;
   if (epi == kEpiLogitsArgmax) {
     const int groups = ((features + 127) / 128) * 4;
@@ -81,6 +81,11 @@ int main() {
   run("pf fc 8192x3072x768 gelu", 8192, 3072, 768, kEpiBiasGeluBf16, 1, 0, 0);
   run("pf proj 8192x768x768 resid", 8192, 768, 768, kEpiBiasResidF32, 1, 0, 0);
   run("pf proj2 8192x768x3072 resid", 8192, 768, 3072, kEpiBiasResidF32, 1, 0, 0);
+  printf("-- prefill orientation with CTA pairs (cta_group::2)\n");
+  run("pair qkv 8192x2304x768", 8192, 2304, 768, kEpiBiasBf16, 1, 0, 2);
+  run("pair fc 8192x3072x768 gelu", 8192, 3072, 768, kEpiBiasGeluBf16, 1, 0, 2);
+  run("pair proj 8192x768x768 resid", 8192, 768, 768, kEpiBiasResidF32, 1, 0, 2);
+  run("pair proj2 8192x768x3072", 8192, 768, 3072, kEpiBiasResidF32, 1, 0, 2);
   printf("-- cluster (DSMEM) split-K: ld0=staged in smem, ld1=after cluster barrier 1, epilogue end=before barrier 2\n");
   run("qkv cluster6", 64, 2304, 768, kEpiBiasBf16, 1, 6);
   run("proj cluster6", 64, 768, 768, kEpiBiasResidF32, 1, 6);

@@ -48,6 +48,33 @@ def test_gemm_bias_bf16(ops, cuda, tokens, features, k, orientation):
     assert err <= 2e-3 * scale + 2 ** -8 * scale, (err, scale)
 
 
+@pytest.mark.parametrize("tokens,features,k,epi", [
+    (8192, 2304, 768, "bias"),    # BASELINE config 2 prefill QKV: 288 pair tiles, persistent clusters
+    (512, 3072, 768, "gelu"),
+    (640, 768, 3072, "resid"),    # TMA reduce-add into the fp32 residual stream
+    (300, 768, 768, "resid"),     # ragged: the second CTA of the last pair has only out-of-range rows
+    (129, 1024, 1024, "bias"),
+])
+def test_gemm_cta_pair_umma(ops, cuda, tokens, features, k, epi):
+    """tcgen05.mma.cta_group::2: two CTAs share one 256 x 256 tile (orientation code 2)."""
+    act, w, bias = _gemm_inputs(tokens, features, k, cuda, seed=8)
+    ref = act.float() @ w.float().t() + bias
+    if epi == "resid":
+        resid = torch.randn(tokens, features, device=cuda)
+        out = resid.clone()
+        ops.gemm(act, w, bias, out, ops.EPI_BIAS_RESID_F32, orientation=2)
+        ref, got = ref + resid, out
+    else:
+        out = torch.zeros(tokens, features, dtype=torch.bfloat16, device=cuda)
+        ops.gemm(act, w, bias, out, ops.EPI_BIAS_GELU_BF16 if epi == "gelu" else ops.EPI_BIAS_BF16, orientation=2)
+        if epi == "gelu":
+            ref = gelu_new(ref)
+        got = out.float()
+    torch.cuda.synchronize()
+    scale = max(1.0, ref.abs().max().item())
+    assert (got - ref).abs().max().item() <= 1e-2 * scale
+
+
 @pytest.mark.parametrize("orientation,tokens", [(1, 64), (0, 512)])
 def test_gemm_gelu(ops, cuda, orientation, tokens):
     act, w, bias = _gemm_inputs(tokens, 3072, 768, cuda, seed=1)
