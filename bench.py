@@ -469,6 +469,8 @@ def run_reference(args):
     if rank != 0:
         return
     torch, H, hf, ids, (model, B, T, N) = _cpu_setup(args.workload)
+    shape = hf.config
+    shape.n_layer, shape.d_model = hf.config.n_layer, hf.config.n_embd
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     # size the per-step sample so that (K + W) steps end within ~150 s
@@ -493,8 +495,9 @@ def run_reference(args):
         "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: GPT-2 {model}, batch {B}, {T}-token prompts, {N} new tokens, greedy",
-                   "note": "CPU reference arm; rank 0 only"},
+        "config": {"workload": f"{args.workload}: GPT-2 {model} ({shape.n_layer}L d={shape.d_model}), batch {B} per GPU, "
+                               f"{T}-token prompts, {N} new tokens, greedy (BASELINE configs[1])",
+                   "note": "CPU reference arm (transformers on the host cores); rank 0 only"},
         "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,

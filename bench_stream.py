@@ -1,0 +1,183 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[4]: a mixed-length SmartReply / Summarize / Ask request stream through the
+gRPC llm.LLMService, served by the local B200 engine on 1..N GPUs of one box.
+
+    python bench_stream.py [--gpus N] [--requests R] [--rate REQ_PER_S] [--cpu-sample K]
+
+Stream: request kinds in ratio 6:1:3 (SmartReply : Summarize : Ask), Poisson arrivals
+(seed 99), conversations synthesised from a fixed sentence pool. Every request travels the whole
+drop-in path: gRPC stub -> LLMServicer (reference prompts/parsers) -> LocalGenerativeModel ->
+router -> per-GPU continuous-batching worker -> CUDA engine. Replicas only: the router shards
+requests, there is no collective. Prints ONE JSON line: p50/p95 latency per RPC, aggregate
+generated tokens/s, and (optionally) the same RPCs timed on the host CPU with transformers for a
+small sample.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import sys
+import threading
+import time
+from concurrent import futures
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "distributed-real-time-chat-and-collaboration-tool_b200"
+
+SENTENCES = [
+    "Are we still on for the design review at 3pm?", "Yes, I booked room 4B.", "Bring the latency numbers.",
+    "I can't make it before 3:30, start without me.", "Can you share the doc beforehand?", "Sure, sending it now.",
+    "The benchmark finished overnight.", "Throughput is up but p95 regressed a little.", "Let's look at the traces.",
+    "Who owns the rollout plan?", "I will draft it today.", "Please add the rollback steps.", "Sounds good to me.",
+    "The cache hit rate dropped after the deploy.", "Could be the new key format.", "I'll check the dashboards.",
+]
+USERS = ["alice", "bob", "charlie", "dave"]
+
+
+def make_requests(pb, n: int, seed: int = 99):
+    rng = np.random.default_rng(seed)
+    kinds = rng.choice(["smart", "summarize", "ask"], size=n, p=[0.6, 0.1, 0.3])
+    reqs = []
+    for i, kind in enumerate(kinds):
+        def msgs(k):
+            return [pb.Message(sender=USERS[int(rng.integers(len(USERS)))],
+                               content=SENTENCES[int(rng.integers(len(SENTENCES)))]) for _ in range(k)]
+        if kind == "smart":
+            reqs.append(("GetSmartReply", pb.SmartReplyRequest(request_id=str(i), recent_messages=msgs(5), user_id="bob")))
+        elif kind == "summarize":
+            reqs.append(("SummarizeConversation",
+                         pb.SummarizeRequest(request_id=str(i), messages=msgs(int(rng.integers(8, 14))), max_length=200)))
+        else:
+            ctx = [f"{m.sender}: {m.content}" for m in msgs(3)]
+            reqs.append(("GetLLMAnswer", pb.LLMRequest(request_id=str(i), query="What did we decide about the rollout?",
+                                                        context=ctx)))
+    return reqs
+
+
+class CountingModel:
+    """Wraps the generator to total the generated tokens (the RPC responses do not carry them)."""
+
+    def __init__(self, inner):
+        self.inner = inner
+        self.lock = threading.Lock()
+        self.generated = 0
+        self.prompt = 0
+
+    def generate_content(self, prompt, generation_config=None):
+        resp = self.inner.generate_content(prompt, generation_config=generation_config)
+        with self.lock:
+            self.generated += resp.usage["generated_tokens"]
+            self.prompt += resp.usage["prompt_tokens"]
+        return resp
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--requests", type=int, default=400)
+    ap.add_argument("--rate", type=float, default=0.0, help="Poisson arrival rate in requests/s (0 = closed loop)")
+    ap.add_argument("--clients", type=int, default=64, help="concurrent callers")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="also time this many requests per RPC on the host CPU")
+    args = ap.parse_args()
+
+    import grpc
+
+    server_mod = importlib.import_module(f"{PKG}.server")
+    svc = importlib.import_module(f"{PKG}.llm_service")
+    pb = importlib.import_module(f"{PKG}.llm_proto")
+
+    model = CountingModel(server_mod.build_local_model("small", args.gpus, max_seqs=64, max_seq_len=1024,
+                                                       max_new_tokens=160))
+    model.inner.default_max_new_tokens = 32        # SmartReply 32; Summarize overrides below; Ask passes 150
+    servicer = svc.LLMServicer(model)
+    server = grpc.server(futures.ThreadPoolExecutor(max_workers=max(args.clients, 8) + 8))
+    server_mod.add_llm_service(servicer, server)
+    port = server.add_insecure_port("127.0.0.1:0")
+    server.start()
+
+    reqs = make_requests(pb, args.requests)
+    rng = np.random.default_rng(99)
+    arrivals = np.cumsum(rng.exponential(1.0 / args.rate, size=len(reqs))) if args.rate > 0 else np.zeros(len(reqs))
+    lat: dict[str, list[float]] = {"GetSmartReply": [], "SummarizeConversation": [], "GetLLMAnswer": []}
+    lock = threading.Lock()
+
+    with grpc.insecure_channel(f"127.0.0.1:{port}") as ch:
+        stub = server_mod.LLMServiceStub(ch)
+        for rpc, req in reqs[:8]:  # warm-up (graph capture, tokenizer caches)
+            getattr(stub, rpc)(req, timeout=60)
+        model.generated = model.prompt = 0
+        t_start = time.perf_counter()
+
+        def call(i):
+            rpc, req = reqs[i]
+            delay = t_start + arrivals[i] - time.perf_counter()
+            if delay > 0:
+                time.sleep(delay)
+            t0 = time.perf_counter()
+            getattr(stub, rpc)(req, timeout=60)
+            with lock:
+                lat[rpc].append((time.perf_counter() - t0) * 1e3)
+
+        with futures.ThreadPoolExecutor(max_workers=args.clients) as pool:
+            list(pool.map(call, range(len(reqs))))
+        wall = time.perf_counter() - t_start
+    server.stop(0)
+    model.inner.router.shutdown()
+
+    out = {
+        "metric": "mixed SmartReply/Summarize/Ask stream through gRPC LLMService (BASELINE configs[4])",
+        "n_gpus": args.gpus, "requests": len(reqs), "arrival_rate_rps": args.rate or None, "clients": args.clients,
+        "wall_s": wall, "requests_per_s": len(reqs) / wall,
+        "generated_tokens_per_s": model.generated / wall, "prompt_tokens_per_s": model.prompt / wall,
+        "latency_ms": {k: {"n": len(v), "p50": float(np.percentile(v, 50)), "p95": float(np.percentile(v, 95))}
+                       for k, v in lat.items() if v},
+        "tokenizer": "byte-level GPT-2 ids (no vocab files offline): prompts are ~4x longer than with BPE",
+        "data": "synthetic conversations, random-init GPT-2 small",
+    }
+    if args.cpu_sample > 0:
+        out["cpu_latency_ms"] = cpu_sample(pb, svc, reqs, args.cpu_sample)
+    print(json.dumps(out))
+
+
+def cpu_sample(pb, svc, reqs, k: int) -> dict:
+    """The same RPC bodies on the host cores: transformers GPT2LMHeadModel.generate behind the same
+    servicer code (checker-side only; uses oracle/)."""
+    import torch
+
+    from oracle import gpt2_oracle as O
+    from oracle import hf_reference as H
+
+    tok = importlib.import_module(f"{PKG}.tokenizer").ByteLevelTokenizer()
+    lm = importlib.import_module(f"{PKG}.local_model")
+    torch.manual_seed(0)
+    torch.set_num_threads(os.cpu_count() or 1)
+    shape = O.GPT2Shape(**{**O.SMALL.__dict__, "n_positions": 2048})
+    hf = H.build_hf_model(shape, None, attn="sdpa")
+
+    class HfModel:
+        def generate_content(self, prompt, generation_config=None):
+            n = int((generation_config or {}).get("max_output_tokens", 32))
+            ids = torch.tensor([tok.encode(prompt)[-860:]])
+            toks = H.hf_generate(hf, ids, n, min_new_tokens=n)[0].tolist()
+            return lm.GenerateContentResponse(candidates=[lm.Candidate(2, lm.Content([lm.Part(tok.decode(toks))]))])
+
+    servicer = svc.LLMServicer(HfModel())
+    res: dict[str, list[float]] = {}
+    for rpc, req in reqs:
+        if len(res.setdefault(rpc, [])) >= k:
+            continue
+        t0 = time.perf_counter()
+        getattr(servicer, rpc)(req, None)
+        res[rpc].append((time.perf_counter() - t0) * 1e3)
+        if all(len(v) >= k for v in res.values()) and len(res) == 3:
+            break
+    return {r: {"n": len(v), "p50": float(np.percentile(v, 50))} for r, v in res.items()}
+
+
+if __name__ == "__main__":
+    main()

@@ -962,6 +962,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     int splits = 1;
     while (splits < 16 && ctas * splits < 4 * sms && max_ctx / (splits * 2) >= 64) splits *= 2;
     p.attn_splits = splits;
+    if (const char* env = std::getenv("B200LLM_ATTN_SPLITS")) p.attn_splits = std::max(1, std::min(16, std::atoi(env)));
   }
 
   if (!e->cfg.use_cuda_graphs) {

@@ -224,3 +224,28 @@ def test_medium_and_large_teacher_forced_logits(cuda, name):
     same_prefix = np.cumprod(np.concatenate([np.ones((B, 1), bool), out[:, :-1] == ref[:, :-1]], 1), 1).astype(bool)
     assert (out[same_prefix & (margins.numpy() > 2 * LOGIT_TOL)] == ref[same_prefix & (margins.numpy() > 2 * LOGIT_TOL)]).all()
     eng.close()
+
+
+def test_temperature_topk_sampling_matches_the_softmax_distribution(cuda):
+    """Distributional check: first sampled token over 4096 seeds vs
+    softmax(top-k logits / T) from the oracle. Total-variation distance must be small."""
+    w = O.synthetic_weights(TINY, seed=3)
+    eng, E = _engine(TINY, w, max_seqs=64, max_seq_len=32, max_batch_tokens=1024, max_new_tokens=2)
+    prompt = [5, 6, 7, 8]
+    T, K, n = 0.7, 8, 4096
+    logits = O.forward(TINY, w, torch.tensor([prompt]))[0, -1].double()
+    logits[TINY.eos_token_id] = -float("inf")          # min_new_tokens masks EOS
+    top = logits.topk(K)
+    probs = torch.softmax(top.values / T, dim=0).numpy()
+    counts = {int(i): 0 for i in top.indices}
+    for s0 in range(0, n, 64):
+        sp = [E.SamplingParams(max_new_tokens=1, min_new_tokens=1, temperature=T, top_k=K, seed=1000 + s0 + j)
+              for j in range(64)]
+        for toks in eng.generate([prompt] * 64, sp):
+            assert toks[0] in counts, "sampled token outside the oracle's top-k"
+            counts[toks[0]] += 1
+    emp = np.array([counts[int(i)] for i in top.indices]) / n
+    tv = 0.5 * np.abs(emp - probs).sum()
+    print(f"total-variation distance to softmax(top-{K}/T={T}): {tv:.4f}")
+    assert tv < 0.04            # ~3 sigma for 4096 draws over 8 outcomes
+    eng.close()
