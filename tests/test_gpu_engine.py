@@ -228,12 +228,18 @@ def test_medium_and_large_teacher_forced_logits(cuda, name):
 
 def test_temperature_topk_sampling_matches_the_softmax_distribution(cuda):
     """Distributional check: first sampled token over 4096 seeds vs
-    softmax(top-k logits / T) from the oracle. Total-variation distance must be small."""
+    softmax(top-k logits / T). Total-variation distance must be small."""
     w = O.synthetic_weights(TINY, seed=3)
     eng, E = _engine(TINY, w, max_seqs=64, max_seq_len=32, max_batch_tokens=1024, max_new_tokens=2)
     prompt = [5, 6, 7, 8]
     T, K, n = 0.7, 8, 4096
-    logits = O.forward(TINY, w, torch.tensor([prompt]))[0, -1].double()
+    # expected distribution from the ENGINE's own last-position logits (their parity with the
+    # oracle is gated elsewhere; near-ties at rank k would otherwise make the top-k sets differ)
+    slot = eng.seq_alloc(32)
+    eng.prefill([prompt], [slot])
+    logits = torch.from_numpy(eng.read_last_logits(1)[0]).double()
+    eng.seq_free(slot)
+    assert (logits - O.forward(TINY, w, torch.tensor([prompt]))[0, -1].double()).abs().max() <= 0.02
     logits[TINY.eos_token_id] = -float("inf")          # min_new_tokens masks EOS
     top = logits.topk(K)
     probs = torch.softmax(top.values / T, dim=0).numpy()
@@ -242,7 +248,7 @@ def test_temperature_topk_sampling_matches_the_softmax_distribution(cuda):
         sp = [E.SamplingParams(max_new_tokens=1, min_new_tokens=1, temperature=T, top_k=K, seed=1000 + s0 + j)
               for j in range(64)]
         for toks in eng.generate([prompt] * 64, sp):
-            assert toks[0] in counts, "sampled token outside the oracle's top-k"
+            assert toks[0] in counts, "sampled token outside the top-k"
             counts[toks[0]] += 1
     emp = np.array([counts[int(i)] for i in top.indices]) / n
     tv = 0.5 * np.abs(emp - probs).sum()
