@@ -255,3 +255,26 @@ def test_temperature_topk_sampling_matches_the_softmax_distribution(cuda):
     print(f"total-variation distance to softmax(top-{K}/T={T}): {tv:.4f}")
     assert tv < 0.04            # ~3 sigma for 4096 draws over 8 outcomes
     eng.close()
+
+
+def test_decode_batch_larger_than_one_umma_n_tile(cuda):
+    """More than 256 live sequences: decode GEMMs leave the swap-AB path (tokens on UMMA-M, no
+    split-K), the LM head runs several token tiles. Tokens must equal the small-batch run."""
+    w = O.synthetic_weights(TINY, seed=3)
+    B, T, N = 300, 6, 5
+    ids = O.synthetic_prompts(B, T, vocab=1000, seed=31)
+    sp_kw = dict(max_new_tokens=N, min_new_tokens=N)
+    big, E = _engine(TINY, w, max_seqs=320, max_seq_len=16, max_batch_tokens=2048, max_new_tokens=N)
+    got = np.array(big.generate(ids.tolist(), E.SamplingParams(**sp_kw)))
+    big.close()
+    small, _ = _engine(TINY, w, max_seqs=64, max_seq_len=16, max_batch_tokens=512, max_new_tokens=N)
+    ref = np.concatenate([np.array(small.generate(ids[i:i + 50].tolist(), E.SamplingParams(**sp_kw)))
+                          for i in range(0, B, 50)])
+    small.close()
+    oracle, _, margins = O.greedy_generate(TINY, w, ids[:16], N, min_new_tokens=N)
+    assert got.shape == (B, N)
+    # the two engine paths round differently (split-K planes vs single accumulation): compare where decisive
+    same_prefix = np.cumprod(np.concatenate([np.ones((16, 1), bool), got[:16, :-1] == oracle.numpy()[:, :-1]], 1), 1).astype(bool)
+    decisive = margins.numpy() > 0.05
+    assert (got[:16][same_prefix & decisive] == oracle.numpy()[same_prefix & decisive]).all()
+    assert (got == ref).mean() > 0.9
