@@ -21,13 +21,30 @@
 #ifdef B200_ATTN_TRACE
 // Profiling build only (profiles/attn_trace.cu): CTA 0 records SM-clock milestones.
 __device__ unsigned long long g_attn_trace[16];
+// ... and every CTA of the last launch records %globaltimer at entry / after the grid
+// dependency wait / at exit, plus the SM it ran on.
+__device__ unsigned long long g_attn_cta_trace[4096][4];
 #define B200_ATRACE(slot)                                                                  \
   do {                                                                                     \
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_attn_trace[slot] = clock64(); \
   } while (0)
+#define B200_ATRACE_CTA(which)                                                             \
+  do {                                                                                     \
+    if (threadIdx.x == 0 && blockIdx.y == 0 && blockIdx.x < 4096) {                        \
+      unsigned long long _t;                                                               \
+      unsigned int _sm;                                                                    \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t));                               \
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(_sm));                                     \
+      g_attn_cta_trace[blockIdx.x][which] = _t;                                            \
+      g_attn_cta_trace[blockIdx.x][3] = _sm;                                               \
+    }                                                                                      \
+  } while (0)
 #else
 #define B200_ATRACE(slot) \
   do {                    \
+  } while (0)
+#define B200_ATRACE_CTA(which) \
+  do {                         \
   } while (0)
 #endif
 
@@ -269,92 +286,30 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
 // ---------------------------------------------------------------------------------------
 // Decode
 // ---------------------------------------------------------------------------------------
-struct Softmax8 {
-  float m;     // running max (log2 domain)
-  float l;     // running sum
-  float o[8];  // running weighted V for this lane's 8 dims
-};
-
-__device__ __forceinline__ void merge_into(Softmax8& a, float m2, float l2, const float (&o2)[8]) {
-  const float m = fmaxf(a.m, m2);
-  const float f1 = (a.m == -INFINITY) ? 0.f : exp2f(a.m - m);
-  const float f2 = (m2 == -INFINITY) ? 0.f : exp2f(m2 - m);
-  a.l = a.l * f1 + l2 * f2;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) a.o[i] = a.o[i] * f1 + o2[i] * f2;
-  a.m = m;
-}
-
-__device__ __forceinline__ void bf16x8_to_float(const uint4& v, float (&f)[8]) {
-  float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y), c = unpack_bf16x2(v.z),
-         d = unpack_bf16x2(v.w);
-  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
-  f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
-}
-
-constexpr int kDecUnroll = 3;
+// One CTA per (row, head, KV split), 4 warps. The CTA's cached K/V rows are staged in shared
+// memory 128 tokens at a time (the first 128 before the grid dependency resolves) and both
+// products run on the tensor cores: a single query only fills one row of an m16n8k16 tile, but
+// the kernel is bound by instruction issue, not by math, and the MMA form needs ~5x fewer
+// instructions per cached token than a CUDA-core dot product per lane group.
+//   scores:  D[16 x 8 tokens] = A[16 x 16 dims] * B[16 dims x 8 tokens]
+//            A row 0 = q (bf16 high part), row 8 = q - high part (low part): lanes 0..3 hold both
+//            rows, so c0 + c2 is the score with q at ~fp32 precision;  B = K rows via ldmatrix.
+//   output:  D[16 dims x 8] = A[16 dims x 16 tokens] * B[16 tokens x 8]
+//            A = V^T via ldmatrix.trans;  B column 0 = softmax weights, which sit in lanes 0..3 in
+//            exactly the layout the score tile left them in.  Column 0 of D is the result.
 constexpr int kScratchStride = kHeadDim + 2;  // o[64], m, l
 constexpr int kMaxSmemPages = 256;            // page ids staged in smem (4096 tokens)
-constexpr int kStageTokens = 128;             // cached tokens staged in smem per CTA (32 KB)
-
-struct KvBatch {
-  uint4 k[kDecUnroll];
-  uint4 v[kDecUnroll];
-};
+constexpr int kStageTokens = 128;             // K/V rows staged per pass (32 KB)
+constexpr int kWarpTokens = kStageTokens / 4; // rows of a pass one warp attends
+constexpr int kTailRows = 32;                 // rows of the second pass prefetched into registers
 
 __device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src)
                : "memory");
 }
-__device__ __forceinline__ void cp_async_commit_wait_all() {
-  asm volatile("cp.async.commit_group;" ::: "memory");
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-}
-
-// Online-softmax update with N cached tokens at once: the N dot products, their shuffle
-// reductions and exponentials are independent, so one pass through the dependent chain
-// (max -> rescale -> accumulate) serves N tokens instead of one.
-template <int N>
-__device__ __forceinline__ void attend_tokens(Softmax8& acc, const float (&q)[8], const uint4 (&kraw)[N],
-                                              const uint4 (&vraw)[N], const bool (&valid)[N]) {
-  float s[N];
-#pragma unroll
-  for (int n = 0; n < N; ++n) {
-    float kf[8];
-    bf16x8_to_float(kraw[n], kf);
-    float d = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) d = fmaf(q[i], kf[i], d);
-    s[n] = d;
-  }
-#pragma unroll
-  for (int o = 1; o <= 4; o <<= 1) {
-#pragma unroll
-    for (int n = 0; n < N; ++n) s[n] += __shfl_xor_sync(0xffffffffu, s[n], o);
-  }
-  float m = acc.m;
-#pragma unroll
-  for (int n = 0; n < N; ++n) m = valid[n] ? fmaxf(m, s[n]) : m;
-  if (m == -INFINITY) return;  // nothing valid yet (uniform within the 8-lane group)
-  const float f = (acc.m == -INFINITY) ? 0.f : exp2f(acc.m - m);
-  float p[N];
-  float psum = 0.f;
-#pragma unroll
-  for (int n = 0; n < N; ++n) {
-    p[n] = valid[n] ? exp2f(s[n] - m) : 0.f;
-    psum += p[n];
-  }
-  acc.l = acc.l * f + psum;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) acc.o[i] *= f;
-#pragma unroll
-  for (int n = 0; n < N; ++n) {
-    float vf[8];
-    bf16x8_to_float(vraw[n], vf);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) acc.o[i] = fmaf(p[n], vf[i], acc.o[i]);
-  }
-  acc.m = m;
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&v);
 }
 
 // Ordering argument for everything this kernel does BEFORE griddepcontrol.wait.
@@ -364,16 +319,19 @@ __device__ __forceinline__ void attend_tokens(Softmax8& acc, const float (&q)[8]
 // can therefore only be running if this step's embed kernel has passed its wait, which means the
 // previous step's selector -- and with it the whole previous step -- is complete and visible:
 // seq_len / finished are final, and KV positions < seq_len (written by earlier steps) are
-// immutable. Only the QKV projection of THIS step is not ready. So the whole cached KV stream is
-// fetched before the wait and overlaps the QKV GEMM.
+// immutable. Only the QKV projection of THIS step is not ready. So the cached KV rows are
+// fetched before the wait and overlap the QKV GEMM.
+//
+// Stage layout: row = token (64 bf16 = 8 chunks of 16 B); chunk c of row r is stored at chunk
+// position c ^ (r & 7), which makes every ldmatrix phase (8 rows x 16 B) conflict-free.
 __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   __shared__ float sm_o[4][kHeadDim];
   __shared__ float sm_ml[4][2];
   __shared__ int32_t sm_pages[kMaxSmemPages];
-  __shared__ __align__(16) float sm_q[kHeadDim];              // this token's q (pre-scaled)
+  __shared__ __align__(16) __nv_bfloat16 sm_q[2][kHeadDim];   // this token's q: high / low bf16 parts
   __shared__ __align__(16) __nv_bfloat16 sm_kv[2][kHeadDim];  // this token's k, v (cache dtype)
-  __shared__ __align__(16) uint4 sm_k[kStageTokens][8];       // staged cached K rows
-  __shared__ __align__(16) uint4 sm_v[kStageTokens][8];       // staged cached V rows
+  __shared__ __align__(16) uint4 sm_k[kStageTokens][8];       // staged K rows (swizzled chunks)
+  __shared__ __align__(16) uint4 sm_v[kStageTokens][8];       // staged V rows (swizzled chunks)
 
   const int bh = blockIdx.x;
   const int b = bh / a.n_head;
@@ -381,10 +339,9 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   const int split = blockIdx.y;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int sub = lane & 7;                // which 16-byte chunk (8 dims) of the 128-byte row
-  const int grp = warp * 4 + (lane >> 3);  // 0..15: token within the 16-token page
   const int d = a.n_head * kHeadDim;
   B200_ATRACE(0);
+  B200_ATRACE_CTA(0);
   B200_STEP_BEGIN(5);
 
   const int slot = a.active_slots ? a.active_slots[b] : b;
@@ -412,9 +369,12 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   int chunk = (ctx + a.n_splits - 1) / a.n_splits;
   chunk = ((chunk + kPageTokens - 1) / kPageTokens) * kPageTokens;
   const int t_begin = split * chunk;
-  const int t_end = min(ctx, t_begin + chunk);        // may include `pos` (the new token)
-  const int t_cached_end = min(t_end, pos);           // cached tokens only
-  const int n_staged = max(0, min(t_cached_end - t_begin, kStageTokens));
+  const int t_end = min(ctx, t_begin + chunk);           // may include `pos` (the new token)
+  const int n_tok = max(0, t_end - t_begin);             // rows this CTA attends
+  const int n_cached = max(0, min(t_end, pos) - t_begin);  // of which already in the cache
+  const bool own_new = pos >= t_begin && pos < t_end;    // then n_tok == n_cached + 1
+  const int new_pass = (n_cached / kStageTokens) * kStageTokens;  // pass holding the new token's row
+  const int new_row = n_cached - new_pass;
 
   auto page_of = [&](int tpos) -> int {
     const int pi = tpos / kPageTokens;
@@ -423,50 +383,69 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   auto kv_offset = [&](int tpos) -> size_t {
     return ((static_cast<size_t>(page_of(tpos)) * a.n_head + h) * kPageTokens + tpos % kPageTokens) * kHeadDim;
   };
-  // (1) the first kStageTokens cached tokens: global -> shared with cp.async, no registers held
-  for (int i = threadIdx.x; i < n_staged * 16; i += blockDim.x) {
-    const int tok = i >> 4, part = i & 15;
-    const size_t off = kv_offset(t_begin + tok) + (part & 7) * 8;
-    if (part < 8) {
-      cp_async_16(&sm_k[tok][part], a.k_pool + off);
-    } else {
-      cp_async_16(&sm_v[tok][part - 8], a.v_pool + off);
-    }
-  }
-  asm volatile("cp.async.commit_group;" ::: "memory");
-  // (2) the remaining tokens stream through registers; their first batch is requested now and
-  //     the rest is pulled into L2
-  const int t_rest = t_begin + n_staged;
-  auto load_batch = [&](int base, KvBatch& kb) {
+  // Stage the rows of the pass that starts at CTA-relative token p0: cached rows by cp.async, and
+  // zeros into the V rows of the last 16-row tile that hold no token (0 * garbage must not be NaN).
+  // The new token's row is written by nobody here; it is filled from sm_kv after the wait.
+  uint4 tail_k[2], tail_v[2];  // rows 128..159 of the CTA's range, fetched before the wait (below)
+  auto stage_pass = [&](int p0) {
+    const int rows_cached = max(0, min(n_cached - p0, kStageTokens));
+    int first_async = 0;
+    if (p0 == kStageTokens) {  // these rows are already in registers
+      first_async = kTailRows;
 #pragma unroll
-    for (int u = 0; u < kDecUnroll; ++u) {
-      const int tpos = base + u * kPageTokens + grp;
-      kb.k[u] = make_uint4(0u, 0u, 0u, 0u);
-      kb.v[u] = make_uint4(0u, 0u, 0u, 0u);
-      if (tpos < t_cached_end) {
-        const size_t off = kv_offset(tpos) + sub * 8;
-        kb.k[u] = ld_nc_v4(a.k_pool + off);
-        kb.v[u] = ld_nc_v4(a.v_pool + off);
+      for (int k = 0; k < 2; ++k) {
+        const int row = (threadIdx.x >> 3) + 16 * k, c = threadIdx.x & 7;
+        if (row < rows_cached) {
+          sm_k[row][c ^ (row & 7)] = tail_k[k];
+          sm_v[row][c ^ (row & 7)] = tail_v[k];
+        }
       }
     }
-  };
-  KvBatch cur;
-  load_batch(t_rest, cur);
-  if (sub < 2) {
-    const __nv_bfloat16* pool = sub == 0 ? a.k_pool : a.v_pool;
-    for (int tpos = t_rest + kPageTokens * kDecUnroll + grp; tpos < t_cached_end; tpos += kPageTokens) {
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(pool + kv_offset(tpos)));
+    for (int i = first_async * 16 + threadIdx.x; i < rows_cached * 16; i += blockDim.x) {
+      const int row = i >> 4, part = i & 15, c = part & 7;
+      const size_t off = kv_offset(t_begin + p0 + row) + c * 8;
+      if (part < 8) {
+        cp_async_16(&sm_k[row][c ^ (row & 7)], a.k_pool + off);
+      } else {
+        cp_async_16(&sm_v[row][c ^ (row & 7)], a.v_pool + off);
+      }
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    const int rows_pass = min(n_tok - p0, kStageTokens);
+    const int first_empty = rows_cached + ((own_new && new_pass == p0) ? 1 : 0);
+    const int rows_tiles = ((rows_pass + 15) / 16) * 16;
+    for (int i = first_empty * 8 + threadIdx.x; i < rows_tiles * 8; i += blockDim.x) {
+      sm_v[i >> 3][i & 7] = make_uint4(0u, 0u, 0u, 0u);
+    }
+  };
+  stage_pass(0);
+  // The first rows of the second pass wait in registers (a context a little over 128 tokens is the
+  // common case for short prompts); anything beyond is pulled into L2 now and staged later.
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int r = kStageTokens + (threadIdx.x >> 3) + 16 * k;
+    tail_k[k] = make_uint4(0u, 0u, 0u, 0u);
+    tail_v[k] = make_uint4(0u, 0u, 0u, 0u);
+    if (r < n_cached) {
+      const size_t off = kv_offset(t_begin + r) + (threadIdx.x & 7) * 8;
+      tail_k[k] = ld_nc_v4(a.k_pool + off);
+      tail_v[k] = ld_nc_v4(a.v_pool + off);
+    }
+  }
+  for (int r = kStageTokens + kTailRows + (threadIdx.x >> 1); r < n_cached; r += 64) {
+    const __nv_bfloat16* pool = (threadIdx.x & 1) ? a.v_pool : a.k_pool;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(pool + kv_offset(t_begin + r)));
   }
 
   B200_ATRACE(1);
   pdl_wait();
   pdl_launch_dependents();
   B200_ATRACE(2);
+  B200_ATRACE_CTA(1);
 
   // This token's q/k/v. With a split-K projection the CTA reduces the fp32 partial planes
-  // (fixed summation order -> deterministic), adds the bias, keeps q in fp32 and rounds k/v to
-  // the cache dtype; everyone then reads them from shared memory.
+  // (fixed summation order -> deterministic) and adds the bias. q (scaled for exp2) is split into
+  // two bf16 parts, k/v are rounded to the cache dtype; everyone reads them from shared memory.
   {
     float val[2] = {rbias[0], rbias[1]};
     if (a.qkv_partials != nullptr) {
@@ -505,9 +484,17 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
       if (vi < 3 * kHeadDim) {
         const int part = vi >> 6, dim = vi & 63;
         if (part == 0) {
-          sm_q[dim] = val[r] * kScaleLog2;
+          const float x = val[r] * kScaleLog2;
+          const __nv_bfloat16 hi = __float2bfloat16(x);
+          sm_q[0][dim] = hi;
+          sm_q[1][dim] = __float2bfloat16(x - __bfloat162float(hi));
         } else {
-          sm_kv[part - 1][dim] = __float2bfloat16(val[r]);
+          const __nv_bfloat16 v16 = __float2bfloat16(val[r]);
+          sm_kv[part - 1][dim] = v16;
+          if (own_new && new_pass == 0) {  // single-pass case: straight into its stage row
+            uint4* rowp = part == 1 ? &sm_k[new_row][(dim >> 3) ^ (new_row & 7)] : &sm_v[new_row][(dim >> 3) ^ (new_row & 7)];
+            reinterpret_cast<__nv_bfloat16*>(rowp)[dim & 7] = v16;
+          }
         }
       }
     }
@@ -517,82 +504,136 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   B200_ATRACE(8);
   __syncthreads();
   B200_ATRACE(4);
-  float q[8];
-  {
-    const float4 q0 = *reinterpret_cast<const float4*>(&sm_q[sub * 8]);
-    const float4 q1 = *reinterpret_cast<const float4*>(&sm_q[sub * 8 + 4]);
-    q[0] = q0.x; q[1] = q0.y; q[2] = q0.z; q[3] = q0.w;
-    q[4] = q1.x; q[5] = q1.y; q[6] = q1.z; q[7] = q1.w;
-  }
-  const uint4 k_new = *reinterpret_cast<const uint4*>(&sm_kv[0][sub * 8]);
-  const uint4 v_new = *reinterpret_cast<const uint4*>(&sm_kv[1][sub * 8]);
 
   // append this token to its page (the split that owns position `pos` does it)
-  if (pos >= t_begin && pos < t_end && !fin && warp == 0 && lane < 8) {
-    const size_t dst = kv_offset(pos) + sub * 8;
-    *reinterpret_cast<uint4*>(a.k_pool + dst) = k_new;
-    *reinterpret_cast<uint4*>(a.v_pool + dst) = v_new;
+  if (own_new && !fin && threadIdx.x < 16) {
+    const int c = threadIdx.x & 7;
+    const size_t dst = kv_offset(pos) + c * 8;
+    __nv_bfloat16* pool = threadIdx.x < 8 ? a.k_pool : a.v_pool;
+    *reinterpret_cast<uint4*>(pool + dst) = *reinterpret_cast<const uint4*>(&sm_kv[threadIdx.x >> 3][c * 8]);
   }
 
-  Softmax8 acc;
-  acc.m = -INFINITY;
-  acc.l = 0.f;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) acc.o[i] = 0.f;
+  // q as the A operand: lanes 0..3 carry row 0 (high part) and row 8 (low part), all others zero
+  auto load_q = [&](uint32_t (&qa)[4], int s) {
+    const int j2 = 2 * (lane & 3);
+    const bool on = lane < 4;
+    qa[0] = on ? *reinterpret_cast<const uint32_t*>(&sm_q[0][16 * s + j2]) : 0u;
+    qa[1] = on ? *reinterpret_cast<const uint32_t*>(&sm_q[1][16 * s + j2]) : 0u;
+    qa[2] = on ? *reinterpret_cast<const uint32_t*>(&sm_q[0][16 * s + 8 + j2]) : 0u;
+    qa[3] = on ? *reinterpret_cast<const uint32_t*>(&sm_q[1][16 * s + 8 + j2]) : 0u;
+  };
 
-  // staged tokens (shared memory; a warp's 4 groups read 4 consecutive 128-byte rows), 4 at a time
-  // (trip count is CTA-uniform: the shuffles inside need every lane of the warp)
-  for (int it0 = 0; it0 < n_staged; it0 += 4 * kPageTokens) {
-    uint4 kk[4], vv[4];
-    bool ok[4];
+  float m_run = -INFINITY;  // warp-uniform running max (log2 domain)
+  float l_part = 0.f;       // this lane's share of the running sum (lanes 0..3 matter)
+  float oacc[4][4];
 #pragma unroll
-    for (int n = 0; n < 4; ++n) {
-      const int i = it0 + grp + n * kPageTokens;
-      ok[n] = i < n_staged;
-      const int ii = ok[n] ? i : 0;
-      kk[n] = sm_k[ii][sub];
-      vv[n] = sm_v[ii][sub];
+  for (int mt = 0; mt < 4; ++mt) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) oacc[mt][e] = 0.f;
+  }
+
+  for (int p0 = 0; p0 < n_tok; p0 += kStageTokens) {  // CTA-uniform trip count
+    if (p0 > 0) {
+      __syncthreads();  // every warp is done with the previous pass's rows
+      stage_pass(p0);
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      if (own_new && new_pass == p0 && threadIdx.x < 16) {
+        const int c = threadIdx.x & 7;
+        uint4* dstp = threadIdx.x < 8 ? &sm_k[new_row][c ^ (new_row & 7)] : &sm_v[new_row][c ^ (new_row & 7)];
+        *dstp = *reinterpret_cast<const uint4*>(&sm_kv[threadIdx.x >> 3][c * 8]);
+      }
+      __syncthreads();
     }
-    attend_tokens<4>(acc, q, kk, vv, ok);
-  }
-  // streamed tokens; the new token rides along with the last batch
-  const bool own_new = pos >= t_begin && pos < t_end;
-  bool new_done = !own_new;
-  for (int base = t_rest; base < t_cached_end || !new_done; base += kPageTokens * kDecUnroll) {
-    if (base != t_rest && base < t_cached_end) load_batch(base, cur);
-    uint4 kk[kDecUnroll + 1], vv[kDecUnroll + 1];
-    bool ok[kDecUnroll + 1];
+    const int rows_pass = min(n_tok - p0, kStageTokens);
+    const int w0 = warp * kWarpTokens;
+    if (w0 < rows_pass) {  // warp-uniform
+      float sacc[4][4];
 #pragma unroll
-    for (int u = 0; u < kDecUnroll; ++u) {
-      kk[u] = cur.k[u];
-      vv[u] = cur.v[u];
-      ok[u] = base + u * kPageTokens + grp < t_cached_end;
+      for (int t = 0; t < 4; ++t) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) sacc[t][e] = 0.f;
+      }
+#pragma unroll
+      for (int sp = 0; sp < 2; ++sp) {  // 32 dims per ldmatrix.x4
+        uint32_t qa0[4], qa1[4];
+        load_q(qa0, 2 * sp);
+        load_q(qa1, 2 * sp + 1);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {   // 8 tokens per score tile
+          uint32_t kb[4];
+          const int row = w0 + 8 * t + (lane & 7);
+          const int c = 4 * sp + (lane >> 3);
+          ldmatrix_x4(kb, &sm_k[row][c ^ (row & 7)]);
+          mma_bf16_16816(sacc[t], qa0, kb[0], kb[1]);
+          mma_bf16_16816(sacc[t], qa1, kb[2], kb[3]);
+        }
+      }
+      float s[4][2];
+      bool ok[4][2];
+      float m_loc = -INFINITY;
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          ok[t][e] = lane < 4 && (w0 + 8 * t + 2 * (lane & 3) + e) < rows_pass;
+          s[t][e] = sacc[t][e] + sacc[t][e + 2];
+          m_loc = ok[t][e] ? fmaxf(m_loc, s[t][e]) : m_loc;
+        }
+      }
+      m_loc = fmaxf(m_loc, __shfl_xor_sync(0xffffffffu, m_loc, 1));
+      m_loc = fmaxf(m_loc, __shfl_xor_sync(0xffffffffu, m_loc, 2));
+      m_loc = __shfl_sync(0xffffffffu, m_loc, 0);  // lanes 0..3 own the real scores
+      const float m_new = fmaxf(m_run, m_loc);     // finite: row w0 of this pass is a real token
+      if (m_run != -INFINITY) {                    // warp-uniform
+        const float f = exp2f(m_run - m_new);
+        l_part *= f;
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) oacc[mt][e] *= f;
+        }
+      }
+      m_run = m_new;
+      float p[4][2];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          p[t][e] = ok[t][e] ? exp2f(s[t][e] - m_new) : 0.f;
+          l_part += p[t][e];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {  // 16 tokens per output tile
+        if (w0 + 16 * u < rows_pass) {  // warp-uniform; rows past the last 16-row tile are never read
+          const uint32_t b0 = pack_bf16x2(p[2 * u][0], p[2 * u][1]);
+          const uint32_t b1 = pack_bf16x2(p[2 * u + 1][0], p[2 * u + 1][1]);
+#pragma unroll
+          for (int mt = 0; mt < 4; ++mt) {  // 16 dims per tile
+            uint32_t va[4];
+            const int row = w0 + 16 * u + ((lane >> 4) << 3) + (lane & 7);
+            const int c = 2 * mt + ((lane >> 3) & 1);
+            ldmatrix_x4_trans(va, &sm_v[row][c ^ (row & 7)]);
+            mma_bf16_16816(oacc[mt], va, b0, b1);
+          }
+        }
+      }
     }
-    const bool last = base + kPageTokens * kDecUnroll >= t_cached_end;
-    kk[kDecUnroll] = k_new;
-    vv[kDecUnroll] = v_new;
-    ok[kDecUnroll] = last && own_new && grp == 0;
-    attend_tokens<kDecUnroll + 1>(acc, q, kk, vv, ok);
-    if (last) new_done = true;
   }
-
   B200_ATRACE(5);
-  // merge the 4 token groups of this warp (lanes differing in bits 3 and 4)
+
+  // per-warp result -> shared: column 0 of the output tiles lives in lanes 0, 4, ..., 28
+  float l_warp = l_part + __shfl_xor_sync(0xffffffffu, l_part, 1);
+  l_warp += __shfl_xor_sync(0xffffffffu, l_warp, 2);
+  if ((lane & 3) == 0) {
 #pragma unroll
-  for (int off = 8; off <= 16; off <<= 1) {
-    const float m2 = __shfl_xor_sync(0xffffffffu, acc.m, off);
-    const float l2 = __shfl_xor_sync(0xffffffffu, acc.l, off);
-    float o2[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) o2[i] = __shfl_xor_sync(0xffffffffu, acc.o[i], off);
-    merge_into(acc, m2, l2, o2);
-  }
-  if (lane < 8) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) sm_o[warp][sub * 8 + i] = acc.o[i];
+    for (int mt = 0; mt < 4; ++mt) {
+      sm_o[warp][16 * mt + (lane >> 2)] = oacc[mt][0];
+      sm_o[warp][16 * mt + 8 + (lane >> 2)] = oacc[mt][2];
+    }
     if (lane == 0) {
-      sm_ml[warp][0] = acc.m;
-      sm_ml[warp][1] = acc.l;
+      sm_ml[warp][0] = m_run;
+      sm_ml[warp][1] = l_warp;
     }
   }
   __syncthreads();
@@ -620,6 +661,7 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
     }
   }
   B200_ATRACE(6);
+  B200_ATRACE_CTA(2);
   B200_STEP_END();
 }
 
@@ -728,6 +770,13 @@ B200_DEFINE_STEP_TRACE_SETTER(step_trace_set_attention)
 // Profiling builds only: read CTA 0's milestone timestamps of the last decode_attn_kernel launch.
 extern "C" int b200llm_debug_attn_trace(unsigned long long* out16) {
   return cudaMemcpyFromSymbol(out16, g_attn_trace, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : 2;
+}
+extern "C" int b200llm_debug_attn_cta_trace(unsigned long long* out, int n_ctas) {
+  if (n_ctas > 4096) n_ctas = 4096;
+  return cudaMemcpyFromSymbol(out, g_attn_cta_trace, static_cast<size_t>(n_ctas) * 4 * sizeof(unsigned long long)) ==
+                 cudaSuccess
+             ? 0
+             : 2;
 }
 namespace b200llm {
 #endif

@@ -17,6 +17,7 @@
 //   workspace residual stream x fp32 [rows,d]; h / qkv / attn / ffn bf16; logits fp32
 //             [max_batch_rows, V]; split-K partial planes; split-KV attention scratch.
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -240,12 +241,18 @@ int pick_cluster(int features, int k, int sms) {
 }
 
 // Largest divisor s of k_blocks with tiles * s <= sms and s <= cap.
+// Split-K factor of a decode GEMM. Every plane costs the consuming kernel (LayerNorm, attention,
+// gelu-reduce) one more fp32 read per element on the step's critical path, while the weight
+// stream of a CTA is prefetched before its grid dependency resolves; so a CTA keeps at least
+// max(3, kb/8) k-blocks (sweeps in profiles/README.md), and the split never exceeds `cap` planes
+// or the SM count.
 int pick_split(int features, int k, int sms, int cap) {
   const int tiles = (features + 127) / 128;
   const int kb = k / 64;
+  const int min_kb = kb / 8 > 3 ? kb / 8 : 3;
   int best = 1;
   for (int s = 1; s <= kb && s <= cap; ++s) {
-    if (kb % s == 0 && tiles * s <= sms) best = s;
+    if (kb % s == 0 && tiles * s <= sms && kb / s >= min_kb) best = s;
   }
   return best;
 }
@@ -955,6 +962,14 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     p.split_p = pick_split(e->d, 4 * e->d, sms, cap);
     p.split_qkv = pick_split(3 * e->d, e->d, sms, cap);
     p.split_fc = pick_split(4 * e->d, e->d, sms, cap);
+  }
+  if (const char* env = std::getenv("B200LLM_SPLITS")) {  // tuning aid: "qkv,o,fc,proj" (0 keeps the pick)
+    int v[4] = {0, 0, 0, 0};
+    std::sscanf(env, "%d,%d,%d,%d", &v[0], &v[1], &v[2], &v[3]);
+    if (v[0] > 0) p.split_qkv = v[0];
+    if (v[1] > 0) p.split_o = v[1];
+    if (v[2] > 0) p.split_fc = v[2];
+    if (v[3] > 0) p.split_p = v[3];
   }
   // split-KV when (rows x heads) alone cannot fill the machine and contexts are long
   {

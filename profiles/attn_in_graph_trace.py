@@ -35,4 +35,17 @@ for steps in (4, 12):
     d["reduce loads done (t0)"] = int(t[7] - t[0])
     d["cp.async drained (t0)"] = int(t[8] - t[0])
     print("cycles from CTA start:", d)
+    nb = B * shape.n_head
+    ct = (C.c_ulonglong * (4 * nb))()
+    L.lib.b200llm_debug_attn_cta_trace.argtypes = [C.c_void_p, C.c_int]
+    assert L.lib.b200llm_debug_attn_cta_trace(ct, nb) == 0
+    r = np.array(ct[:], dtype=np.int64).reshape(nb, 4)
+    t0 = r[:, 0].min()
+    ent, dep, ext, sm = (r[:, 0] - t0) / 1e3, (r[:, 1] - t0) / 1e3, (r[:, 2] - t0) / 1e3, r[:, 3]
+    q = lambda x: "min %.2f p50 %.2f p90 %.2f max %.2f" % (x.min(), np.percentile(x, 50), np.percentile(x, 90), x.max())
+    print("all CTAs of the last launch, us from first entry:\n  entry  ", q(ent), "\n  dep ok ", q(dep), "\n  exit   ", q(ext))
+    late = ent > dep.min()
+    print("  CTAs entering after the dependency resolved: %d of %d; per-SM CTA count min/max %d/%d on %d SMs" % (
+        late.sum(), nb, np.bincount(sm).min(), np.bincount(sm).max(), len(np.unique(sm))))
+    print("  post-dependency time (exit - dep ok):", q(ext - dep))
 eng.close()

@@ -42,8 +42,8 @@ def test_missing_library_fails_loudly(tmp_path, monkeypatch):
 
     spec = importlib.util.spec_from_file_location("_lib_copy", os.path.join(PKG_DIR, "_lib.py"))
     mod = importlib.util.module_from_spec(spec)
-    src = open(os.path.join(PKG_DIR, "_lib.py"), encoding="utf-8").read().replace(
-        'LIB_PATH = HERE / "libb200llm.so"', f'LIB_PATH = Path(r"{tmp_path}") / "libb200llm.so"')
+    monkeypatch.setenv("B200LLM_LIB", str(tmp_path / "libb200llm.so"))  # a path with no library
+    src = open(os.path.join(PKG_DIR, "_lib.py"), encoding="utf-8").read()
     try:
         exec(compile(src, "_lib_copy.py", "exec"), mod.__dict__ | {"__file__": os.path.join(PKG_DIR, "_lib.py")})
     except ImportError as exc:
