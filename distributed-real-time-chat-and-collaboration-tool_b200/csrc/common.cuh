@@ -304,7 +304,7 @@ __device__ __forceinline__ void pdl_launch_dependents() {
 // ---------------------------------------------------------------------------------------
 #ifdef B200_STEP_TRACE
 struct StepTraceSink {
-  unsigned long long* buf;  // [2 * capacity]: begin, end
+  unsigned long long* buf;  // [16 * capacity] records
   unsigned int* idx;
   unsigned int capacity;
 };
@@ -314,18 +314,28 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+// Record layout (16 x u64): [0] entry, [1] exit, [2] tag, [4 + i] milestone i (B200_STEP_MARK).
 #define B200_STEP_BEGIN(tag)                                                                  \
+  __shared__ unsigned int _st_slot_sh;                                                        \
   unsigned int _st_slot = 0xffffffffu;                                                        \
-  if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 &&            \
-      g_step_trace.buf != nullptr) {                                                          \
-    _st_slot = atomicAdd(g_step_trace.idx, 1u);                                               \
-    if (_st_slot < g_step_trace.capacity) {                                                   \
-      g_step_trace.buf[3 * _st_slot] = global_timer_ns();                                     \
-      g_step_trace.buf[3 * _st_slot + 2] = (tag);                                             \
+  if (threadIdx.x == 0) {                                                                     \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && g_step_trace.buf != nullptr) { \
+      _st_slot = atomicAdd(g_step_trace.idx, 1u);                                             \
+      if (_st_slot < g_step_trace.capacity) {                                                 \
+        g_step_trace.buf[16 * _st_slot] = global_timer_ns();                                  \
+        g_step_trace.buf[16 * _st_slot + 2] = (tag);                                          \
+      }                                                                                       \
     }                                                                                         \
+    _st_slot_sh = _st_slot;                                                                   \
   }
 #define B200_STEP_END()                                                                       \
-  if (_st_slot < g_step_trace.capacity) g_step_trace.buf[3 * _st_slot + 1] = global_timer_ns();
+  if (_st_slot < g_step_trace.capacity) g_step_trace.buf[16 * _st_slot + 1] = global_timer_ns();
+// any thread of block 0, after a __syncthreads() that follows B200_STEP_BEGIN
+#define B200_STEP_MARK(i)                                                                     \
+  do {                                                                                        \
+    const unsigned int _s = _st_slot_sh;                                                      \
+    if (_s < g_step_trace.capacity) g_step_trace.buf[16 * _s + 4 + (i)] = global_timer_ns();  \
+  } while (0)
 #define B200_DEFINE_STEP_TRACE_SETTER(fn)                                                     \
   void fn(unsigned long long* buf, unsigned int* idx, unsigned int capacity) {                \
     StepTraceSink s{buf, idx, capacity};                                                      \
@@ -334,6 +344,9 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 #else
 #define B200_STEP_BEGIN(tag)
 #define B200_STEP_END()
+#define B200_STEP_MARK(i) \
+  do {                    \
+  } while (0)
 #define B200_DEFINE_STEP_TRACE_SETTER(fn)
 #endif
 

@@ -199,6 +199,7 @@ struct b200llm_engine {
   // Profiling aid (env B200LLM_SKIP, bit mask): drop a class of kernels from the decode step to
   // read its in-graph cost by difference. Results are garbage when set; never set in tests.
   int skip_mask = 0;
+  int act_via_tma = 0;  // B200LLM_ACT_TMA=1: decode GEMMs fetch activations through TMA (comparison aid)
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
 };
 
@@ -303,6 +304,7 @@ int gemm(b200llm_engine* e, const __nv_bfloat16* act, const __nv_bfloat16* w, co
   g.act_rows_alloc = e->max_rows;
   g.force_orientation = -1;
   g.pdl = pdl;
+  g.act_via_tma = e->act_via_tma;
   if (e->skip_mask & kSkipGemm) return kOk;
   return count(e, gemm_bf16(g, e->stream));
 }
@@ -489,6 +491,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
   s.top_k = e->top_k;
   s.seed = e->seed;
   s.advance_seq = p.decode ? 1 : 0;
+  s.pdl = pdl;
   if (!(e->skip_mask & kSkipSelect)) B200_PROPAGATE(count(e, select_tokens(s, e->stream)));
   return kOk;
 }
@@ -553,6 +556,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   std::unique_ptr<b200llm_engine> e(new b200llm_engine());
   e->cfg = *cfg;
   if (const char* skip = std::getenv("B200LLM_SKIP")) e->skip_mask = std::atoi(skip);
+  if (const char* at = std::getenv("B200LLM_ACT_TMA")) e->act_via_tma = std::atoi(at);
   if (const char* pair = std::getenv("B200LLM_PAIR")) e->pair_mode = std::atoi(pair);
   e->d = cfg->d_model;
   e->H = cfg->n_head;
@@ -1161,7 +1165,7 @@ int64_t b200llm_kernel_launches(const b200llm_engine* e) { return e ? e->launche
 
 #ifdef B200_STEP_TRACE
 // Profiling builds only. op 0: arm (allocates a buffer of `capacity` records, resets the counter);
-// op 1: read back up to `capacity` records of (begin ns, end ns, tag) and return the count.
+// op 1: read back up to `capacity` 16-word records (entry ns, exit ns, tag, -, milestones...) and return the count.
 int b200llm_debug_step_trace(int op, unsigned long long* out, int capacity) {
   static unsigned long long* buf = nullptr;
   static unsigned int* idx = nullptr;
@@ -1169,11 +1173,11 @@ int b200llm_debug_step_trace(int op, unsigned long long* out, int capacity) {
   if (op == 0) {
     if (buf == nullptr) {
       cap = capacity;
-      cudaMalloc(&buf, static_cast<size_t>(cap) * 3 * sizeof(unsigned long long));
+      cudaMalloc(&buf, static_cast<size_t>(cap) * 16 * sizeof(unsigned long long));
       cudaMalloc(&idx, sizeof(unsigned int));
     }
     cudaMemset(idx, 0, sizeof(unsigned int));
-    cudaMemset(buf, 0, static_cast<size_t>(cap) * 3 * sizeof(unsigned long long));
+    cudaMemset(buf, 0, static_cast<size_t>(cap) * 16 * sizeof(unsigned long long));
     b200llm::step_trace_set_gemm(buf, idx, cap);
     b200llm::step_trace_set_ops(buf, idx, cap);
     b200llm::step_trace_set_attention(buf, idx, cap);
@@ -1183,7 +1187,7 @@ int b200llm_debug_step_trace(int op, unsigned long long* out, int capacity) {
   cudaMemcpy(&n, idx, sizeof(n), cudaMemcpyDeviceToHost);
   if (static_cast<int>(n) > capacity) n = capacity;
   if (static_cast<int>(n) > cap) n = cap;
-  cudaMemcpy(out, buf, static_cast<size_t>(n) * 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+  cudaMemcpy(out, buf, static_cast<size_t>(n) * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
   return static_cast<int>(n);
 }
 #endif

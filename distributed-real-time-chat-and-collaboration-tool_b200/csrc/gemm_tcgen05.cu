@@ -36,6 +36,12 @@ __device__ unsigned long long g_gemm_trace[16];
   do {                                                                     \
     if (blockIdx.x == 0 && blockIdx.y == 0) g_gemm_trace[slot] = clock64(); \
   } while (0)
+#elif defined(B200_STEP_TRACE)
+// in-pipeline timeline build: the same milestones go into this launch's step-trace record
+#define B200_TRACE(slot)                                              \
+  do {                                                                \
+    if (blockIdx.x == 0 && blockIdx.y == 0) B200_STEP_MARK(slot);     \
+  } while (0)
 #else
 #define B200_TRACE(slot) \
   do {                   \
@@ -81,6 +87,10 @@ struct KernelArgs {
   int ld_amax;
   int eos_id;
   int stages;  // smem ring depth actually allocated (<= TileCfg::kMaxStages)
+  // Swapped orientation with every k-block of the CTA resident in the ring (decode GEMMs): all
+  // operand tiles complete on full_bar[0], the MMA thread waits once and issues one uninterrupted
+  // chain (the per-k-block wait + fence + commit costs more than the MMAs of a 16..64-token tile).
+  int single_pass;
 };
 
 template <int N>
@@ -132,8 +142,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) B200_TRACE(0);
   B200_STEP_BEGIN(100 + EPI);
+  if (threadIdx.x == 0) B200_TRACE(0);
 
   const int num_m_blocks = (args.a_rows + kBlockM - 1) / kBlockM;
   const int num_n_blocks = (args.b_rows + BLOCK_N - 1) / BLOCK_N;
@@ -186,13 +196,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       // dependency resolves (programmatic dependent launch), so the weight stream of this
       // GEMM overlaps the tail of the previous kernel. The activation operand must wait.
       const int pre = TRANS ? (total_iters < kStages ? total_iters : kStages) : 0;
+      const bool single = TRANS && args.single_pass != 0;  // host guarantees total_iters <= kStages
+      if (single) mbar_arrive_expect_tx(&full_bar[0], static_cast<uint32_t>(total_iters) * Cfg::kStageBytes);
       for (int it = 0; it < pre; ++it) {
         const int tile = blockIdx.x + (it / num_kb) * gridDim.x;
         const int kb = kb_begin + it % num_kb;
         const int m_blk = tile % num_m_blocks;
         uint8_t* sa = ring + it * Cfg::kStageBytes;
-        mbar_arrive_expect_tx(&full_bar[it], Cfg::kStageBytes);
-        tma_load_2d(sa, &map_a, &full_bar[it], kb * kBlockK, m_blk * kBlockM, kEvictFirst);
+        if (!single) mbar_arrive_expect_tx(&full_bar[it], Cfg::kStageBytes);
+        tma_load_2d(sa, &map_a, &full_bar[single ? 0 : it], kb * kBlockK, m_blk * kBlockM, kEvictFirst);
       }
       B200_TRACE(2);
       pdl_wait();
@@ -202,7 +214,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         const int kb = kb_begin + it % num_kb;
         const int n_blk = tile / num_m_blocks;
         uint8_t* sb = ring + it * Cfg::kStageBytes + Cfg::kABytes;
-        tma_load_2d(sb, &map_b, &full_bar[it], kb * kBlockK, n_blk * BLOCK_N, kEvictLast);
+        tma_load_2d(sb, &map_b, &full_bar[single ? 0 : it], kb * kBlockK, n_blk * BLOCK_N, kEvictLast);
       }
       for (int it = pre; it < total_iters; ++it) {
         const int stage = it % kStages;
@@ -232,9 +244,38 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         mbar_wait(&tmem_empty_bar[astage], aphase ^ 1u);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(astage * BLOCK_N);
+        if (TRANS && args.single_pass != 0) {
+          // (a CTA has at most one tile per ring slot group here; `it` counts its k-blocks so far)
+          const int it0 = ((tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x)) * num_kb;
+          if (it0 == 0) {
+            mbar_wait(&full_bar[0], 0);
+            B200_TRACE(4);
+            B200_TRACE(11);
+            tc_fence_after();
+          }
+          uint64_t desc_a = umma_desc_k_sw128(smem_u32(ring + it0 * Cfg::kStageBytes));
+          uint64_t desc_b = umma_desc_k_sw128(smem_u32(ring + it0 * Cfg::kStageBytes + Cfg::kABytes));
+          for (int kb = 0; kb < num_kb; ++kb) {
+#pragma unroll
+            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+              umma_bf16_ss(tmem_d, desc_a + static_cast<uint64_t>(k * 2), desc_b + static_cast<uint64_t>(k * 2),
+                           idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            }
+            desc_a += static_cast<uint64_t>(Cfg::kStageBytes >> 4);
+            desc_b += static_cast<uint64_t>(Cfg::kStageBytes >> 4);
+          }
+          umma_commit(&tmem_full_bar[astage]);
+          B200_TRACE(5);
+          if (++astage == kAccumStages) {
+            astage = 0;
+            aphase ^= 1u;
+          }
+          continue;
+        }
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           if (kb == 0) B200_TRACE(4);
+          if (kb == num_kb - 1) B200_TRACE(11);
           tc_fence_after();
           const uint32_t sa = smem_u32(ring + stage * Cfg::kStageBytes);
           const uint32_t sb = sa + Cfg::kABytes;
@@ -611,6 +652,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
   if (threadIdx.x == 64) B200_TRACE(8);
+  B200_STEP_END();
 }
 
 
@@ -673,6 +715,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  B200_STEP_BEGIN(110 + EPI);
   if (threadIdx.x == 0) B200_TRACE(0);
   const uint32_t rank = cluster_ctarank();
   const uint32_t csize = cluster_nctarank();
@@ -838,6 +881,7 @@ gemm_cluster_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
   if (threadIdx.x == 64) B200_TRACE(8);
+  B200_STEP_END();
 }
 
 
@@ -1243,6 +1287,7 @@ int launch(const GemmArgs& g, cudaStream_t stream) {
   int stages = iters_per_cta < Cfg::kMaxStages ? iters_per_cta : Cfg::kMaxStages;
   if (stages < 2) stages = 2;
   ka.stages = stages;
+  ka.single_pass = (TRANS && iters_per_cta <= stages && !g.act_via_tma) ? 1 : 0;
 
   auto kernel = gemm_kernel<BLOCK_N, EPI, TRANS, TMA_EPI>;
   constexpr int kEpiBytes = TMA_EPI ? 2 * kEpiBoxBytes : 0;

@@ -48,6 +48,9 @@ struct GemmArgs {
   // large enough, 0 = never, 1 = always when legal. Zero-initialised structs get "never"; the
   // engine and the op-level ABI pass -1.
   int use_pair;
+  // swap-AB launches whose CTAs keep all their k-blocks in the ring copy the activation operand
+  // with ordinary loads; 1 forces the TMA path for it (A/B comparisons, tests)
+  int act_via_tma;
 };
 
 // Enqueue one GEMM on `stream`. Returns 0 or an error code (see common.cuh Status).

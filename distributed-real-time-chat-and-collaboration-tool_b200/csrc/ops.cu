@@ -67,12 +67,31 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
   return warp_sum(t);
 }
 
+__device__ __forceinline__ float2 block_sum2(float a, float b, float2* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  if (lane == 0) red[warp] = make_float2(a, b);
+  __syncthreads();
+  float2 t = (lane < nwarps) ? red[lane] : make_float2(0.f, 0.f);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    t.x += __shfl_xor_sync(0xffffffffu, t.x, o);
+    t.y += __shfl_xor_sync(0xffffffffu, t.y, o);
+  }
+  return t;
+}
+
 __global__ void __launch_bounds__(512)
 layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int n_partials,
                  const float* __restrict__ add_bias, const float* __restrict__ gamma,
                  const float* __restrict__ beta, const int32_t* __restrict__ row_index,
                  __nv_bfloat16* __restrict__ out, int d, int rows_total, float eps) {
-  __shared__ float red[32];
+  __shared__ float2 red2[32];
   B200_STEP_BEGIN(1);
   // This kernel reads nothing mutable before its dependency wait, so the next kernel (a GEMM
   // that starts by prefetching weights) may be launched as soon as this one is resident.
@@ -117,14 +136,24 @@ layernorm_kernel(float* __restrict__ x, const float* __restrict__ partials, int 
       xr[c] = v;
     }
   }
+  // One block reduction for both moments. The second moment is taken about the row's first
+  // element (every thread reads the same word), so a large common offset cannot cancel
+  // catastrophically in E[(x-c)^2] - (E[x-c])^2.
   const float inv_d = 1.0f / static_cast<float>(d);
-  const float mean = block_sum((v.x + v.y) + (v.z + v.w), red) * inv_d;
-  float sq = 0.f;
+  __shared__ float shift_s;
+  if (threadIdx.x == 0) shift_s = v.x;
+  __syncthreads();
+  const float shift = shift_s;
+  float s1 = 0.f, s2 = 0.f;
   if (active) {
-    const float a0 = v.x - mean, a1 = v.y - mean, a2 = v.z - mean, a3 = v.w - mean;
-    sq = (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
+    const float a0 = v.x - shift, a1 = v.y - shift, a2 = v.z - shift, a3 = v.w - shift;
+    s1 = (a0 + a1) + (a2 + a3);
+    s2 = (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
   }
-  const float var = block_sum(sq, red) * inv_d;
+  const float2 tot = block_sum2(s1, s2, red2);
+  const float dm = tot.x * inv_d;  // mean - shift
+  const float mean = shift + dm;
+  const float var = fmaxf(tot.y * inv_d - dm * dm, 0.f);
   const float rstd = 1.0f / sqrtf(var + eps);
   if (active) {
     uint2 pk;
@@ -537,9 +566,10 @@ int reduce_bias_gelu(const float* partials, int n_partials, int partial_rows, co
 
 int select_tokens(const SelectArgs& a, cudaStream_t stream) {
   B200_CHECK_ARG(a.batch > 0 && a.vocab > 0, "select: bad shape");
-  select_kernel<<<a.batch, 1024, 0, stream>>>(a);
-  B200_CUDA_OK(cudaGetLastError());
-  return kOk;
+  // all-greedy steps only reduce the LM head's group candidates: a small CTA has the shorter
+  // reduction tree; sampling scans the whole logits row and wants every thread it can get
+  const int threads = (a.logits == nullptr && a.amax_val != nullptr) ? 256 : 1024;
+  return launch_pdl(select_kernel, dim3(a.batch), dim3(threads), stream, a.pdl, a);
 }
 
 int argmax_rows(const float* logits, int rows, int ld, int vocab, int32_t* out,

@@ -70,6 +70,7 @@ struct SelectArgs {
   const int32_t* top_k;
   const uint64_t* seed;
   int advance_seq;               // 1: decode step (cache grew by one token), 0: after prefill
+  int pdl;                       // launch with programmatic stream serialization
 };
 // Greedy: argmax over fp32 logits, ties to the lowest index (generation/utils.py:2762,2793);
 // finished rows emit pad (:2796-2797); EOS marks a row finished (stopping_criteria.py:450-471).

@@ -1,7 +1,7 @@
 """Timeline of one decode step inside the CUDA-graph + PDL pipeline (trace build):
     python <pkg>/build.py --trace
     B200LLM_LIB=<pkg>/libb200llm_trace.so python profiles/step_timeline.py [workload]
-Each record is (entry, exit) of block 0 / thread 0 of a kernel, %globaltimer ns, in launch order."""
+Each record is (entry, exit, tag, milestones...) of block 0 of a kernel, %globaltimer ns, in launch order."""
 import ctypes as C
 import importlib
 import os
@@ -35,9 +35,10 @@ cap = 4096
 assert fn(0, None, cap) == 0
 eng.decode(slots, 3)
 eng.sync()
-buf = (C.c_ulonglong * (3 * cap))()
+buf = (C.c_ulonglong * (16 * cap))()
 n = fn(1, buf, cap)
-rec = np.array(buf[: 3 * n], dtype=np.int64).reshape(n, 3)
+full = np.array(buf[: 16 * n], dtype=np.int64).reshape(n, 16)
+rec = full[:, :3]
 t0 = rec[0, 0]
 per_step = n // 3
 print(f"{n} kernel records, {per_step} per step; step = {(rec[per_step, 0] - rec[0, 0]) / 1e3:.1f} us")
@@ -45,6 +46,9 @@ step = rec[per_step: 2 * per_step]  # the middle step
 base = step[0, 0]
 agg = {}
 prev_end = None
+marks = full[per_step: 2 * per_step, 4:]
+MARK_NAMES = ["entry", "triggered", "weights issued", "dep ok", "1st k-block landed", "mma committed", "epi sees acc",
+              "stores done", "dealloc", "epi ld done", "epi 2nd half", "last k-block landed"]
 for i, (b, e, tag) in enumerate(step):
     nxt = step[i + 1, 0] if i + 1 < len(step) else rec[2 * per_step, 0]
     name = TAGS.get(int(tag), str(tag))
@@ -52,8 +56,10 @@ for i, (b, e, tag) in enumerate(step):
     a[0] += 1
     a[1] += (e - b) / 1e3          # entry -> exit of CTA 0
     a[2] += (nxt - b) / 1e3        # entry -> next kernel's entry (pipeline pitch)
-    if i < 16:
+    if 8 <= i < 26:
         print(f"{i:3d} {name:22s} entry {(b - base) / 1e3:8.2f} us  exit {(e - base) / 1e3:8.2f} us  dur {(e - b) / 1e3:6.2f}")
+        if name.startswith("gemm"):
+            print("      " + "  ".join(f"{MARK_NAMES[j]} {(m - base) / 1e3:.2f}" for j, m in enumerate(marks[i]) if m > 0))
 print("per kernel class in one step: count, sum CTA0 duration us, sum entry-to-next-entry us")
 for k, a in sorted(agg.items(), key=lambda kv: -kv[1][2]):
     print(f"  {k:22s} {a[0]:4d} {a[1]:9.1f} {a[2]:9.1f}")
