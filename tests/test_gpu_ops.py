@@ -243,6 +243,8 @@ def test_prefill_attention(ops, cuda, lens, n_head):
 @pytest.mark.parametrize("ctx_lens,n_head,n_splits", [
     ([0, 1, 15, 16, 17, 159, 160], 12, 1),
     ([127] * 8, 12, 1),
+    # several 128-row staging passes in one CTA, incl. the register-held head of the 2nd pass
+    ([126, 127, 128, 129, 143, 144, 160, 161, 255, 256, 257, 511, 640], 12, 1),
     ([1100, 3, 64, 700], 16, 4),
     ([1100, 3, 64, 700], 16, 16),
     ([300, 299], 20, 2),
