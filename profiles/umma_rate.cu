@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(unsigned long long* out, i
       for (int kb = 0; kb < kblocks; ++kb) {
         if (mode & 2) {  // wait on an (already complete) full barrier + fence, like the GEMM's k-loop
           mbar_wait(&ready_bar[kb & 15], 0);
-          tc_fence_after();
+          if (!(mode & 4)) tc_fence_after();
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_bf16_ss(tmem, da + k * 2, db + k * 2, idesc, (kb > 0 || k > 0) ? 1u : 0u);
@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(unsigned long long* out, i
 template <int N>
 void run(unsigned long long* d) {
   cudaFuncSetAttribute(rate_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-  for (int mode : {0, 1, 2, 3})
+  for (int mode : {0, 1, 2, 3, 6, 7})
   for (int kblocks : {3, 8}) {
     rate_kernel<N><<<1, 128, 64 * 1024>>>(d, 4, kblocks, mode);
     unsigned long long h[8];
@@ -92,7 +92,7 @@ void run(unsigned long long* d) {
 int main() {
   unsigned long long* d;
   cudaMalloc(&d, 64 * sizeof(unsigned long long));
-  printf("mode bit 0: tcgen05.commit after every k-block; bit 1: mbarrier wait + fence before every k-block\n");
+  printf("mode bit 0: tcgen05.commit after every k-block; bit 1: mbarrier wait + fence before every k-block; bit 2: wait without the fence\n");
   run<64>(d);
   run<256>(d);
   return 0;
