@@ -179,11 +179,12 @@ struct b200llm_engine {
 
   // decode graphs
   struct GraphKey {
-    int bucket, splits, logits;
+    int bucket, splits, logits, steps;
     bool operator<(const GraphKey& o) const {
       if (bucket != o.bucket) return bucket < o.bucket;
       if (splits != o.splits) return splits < o.splits;
-      return logits < o.logits;
+      if (logits != o.logits) return logits < o.logits;
+      return steps < o.steps;
     }
   };
   struct GraphEntry {
@@ -199,6 +200,7 @@ struct b200llm_engine {
   // Profiling aid (env B200LLM_SKIP, bit mask): drop a class of kernels from the decode step to
   // read its in-graph cost by difference. Results are garbage when set; never set in tests.
   int skip_mask = 0;
+  int steps_per_graph = 4;  // decode steps captured per CUDA graph (B200LLM_STEPS_PER_GRAPH overrides)
   int act_via_tma = 0;  // B200LLM_ACT_TMA=1: decode GEMMs fetch activations through TMA (comparison aid)
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
 };
@@ -557,6 +559,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   e->cfg = *cfg;
   if (const char* skip = std::getenv("B200LLM_SKIP")) e->skip_mask = std::atoi(skip);
   if (const char* at = std::getenv("B200LLM_ACT_TMA")) e->act_via_tma = std::atoi(at);
+  if (const char* sg = std::getenv("B200LLM_STEPS_PER_GRAPH")) e->steps_per_graph = std::max(1, std::min(32, std::atoi(sg)));
   if (const char* pair = std::getenv("B200LLM_PAIR")) e->pair_mode = std::atoi(pair);
   e->d = cfg->d_model;
   e->H = cfg->n_head;
@@ -953,8 +956,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   p.store_logits = need_logits;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.device);
-  // auto: 12 planes at most -- measured optimum (more planes cost the reducing kernel more than
-  // the extra CTAs save the GEMM; profiles/split_sweep.py)
+  // auto: pick_split's rule, never more than 12 planes
   const int cap = e->cfg.decode_split_k == 0 ? 12 : std::min(e->cfg.decode_split_k, 32);
   if (bucket <= 256 && cap > 1 && e->cfg.decode_reduce == 2) {
     p.cl_qkv = pick_cluster(3 * e->d, e->d, sms);
@@ -987,35 +989,57 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   if (!e->cfg.use_cuda_graphs) {
     for (int i = 0; i < n_steps; ++i) B200_PROPAGATE(decode_step_launches(e, p));
   } else {
-    b200llm_engine::GraphKey key{bucket, p.attn_splits, need_logits ? 1 : 0};
-    auto it = e->graphs.find(key);
-    if (it == e->graphs.end()) {
-      cudaGraph_t graph = nullptr;
-      const int64_t launches_before = e->launches;
-      e->launches_in_capture = 0;
-      B200_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-      int rc = decode_step_launches(e, p);
-      cudaError_t cerr = cudaStreamEndCapture(st, &graph);
-      e->launches = launches_before;  // captured, not executed
-      if (rc != kOk) {
-        if (graph) cudaGraphDestroy(graph);
-        return rc;
+    // Steps are captured in groups: inside a graph the selector -> embed edge of two consecutive
+    // steps is a programmatic edge (~1 us), between two graph launches it is a full drain + launch
+    // (~4 us). The remainder runs on the single-step graph.
+    auto get_graph = [&](int steps, b200llm_engine::GraphEntry** out) -> int {
+      b200llm_engine::GraphKey key{bucket, p.attn_splits, need_logits ? 1 : 0, steps};
+      auto it = e->graphs.find(key);
+      if (it == e->graphs.end()) {
+        cudaGraph_t graph = nullptr;
+        const int64_t launches_before = e->launches;
+        e->launches_in_capture = 0;
+        B200_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int rc = kOk;
+        for (int i = 0; i < steps && rc == kOk; ++i) rc = decode_step_launches(e, p);
+        cudaError_t cerr = cudaStreamEndCapture(st, &graph);
+        e->launches = launches_before;  // captured, not executed
+        if (rc != kOk) {
+          if (graph) cudaGraphDestroy(graph);
+          return rc;
+        }
+        if (cerr != cudaSuccess) {
+          return fail(kErrCuda, std::string("decode: graph capture failed: ") + cudaGetErrorString(cerr));
+        }
+        b200llm_engine::GraphEntry entry;
+        entry.kernels = e->launches_in_capture;
+        cerr = cudaGraphInstantiate(&entry.exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (cerr != cudaSuccess) {
+          return fail(kErrCuda, std::string("decode: graph instantiate failed: ") + cudaGetErrorString(cerr));
+        }
+        it = e->graphs.emplace(key, entry).first;
       }
-      if (cerr != cudaSuccess) {
-        return fail(kErrCuda, std::string("decode: graph capture failed: ") + cudaGetErrorString(cerr));
+      *out = &it->second;
+      return kOk;
+    };
+    const int group = e->steps_per_graph;
+    int done = 0;
+    if (group > 1 && n_steps >= group) {
+      b200llm_engine::GraphEntry* g = nullptr;
+      B200_PROPAGATE(get_graph(group, &g));
+      for (; done + group <= n_steps; done += group) {
+        B200_CUDA_OK(cudaGraphLaunch(g->exec, st));
+        e->launches += g->kernels;
       }
-      b200llm_engine::GraphEntry entry;
-      entry.kernels = e->launches_in_capture;
-      cerr = cudaGraphInstantiate(&entry.exec, graph, 0);
-      cudaGraphDestroy(graph);
-      if (cerr != cudaSuccess) {
-        return fail(kErrCuda, std::string("decode: graph instantiate failed: ") + cudaGetErrorString(cerr));
-      }
-      it = e->graphs.emplace(key, entry).first;
     }
-    for (int i = 0; i < n_steps; ++i) {
-      B200_CUDA_OK(cudaGraphLaunch(it->second.exec, st));
-      e->launches += it->second.kernels;
+    if (done < n_steps) {
+      b200llm_engine::GraphEntry* g = nullptr;
+      B200_PROPAGATE(get_graph(1, &g));
+      for (; done < n_steps; ++done) {
+        B200_CUDA_OK(cudaGraphLaunch(g->exec, st));
+        e->launches += g->kernels;
+      }
     }
   }
   for (int b = 0; b < batch; ++b) {
