@@ -233,8 +233,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer (single thread) =================
-    if (lane == 0) {
+    // ================= MMA issuer =================
+    // The whole warp runs the loop (waits, descriptor arithmetic: all warp-uniform) and one elected
+    // lane issues. Issuing from inside an `if (lane == 0)` region instead makes the compiler wrap
+    // every tcgen05 instruction in its own elect/branch sequence: ~25 % more cycles per k-block
+    // (profiles/umma_rate.cu), and the issue loop, not the tensor pipe, is what a 16..64-token
+    // tile waits for.
+    {
       constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N);
       int stage = 0;
       uint32_t phase = 0;
@@ -249,23 +254,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           const int it0 = ((tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x)) * num_kb;
           if (it0 == 0) {
             mbar_wait(&full_bar[0], 0);
-            B200_TRACE(4);
-            B200_TRACE(11);
+            if (lane == 0) {
+              B200_TRACE(4);
+              B200_TRACE(11);
+            }
             tc_fence_after();
           }
-          uint64_t desc_a = umma_desc_k_sw128(smem_u32(ring + it0 * Cfg::kStageBytes));
-          uint64_t desc_b = umma_desc_k_sw128(smem_u32(ring + it0 * Cfg::kStageBytes + Cfg::kABytes));
-          for (int kb = 0; kb < num_kb; ++kb) {
+          if (elect_one()) {
+            uint64_t desc_a = umma_desc_k_sw128(smem_u32(ring + it0 * Cfg::kStageBytes));
+            uint64_t desc_b = umma_desc_k_sw128(smem_u32(ring + it0 * Cfg::kStageBytes + Cfg::kABytes));
+            for (int kb = 0; kb < num_kb; ++kb) {
 #pragma unroll
-            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-              umma_bf16_ss(tmem_d, desc_a + static_cast<uint64_t>(k * 2), desc_b + static_cast<uint64_t>(k * 2),
-                           idesc, (kb > 0 || k > 0) ? 1u : 0u);
+              for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                umma_bf16_ss(tmem_d, desc_a + static_cast<uint64_t>(k * 2), desc_b + static_cast<uint64_t>(k * 2),
+                             idesc, (kb > 0 || k > 0) ? 1u : 0u);
+              }
+              desc_a += static_cast<uint64_t>(Cfg::kStageBytes >> 4);
+              desc_b += static_cast<uint64_t>(Cfg::kStageBytes >> 4);
             }
-            desc_a += static_cast<uint64_t>(Cfg::kStageBytes >> 4);
-            desc_b += static_cast<uint64_t>(Cfg::kStageBytes >> 4);
+            umma_commit(&tmem_full_bar[astage]);
           }
-          umma_commit(&tmem_full_bar[astage]);
-          B200_TRACE(5);
+          __syncwarp();
+          if (lane == 0) B200_TRACE(5);
           if (++astage == kAccumStages) {
             astage = 0;
             aphase ^= 1u;
@@ -274,28 +284,34 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         }
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
-          if (kb == 0) B200_TRACE(4);
-          if (kb == num_kb - 1) B200_TRACE(11);
+          if (lane == 0) {
+            if (kb == 0) B200_TRACE(4);
+            if (kb == num_kb - 1) B200_TRACE(11);
+          }
           tc_fence_after();
           const uint32_t sa = smem_u32(ring + stage * Cfg::kStageBytes);
           const uint32_t sb = sa + Cfg::kABytes;
           const uint64_t desc_a = umma_desc_k_sw128(sa);
           const uint64_t desc_b = umma_desc_k_sw128(sb);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in 16-byte units
-            umma_bf16_ss(tmem_d, desc_a + static_cast<uint64_t>(k * 2),
-                         desc_b + static_cast<uint64_t>(k * 2), idesc,
-                         (kb > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+              // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in 16-byte units
+              umma_bf16_ss(tmem_d, desc_a + static_cast<uint64_t>(k * 2),
+                           desc_b + static_cast<uint64_t>(k * 2), idesc,
+                           (kb > 0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+            // accumulator complete (same lane as the MMAs: a commit covers its own thread's work)
+            if (kb == num_kb - 1) umma_commit(&tmem_full_bar[astage]);
           }
-          umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+          __syncwarp();
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma_commit(&tmem_full_bar[astage]);  // accumulator complete
-        B200_TRACE(5);
+        if (lane == 0) B200_TRACE(5);
         if (++astage == kAccumStages) {
           astage = 0;
           aphase ^= 1u;

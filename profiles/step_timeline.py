@@ -56,7 +56,7 @@ for i, (b, e, tag) in enumerate(step):
     a[0] += 1
     a[1] += (e - b) / 1e3          # entry -> exit of CTA 0
     a[2] += (nxt - b) / 1e3        # entry -> next kernel's entry (pipeline pitch)
-    if 8 <= i < 26:
+    if 8 <= i < 26 or i >= len(step) - 4:
         print(f"{i:3d} {name:22s} entry {(b - base) / 1e3:8.2f} us  exit {(e - base) / 1e3:8.2f} us  dur {(e - b) / 1e3:6.2f}")
         if name.startswith("gemm"):
             print("      " + "  ".join(f"{MARK_NAMES[j]} {(m - base) / 1e3:.2f}" for j, m in enumerate(marks[i]) if m > 0))
