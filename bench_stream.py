@@ -2,7 +2,7 @@
 """BASELINE.json configs[4]: a mixed-length SmartReply / Summarize / Ask request stream through the
 gRPC llm.LLMService, served by the local B200 engine on 1..N GPUs of one box.
 
-    python bench_stream.py [--gpus N] [--requests R] [--rate REQ_PER_S] [--cpu-sample K]
+    python bench_stream.py [--gpus N] [--requests R] [--rate REQ_PER_S] [--client-procs P] [--cpu-sample K]
 
 Stream: request kinds in ratio 6:1:3 (SmartReply : Summarize : Ask), Poisson arrivals
 (seed 99), conversations synthesised from a fixed sentence pool. Every request travels the whole
@@ -10,7 +10,8 @@ drop-in path: gRPC stub -> LLMServicer (reference prompts/parsers) -> LocalGener
 router -> per-GPU continuous-batching worker -> CUDA engine. Replicas only: the router shards
 requests, there is no collective. Prints ONE JSON line: p50/p95 latency per RPC, aggregate
 generated tokens/s, and (optionally) the same RPCs timed on the host CPU with transformers for a
-small sample.
+small sample. The callers run in separate processes (`--client-procs`, like the reference's remote
+Raft nodes) so that their Python does not share an interpreter lock with the server.
 """
 from __future__ import annotations
 
@@ -18,6 +19,7 @@ import argparse
 import importlib
 import json
 import os
+import subprocess
 import sys
 import threading
 import time
@@ -76,14 +78,63 @@ class CountingModel:
         return resp
 
 
+def run_calls(stub_factory, reqs, indices, arrivals, threads, t_zero):
+    """Issue reqs[i] for i in indices from `threads` caller threads; returns (latencies, t_first, t_last)
+    with wall-clock (time.time) stamps that are comparable across processes."""
+    lat: dict[str, list[float]] = {"GetSmartReply": [], "SummarizeConversation": [], "GetLLMAnswer": []}
+    lock = threading.Lock()
+    stub = stub_factory()
+    stamps = []
+
+    def call(i):
+        rpc, req = reqs[i]
+        delay = t_zero + arrivals[i] - time.time()
+        if delay > 0:
+            time.sleep(delay)
+        t0 = time.time()
+        getattr(stub, rpc)(req, timeout=60)
+        t1 = time.time()
+        with lock:
+            lat[rpc].append((t1 - t0) * 1e3)
+            stamps.append((t0, t1))
+
+    with futures.ThreadPoolExecutor(max_workers=threads) as pool:
+        list(pool.map(call, indices))
+    return lat, min(s[0] for s in stamps), max(s[1] for s in stamps)
+
+
+def client_main(args):
+    """--as-client: one caller process. Prints one JSON line with its latencies and time stamps."""
+    import grpc
+
+    server_mod = importlib.import_module(f"{PKG}.server")
+    pb = importlib.import_module(f"{PKG}.llm_proto")
+    reqs = make_requests(pb, args.requests)
+    rng = np.random.default_rng(99)
+    arrivals = np.cumsum(rng.exponential(1.0 / args.rate, size=len(reqs))) if args.rate > 0 else np.zeros(len(reqs))
+    indices = list(range(args.client_index, len(reqs), args.client_procs))
+    with grpc.insecure_channel(f"127.0.0.1:{args.port}") as ch:
+        lat, t_first, t_last = run_calls(lambda: server_mod.LLMServiceStub(ch), reqs, indices, arrivals,
+                                         max(1, args.clients // args.client_procs), args.t_zero)
+    print(json.dumps({"lat": lat, "t_first": t_first, "t_last": t_last}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--requests", type=int, default=400)
     ap.add_argument("--rate", type=float, default=0.0, help="Poisson arrival rate in requests/s (0 = closed loop)")
-    ap.add_argument("--clients", type=int, default=64, help="concurrent callers")
+    ap.add_argument("--clients", type=int, default=64, help="concurrent callers (threads over all caller processes)")
+    ap.add_argument("--client-procs", type=int, default=4, help="caller processes (0 = callers share this process)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="also time this many requests per RPC on the host CPU")
+    ap.add_argument("--as-client", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--port", type=int, default=0, help=argparse.SUPPRESS)
+    ap.add_argument("--client-index", type=int, default=0, help=argparse.SUPPRESS)
+    ap.add_argument("--t-zero", type=float, default=0.0, help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.as_client:
+        client_main(args)
+        return
 
     import grpc
 
@@ -103,39 +154,45 @@ def main():
     reqs = make_requests(pb, args.requests)
     rng = np.random.default_rng(99)
     arrivals = np.cumsum(rng.exponential(1.0 / args.rate, size=len(reqs))) if args.rate > 0 else np.zeros(len(reqs))
-    lat: dict[str, list[float]] = {"GetSmartReply": [], "SummarizeConversation": [], "GetLLMAnswer": []}
-    lock = threading.Lock()
-
     with grpc.insecure_channel(f"127.0.0.1:{port}") as ch:
         stub = server_mod.LLMServiceStub(ch)
         for rpc, req in reqs[:8]:  # warm-up (graph capture, tokenizer caches)
             getattr(stub, rpc)(req, timeout=60)
         model.generated = model.prompt = 0
-        t_start = time.perf_counter()
-
-        def call(i):
-            rpc, req = reqs[i]
-            delay = t_start + arrivals[i] - time.perf_counter()
-            if delay > 0:
-                time.sleep(delay)
-            t0 = time.perf_counter()
-            getattr(stub, rpc)(req, timeout=60)
-            with lock:
-                lat[rpc].append((time.perf_counter() - t0) * 1e3)
-
-        with futures.ThreadPoolExecutor(max_workers=args.clients) as pool:
-            list(pool.map(call, range(len(reqs))))
-        wall = time.perf_counter() - t_start
+        if args.client_procs <= 0:
+            lat, t_first, t_last = run_calls(lambda: stub, reqs, range(len(reqs)), arrivals, args.clients, time.time())
+        else:
+            t_zero = time.time() + 10.0  # callers import grpc / build the descriptors first, then start together
+            procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--as-client", "--port", str(port),
+                                       "--requests", str(args.requests), "--rate", str(args.rate),
+                                       "--clients", str(args.clients), "--client-procs", str(args.client_procs),
+                                       "--client-index", str(i), "--t-zero", repr(t_zero)],
+                                      stdout=subprocess.PIPE, text=True) for i in range(args.client_procs)]
+            lat = {"GetSmartReply": [], "SummarizeConversation": [], "GetLLMAnswer": []}
+            t_first, t_last = float("inf"), 0.0
+            for pr in procs:
+                out, _ = pr.communicate(timeout=600)
+                if pr.returncode != 0:
+                    raise RuntimeError(f"caller process failed with code {pr.returncode}")
+                d = json.loads(out.strip().splitlines()[-1])
+                for k, v in d["lat"].items():
+                    lat[k].extend(v)
+                t_first, t_last = min(t_first, d["t_first"]), max(t_last, d["t_last"])
+        wall = t_last - t_first
     server.stop(0)
+    workers = model.inner.router.workers
+    worker_phases = [{**{k: round(v, 3) for k, v in w.phase_s.items()}, "iterations": w.iterations} for w in workers]
     model.inner.router.shutdown()
 
     out = {
         "metric": "mixed SmartReply/Summarize/Ask stream through gRPC LLMService (BASELINE configs[4])",
         "n_gpus": args.gpus, "requests": len(reqs), "arrival_rate_rps": args.rate or None, "clients": args.clients,
+        "client_processes": args.client_procs,
         "wall_s": wall, "requests_per_s": len(reqs) / wall,
         "generated_tokens_per_s": model.generated / wall, "prompt_tokens_per_s": model.prompt / wall,
         "latency_ms": {k: {"n": len(v), "p50": float(np.percentile(v, 50)), "p95": float(np.percentile(v, 95))}
                        for k, v in lat.items() if v},
+        "worker_loop_s": worker_phases,
         "tokenizer": "byte-level GPT-2 ids (no vocab files offline): prompts are ~4x longer than with BPE",
         "data": "synthetic conversations, random-init GPT-2 small",
     }

@@ -56,6 +56,9 @@ class EngineWorker(threading.Thread):
         self.completed = 0
         self.generated_tokens = 0
         self._stopping = False
+        # wall time of the worker loop by phase, for the stream benchmark's report
+        self.phase_s = {"idle": 0.0, "admit": 0.0, "decode": 0.0, "retire": 0.0}
+        self.iterations = 0
 
     # ---- called from any thread ----
     def submit(self, ids: Sequence[int], sampling: SamplingParams) -> Future:
@@ -159,17 +162,28 @@ class EngineWorker(threading.Thread):
         self.active = still
 
     def run(self) -> None:
+        clock = time.perf_counter
         while not self._stopping:
+            t0 = clock()
             self._drain_inbox(block=not self.active and not self.waiting)
+            t1 = clock()
+            self.phase_s["idle"] += t1 - t0
             if self._stopping:
                 break
             try:
                 if self.waiting:
                     self._admit()
                     self._retire()  # max_new_tokens == 1 finishes at prefill
+                t2 = clock()
+                self.phase_s["admit"] += t2 - t1
                 if self.active:
                     self.engine.decode([r.slot for r in self.active], self.decode_burst)
+                    t3 = clock()
                     self._retire()
+                    t4 = clock()
+                    self.phase_s["decode"] += t3 - t2
+                    self.phase_s["retire"] += t4 - t3
+                    self.iterations += 1
             except Exception as exc:  # noqa: BLE001  a broken engine fails its requests, not the server
                 for req in self.active + self.waiting:
                     self._fail(req, exc)
