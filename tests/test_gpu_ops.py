@@ -245,6 +245,7 @@ def test_prefill_attention(ops, cuda, lens, n_head):
     ([127] * 8, 12, 1),
     # several 128-row staging passes in one CTA, incl. the register-held head of the 2nd pass
     ([126, 127, 128, 129, 143, 144, 160, 161, 255, 256, 257, 511, 640], 12, 1),
+    ([62, 63, 64, 65, 191, 192, 193], 12, 1),
     ([1100, 3, 64, 700], 16, 4),
     ([1100, 3, 64, 700], 16, 16),
     ([300, 299], 20, 2),
