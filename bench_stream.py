@@ -127,6 +127,7 @@ def main():
     ap.add_argument("--clients", type=int, default=64, help="concurrent callers (threads over all caller processes)")
     ap.add_argument("--client-procs", type=int, default=4, help="caller processes (0 = callers share this process)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="also time this many requests per RPC on the host CPU")
+    ap.add_argument("--switch-interval", type=float, default=0.0, help="sys.setswitchinterval for the server process (0 = leave)")
     ap.add_argument("--as-client", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--port", type=int, default=0, help=argparse.SUPPRESS)
     ap.add_argument("--client-index", type=int, default=0, help=argparse.SUPPRESS)
@@ -138,6 +139,8 @@ def main():
 
     import grpc
 
+    if args.switch_interval > 0:
+        sys.setswitchinterval(args.switch_interval)
     server_mod = importlib.import_module(f"{PKG}.server")
     svc = importlib.import_module(f"{PKG}.llm_service")
     pb = importlib.import_module(f"{PKG}.llm_proto")

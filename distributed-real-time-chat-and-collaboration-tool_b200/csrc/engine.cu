@@ -173,6 +173,8 @@ struct b200llm_engine {
   // pinned staging
   int32_t* pin_i32 = nullptr;
   size_t pin_i32_count = 0;
+  cudaEvent_t pin_event = nullptr;  // recorded after the last copy that read the pinned staging buffers
+  bool pin_busy = false;
   SlotInit* pin_init = nullptr;
   int32_t* pin_pt = nullptr;    // pinned mirror of the page table (bulk uploads)
   int32_t* pin_tok = nullptr;   // pinned landing zone for generated tokens [max_seqs][max_new]
@@ -504,6 +506,23 @@ int decode_step_launches(b200llm_engine* e, const StepPlan& p) {
   return run_stack(e, p);
 }
 
+// The pinned staging buffers are reused call to call. Instead of draining the whole stream before
+// a reuse (which would make every prefill / active-set upload wait for the decode burst queued
+// ahead of it), an event marks the last copy that read them; only that copy has to be done.
+int wait_pinned_free(b200llm_engine* e) {
+  if (e->pin_busy) {
+    B200_CUDA_OK(cudaEventSynchronize(e->pin_event));
+    e->pin_busy = false;
+  }
+  return kOk;
+}
+int mark_pinned_used(b200llm_engine* e) {
+  if (e->pin_event == nullptr) B200_CUDA_OK(cudaEventCreateWithFlags(&e->pin_event, cudaEventDisableTiming));
+  B200_CUDA_OK(cudaEventRecord(e->pin_event, e->stream));
+  e->pin_busy = true;
+  return kOk;
+}
+
 int ensure_pinned(b200llm_engine* e, size_t count_i32) {
   if (count_i32 <= e->pin_i32_count) return kOk;
   if (e->pin_i32) cudaFreeHost(e->pin_i32);
@@ -736,6 +755,7 @@ int b200llm_engine_destroy(b200llm_engine* e) {
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   }
   for (void* p : e->allocations) cudaFree(p);
+  if (e->pin_event) cudaEventDestroy(e->pin_event);
   if (e->pin_i32) cudaFreeHost(e->pin_i32);
   if (e->pin_init) cudaFreeHost(e->pin_init);
   if (e->pin_pt) cudaFreeHost(e->pin_pt);
@@ -831,9 +851,9 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   cudaStream_t st = e->stream;
 
   // staging: [cu (batch+1) | slots (batch) | ids (n_tok, host case)]
-  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(2 * batch + 1 + n_tok)));
   // pinned buffers are reused call to call: the previous call's copies must have drained
-  B200_CUDA_OK(cudaStreamSynchronize(st));
+  B200_PROPAGATE(wait_pinned_free(e));
+  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(2 * batch + 1 + n_tok)));
   int32_t* pin = e->pin_i32;
   std::memcpy(pin, cu, (batch + 1) * sizeof(int32_t));
   std::memcpy(pin + batch + 1, slots, batch * sizeof(int32_t));
@@ -893,6 +913,7 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   }
   B200_CUDA_OK(cudaMemcpyAsync(e->init_dev, e->pin_init, batch * sizeof(SlotInit),
                                cudaMemcpyHostToDevice, st));
+  B200_PROPAGATE(mark_pinned_used(e));
   init_slots_kernel<<<(batch + 127) / 128, 128, 0, st>>>(e->init_dev, batch, e->last_tok, e->finished,
                                                          e->n_gen, e->min_new, e->max_new,
                                                          e->temperature, e->top_k, e->seed);
@@ -940,11 +961,12 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   std::vector<int32_t> active(bucket, -1);
   std::copy(slots, slots + batch, active.begin());
   if (active != e->active_host) {
+    B200_PROPAGATE(wait_pinned_free(e));
     B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(bucket)));
-    B200_CUDA_OK(cudaStreamSynchronize(st));
     std::memcpy(e->pin_i32, active.data(), bucket * sizeof(int32_t));
     B200_CUDA_OK(cudaMemcpyAsync(e->active_dev, e->pin_i32, bucket * sizeof(int32_t),
                                  cudaMemcpyHostToDevice, st));
+    B200_PROPAGATE(mark_pinned_used(e));
     e->active_host = active;
   }
 
@@ -1080,8 +1102,9 @@ int b200llm_read_status(b200llm_engine* e, const int32_t* slots, int32_t batch, 
   B200_CHECK_ARG(e && slots && out_counts && out_finished, "read_status: null argument");
   B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "read_status: bad batch");
   cudaStream_t st = e->stream;
-  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(3 * batch)));
   B200_CUDA_OK(cudaStreamSynchronize(st));
+  e->pin_busy = false;
+  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(3 * batch)));
   std::memcpy(e->pin_i32, slots, batch * sizeof(int32_t));
   B200_CUDA_OK(cudaMemcpyAsync(e->last_rows, e->pin_i32, batch * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   gather_status_kernel<<<(batch + 127) / 128, 128, 0, st>>>(e->last_rows, batch, e->n_gen, e->finished,

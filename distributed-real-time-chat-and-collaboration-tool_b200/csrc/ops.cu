@@ -298,10 +298,154 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
 
 constexpr int kMaxTopK = 64;
 
+// ---------------------------------------------------------------------------------------
+// Top-k of one logits row by radix select (sampling path).
+// k successive arg-max passes over the 50k-entry row cost ~14 us each; here the k-th largest
+// value is located with three histogram passes over an order-preserving 32-bit key (11 + 11 + 10
+// bits), a fourth pass collects everything above it plus the lowest-index ties, and the <= 64
+// survivors are ranked by (value desc, index asc) -- the same order the pass-per-entry version
+// produced, so the draw that follows is bit-identical.
+// ---------------------------------------------------------------------------------------
+constexpr int kTopkBins = 2048;
+constexpr int kTopkEqCap = 1024;
+
+struct TopkSmem {
+  unsigned int hist[kTopkBins];
+  int eq_idx[kTopkEqCap];
+  float cand_v[kMaxTopK];
+  int cand_i[kMaxTopK];
+  unsigned int n_cand, n_eq;
+  unsigned int sel_bin, sel_above;
+};
+
+__device__ __forceinline__ unsigned int topk_key(float v) {
+  unsigned int b = __float_as_uint(v);
+  if (b == 0x80000000u) b = 0u;  // -0 == +0
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+// Warp 0: walk the histogram from the highest bin down and find the bin in which the running
+// count reaches `need`; publishes the bin and the count strictly above it.
+__device__ __forceinline__ void topk_find_bin(TopkSmem& sm, int nbins, unsigned int need) {
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    const int per = nbins / 32;
+    const int hi = nbins - 1 - lane * per;  // this lane's segment: bins hi, hi-1, ..., hi-per+1
+    unsigned int seg = 0;
+    for (int j = 0; j < per; ++j) seg += sm.hist[hi - j];
+    unsigned int incl = seg;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned int up = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += up;
+    }
+    const unsigned int excl = incl - seg;
+    if (excl < need && incl >= need) {  // exactly one lane (need >= 1 and need <= total)
+      unsigned int run = excl;
+      for (int j = 0; j < per; ++j) {
+        const unsigned int c = sm.hist[hi - j];
+        if (run + c >= need) {
+          sm.sel_bin = static_cast<unsigned int>(hi - j);
+          sm.sel_above = run;
+          break;
+        }
+        run += c;
+      }
+    }
+  }
+}
+
+// All threads of the CTA. Returns false (nothing written) when more than kTopkEqCap entries tie
+// with the k-th value; the caller then uses the pass-per-entry selection. On success top_v/top_i
+// hold the k entries in (value desc, index asc) order.
+__device__ bool topk_radix(const float* __restrict__ lg, int vocab, int skip_id, int k, TopkSmem& sm, float* top_v,
+                           int* top_i) {
+  unsigned int prefix = 0, prefix_mask = 0;
+  unsigned int need = static_cast<unsigned int>(k);
+  const int shifts[3] = {21, 10, 0};
+  const int widths[3] = {11, 11, 10};
+#pragma unroll
+  for (int pass = 0; pass < 3; ++pass) {
+    const int nbins = 1 << widths[pass];
+    for (int i = threadIdx.x; i < nbins; i += blockDim.x) sm.hist[i] = 0u;
+    __syncthreads();
+    for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+      if (i == skip_id) continue;
+      const unsigned int key = topk_key(lg[i]);
+      if ((key & prefix_mask) == prefix) atomicAdd(&sm.hist[(key >> shifts[pass]) & (nbins - 1)], 1u);
+    }
+    __syncthreads();
+    topk_find_bin(sm, nbins, need);
+    __syncthreads();
+    prefix |= sm.sel_bin << shifts[pass];
+    prefix_mask |= static_cast<unsigned int>(nbins - 1) << shifts[pass];
+    need -= sm.sel_above;
+    __syncthreads();  // sel_* are rewritten by the next pass
+  }
+  // prefix is now the key of the k-th largest entry; `need` of the entries equal to it are taken
+  const unsigned int thr = prefix;
+  if (threadIdx.x == 0) {
+    sm.n_cand = 0u;
+    sm.n_eq = 0u;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+    if (i == skip_id) continue;
+    const float v = lg[i];
+    const unsigned int key = topk_key(v);
+    if (key > thr) {
+      const unsigned int p = atomicAdd(&sm.n_cand, 1u);
+      if (p < static_cast<unsigned int>(kMaxTopK)) {
+        sm.cand_v[p] = v;
+        sm.cand_i[p] = i;
+      }
+    } else if (key == thr) {
+      const unsigned int p = atomicAdd(&sm.n_eq, 1u);
+      if (p < static_cast<unsigned int>(kTopkEqCap)) sm.eq_idx[p] = i;
+    }
+  }
+  __syncthreads();
+  const unsigned int n_eq = sm.n_eq;
+  const unsigned int n_gt = sm.n_cand;  // == k - need
+  if (n_eq > static_cast<unsigned int>(kTopkEqCap)) return false;
+  // the `need` lowest indices among the ties
+  float thr_v = 0.f;
+  {
+    const unsigned int b = (thr & 0x80000000u) ? (thr & 0x7fffffffu) : ~thr;
+    thr_v = __uint_as_float(b);
+  }
+  for (unsigned int t = threadIdx.x; t < n_eq; t += blockDim.x) {
+    const int mine = sm.eq_idx[t];
+    unsigned int rank = 0;
+    for (unsigned int j = 0; j < n_eq; ++j) rank += sm.eq_idx[j] < mine ? 1u : 0u;
+    if (rank < need) {
+      sm.cand_v[n_gt + rank] = thr_v;
+      sm.cand_i[n_gt + rank] = mine;
+    }
+  }
+  __syncthreads();
+  // rank the k survivors
+  if (threadIdx.x < static_cast<unsigned int>(k)) {
+    const float v = sm.cand_v[threadIdx.x];
+    const int idx = sm.cand_i[threadIdx.x];
+    int rank = 0;
+    for (int j = 0; j < k; ++j) {
+      const float vj = sm.cand_v[j];
+      const int ij = sm.cand_i[j];
+      rank += (vj > v || (vj == v && ij < idx)) ? 1 : 0;
+    }
+    top_v[rank] = v;
+    top_i[rank] = idx;
+  }
+  __syncthreads();
+  return true;
+}
+
 __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
   __shared__ MaxIdx red[32];
   __shared__ float top_v[kMaxTopK];
   __shared__ int top_i[kMaxTopK];
+  __shared__ TopkSmem topk_sm;
   B200_STEP_BEGIN(3);
   pdl_wait();
   pdl_launch_dependents();
@@ -351,10 +495,13 @@ __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
   } else {
     // top-k by k successive block-wide argmax passes over the (L2-resident) logits row,
     // then a temperature softmax over the k survivors and one inverse-CDF draw.
-    const int k = top_k_req < kMaxTopK ? top_k_req : kMaxTopK;
+    int k = top_k_req < kMaxTopK ? top_k_req : kMaxTopK;
+    const int n_valid = a.vocab - ((ban_eos && a.eos_id >= 0 && a.eos_id < a.vocab) ? 1 : 0);
+    if (k > n_valid) k = n_valid;
+    const bool have_topk = topk_radix(lg, a.vocab, ban_eos ? a.eos_id : -1, k, topk_sm, top_v, top_i);
     float prev_v = INFINITY;
     int prev_i = -1;
-    for (int r = 0; r < k; ++r) {
+    for (int r = 0; r < (have_topk ? 0 : k); ++r) {  // fallback: one arg-max pass per entry
       MaxIdx m;
       m.v = -INFINITY;
       m.i = 0x7fffffff;

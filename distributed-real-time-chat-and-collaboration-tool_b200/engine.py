@@ -141,8 +141,7 @@ class Engine:
         check(lib.b200llm_prefill(self._h, ids_ptr, on_dev, cu.ctypes.data, sl.ctypes.data,
                                   C.cast(samp, C.c_void_p) if samp is not None else None,
                                   len(prompts), logits_all_ptr))
-        if ids is not None:
-            self.sync()  # `ids` (pageable numpy memory) must outlive the staged copy
+        # (host ids are copied into the engine's pinned staging buffer before the call returns)
 
     def decode(self, slots: Sequence[int], n_steps: int = 1) -> None:
         sl = _i32(slots)

@@ -27,6 +27,9 @@ rng = np.random.default_rng(0)
 prompts = rng.integers(0, shape.vocab_size - 1, size=(B, T), dtype=np.int32)
 stream = torch.cuda.Stream()
 chunk = max(1, min(B, 16384 // T))
+# TIME_DECODE_SAMPLING=1: every row samples (temperature 0.7, top-k 40) like the service's ask-AI path
+SP = (E.SamplingParams(N, N, temperature=0.7, top_k=40, seed=1) if os.environ.get("TIME_DECODE_SAMPLING")
+      else E.SamplingParams(N, N))
 
 for graphs, pdl, split, reduce in [(True, False, 1, 0), (True, False, 0, 0), (True, True, 0, 0), (True, True, 0, 2)]:
     eng = E.Engine(shape, blob, max_seqs=B, max_seq_len=T + N, max_batch_tokens=min(B * T, 16384),
@@ -41,7 +44,7 @@ for graphs, pdl, split, reduce in [(True, False, 1, 0), (True, False, 0, 0), (Tr
         e0.record(stream)
         for c0 in range(0, B, chunk):
             eng.prefill(list(prompts[c0:c0 + chunk]), slots[c0:c0 + chunk],
-                        [E.SamplingParams(N, N)] * len(slots[c0:c0 + chunk]))
+                        [SP] * len(slots[c0:c0 + chunk]))
         e1.record(stream)
         eng.decode(slots, N - 1)
         e2.record(stream)
