@@ -301,17 +301,19 @@ constexpr int kMaxTopK = 64;
 // ---------------------------------------------------------------------------------------
 // Top-k of one logits row by radix select (sampling path).
 // k successive arg-max passes over the 50k-entry row cost ~14 us each; here the k-th largest
-// value is located with three histogram passes over an order-preserving 32-bit key (11 + 11 + 10
-// bits), a fourth pass collects everything above it plus the lowest-index ties, and the <= 64
+// value is located with histogram passes over an order-preserving 32-bit key (11 + 11 + 10 bits;
+// normally the first pass leaves a short list that is finished in shared memory), a last pass
+// collects everything above it plus the lowest-index ties, and the <= 64
 // survivors are ranked by (value desc, index asc) -- the same order the pass-per-entry version
 // produced, so the draw that follows is bit-identical.
 // ---------------------------------------------------------------------------------------
 constexpr int kTopkBins = 2048;
-constexpr int kTopkEqCap = 1024;
+constexpr int kTopkEqCap = 4096;  // also the capacity of the short list after the first pass
 
 struct TopkSmem {
   unsigned int hist[kTopkBins];
-  int eq_idx[kTopkEqCap];
+  int eq_idx[kTopkEqCap];             // indices of the ties (long path) / of the short list
+  unsigned int list_key[kTopkEqCap];  // keys of the short list
   float cand_v[kMaxTopK];
   int cand_i[kMaxTopK];
   unsigned int n_cand, n_eq;
@@ -362,17 +364,32 @@ __device__ bool topk_radix(const float* __restrict__ lg, int vocab, int skip_id,
                            int* top_i) {
   unsigned int prefix = 0, prefix_mask = 0;
   unsigned int need = static_cast<unsigned int>(k);
+  bool short_list = false;
   const int shifts[3] = {21, 10, 0};
   const int widths[3] = {11, 11, 10};
 #pragma unroll
   for (int pass = 0; pass < 3; ++pass) {
     const int nbins = 1 << widths[pass];
+    if (pass == 1 && short_list) break;  // CTA-uniform
     for (int i = threadIdx.x; i < nbins; i += blockDim.x) sm.hist[i] = 0u;
     __syncthreads();
-    for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
-      if (i == skip_id) continue;
-      const unsigned int key = topk_key(lg[i]);
-      if ((key & prefix_mask) == prefix) atomicAdd(&sm.hist[(key >> shifts[pass]) & (nbins - 1)], 1u);
+    // eight independent loads in flight per thread: a load -> atomic loop runs at one L2 round trip
+    // per element
+    for (int i0 = threadIdx.x; i0 < vocab; i0 += 8 * blockDim.x) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * blockDim.x;
+        v[u] = (i < vocab) ? __ldcg(lg + i) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * blockDim.x;
+        if (i < vocab && i != skip_id) {
+          const unsigned int key = topk_key(v[u]);
+          if ((key & prefix_mask) == prefix) atomicAdd(&sm.hist[(key >> shifts[pass]) & (nbins - 1)], 1u);
+        }
+      }
     }
     __syncthreads();
     topk_find_bin(sm, nbins, need);
@@ -380,8 +397,66 @@ __device__ bool topk_radix(const float* __restrict__ lg, int vocab, int skip_id,
     prefix |= sm.sel_bin << shifts[pass];
     prefix_mask |= static_cast<unsigned int>(nbins - 1) << shifts[pass];
     need -= sm.sel_above;
-    __syncthreads();  // sel_* are rewritten by the next pass
+    if (pass == 0) short_list = sm.hist[sm.sel_bin] <= static_cast<unsigned int>(kTopkEqCap);
+    __syncthreads();  // sel_* and hist are rewritten by the next pass
   }
+  if (short_list) {
+    // Usual case: few entries share the leading 11 key bits of the k-th largest one. One more pass
+    // over the row moves everything above that bin straight to the survivors and the bin itself
+    // to a short list in shared memory, where the remaining `need` entries are found by rank.
+    const unsigned int bin0 = prefix >> 21;
+    if (threadIdx.x == 0) {
+      sm.n_cand = 0u;
+      sm.n_eq = 0u;
+    }
+    __syncthreads();
+    for (int i0 = threadIdx.x; i0 < vocab; i0 += 8 * blockDim.x) {
+      float vv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * blockDim.x;
+        vv[u] = (i < vocab) ? __ldcg(lg + i) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * blockDim.x;
+        if (i >= vocab || i == skip_id) continue;
+        const unsigned int key = topk_key(vv[u]);
+        const unsigned int top = key >> 21;
+        if (top > bin0) {
+          const unsigned int p = atomicAdd(&sm.n_cand, 1u);
+          if (p < static_cast<unsigned int>(kMaxTopK)) {
+            sm.cand_v[p] = vv[u];
+            sm.cand_i[p] = i;
+          }
+        } else if (top == bin0) {
+          const unsigned int p = atomicAdd(&sm.n_eq, 1u);
+          if (p < static_cast<unsigned int>(kTopkEqCap)) {
+            sm.list_key[p] = key;
+            sm.eq_idx[p] = i;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    const unsigned int n_list = sm.n_eq;
+    const unsigned int n_gt = sm.n_cand;  // == k - need
+    for (unsigned int t = threadIdx.x; t < n_list; t += blockDim.x) {
+      const unsigned int key = sm.list_key[t];
+      const int idx = sm.eq_idx[t];
+      unsigned int rank = 0;
+      for (unsigned int j = 0; j < n_list; ++j) {
+        const unsigned int kj = sm.list_key[j];
+        rank += (kj > key || (kj == key && sm.eq_idx[j] < idx)) ? 1u : 0u;
+      }
+      if (rank < need) {
+        const unsigned int b = (key & 0x80000000u) ? (key & 0x7fffffffu) : ~key;
+        sm.cand_v[n_gt + rank] = __uint_as_float(b);
+        sm.cand_i[n_gt + rank] = idx;
+      }
+    }
+    __syncthreads();
+  } else {
   // prefix is now the key of the k-th largest entry; `need` of the entries equal to it are taken
   const unsigned int thr = prefix;
   if (threadIdx.x == 0) {
@@ -389,19 +464,29 @@ __device__ bool topk_radix(const float* __restrict__ lg, int vocab, int skip_id,
     sm.n_eq = 0u;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
-    if (i == skip_id) continue;
-    const float v = lg[i];
-    const unsigned int key = topk_key(v);
-    if (key > thr) {
-      const unsigned int p = atomicAdd(&sm.n_cand, 1u);
-      if (p < static_cast<unsigned int>(kMaxTopK)) {
-        sm.cand_v[p] = v;
-        sm.cand_i[p] = i;
+  for (int i0 = threadIdx.x; i0 < vocab; i0 += 8 * blockDim.x) {
+    float vv[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * blockDim.x;
+      vv[u] = (i < vocab) ? __ldcg(lg + i) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * blockDim.x;
+      if (i >= vocab || i == skip_id) continue;
+      const float v = vv[u];
+      const unsigned int key = topk_key(v);
+      if (key > thr) {
+        const unsigned int p = atomicAdd(&sm.n_cand, 1u);
+        if (p < static_cast<unsigned int>(kMaxTopK)) {
+          sm.cand_v[p] = v;
+          sm.cand_i[p] = i;
+        }
+      } else if (key == thr) {
+        const unsigned int p = atomicAdd(&sm.n_eq, 1u);
+        if (p < static_cast<unsigned int>(kTopkEqCap)) sm.eq_idx[p] = i;
       }
-    } else if (key == thr) {
-      const unsigned int p = atomicAdd(&sm.n_eq, 1u);
-      if (p < static_cast<unsigned int>(kTopkEqCap)) sm.eq_idx[p] = i;
     }
   }
   __syncthreads();
@@ -424,6 +509,7 @@ __device__ bool topk_radix(const float* __restrict__ lg, int vocab, int skip_id,
     }
   }
   __syncthreads();
+  }  // long-list path
   // rank the k survivors
   if (threadIdx.x < static_cast<unsigned int>(k)) {
     const float v = sm.cand_v[threadIdx.x];
