@@ -257,6 +257,57 @@ def test_temperature_topk_sampling_matches_the_softmax_distribution(cuda):
     eng.close()
 
 
+@pytest.mark.parametrize("dups", [(10, 0), (3000, 2500), (5000, 0)], ids=["short-list", "long-path", "tie-overflow"])
+def test_topk_sampling_with_tied_logits(cuda, dups):
+    """Exact ties at the top-k boundary: rows of the tied embedding / LM-head matrix are duplicated,
+    so many vocabulary entries get bit-identical logits. The selector must keep the LOWEST indices
+    among the ties (value desc, index asc -- the order torch.topk / repeated argmax would give), in
+    all three of its paths: short list after the first radix pass, three radix passes (more than
+    4096 entries share the leading key bits), and the pass-per-entry fallback (more than 4096 exact
+    ties)."""
+    shape = O.GPT2Shape(n_layer=2, n_head=2, d_model=128, vocab_size=12000, n_positions=96, eos_token_id=11999)
+    w = O.synthetic_weights(shape, seed=3)
+    prompt = [5, 6, 7, 8]
+    K, T = 8, 0.7
+    base = O.forward(shape, w, torch.tensor([prompt]))[0, -1]
+    base[shape.eos_token_id] = -float("inf")
+    order = base.argsort(descending=True)
+    r5, r6 = int(order[5]), int(order[6])
+    wte = w["transformer.wte.weight"]
+    top16 = set(order[:16].tolist())
+    free = [i for i in range(100, shape.vocab_size - 1) if i not in top16]
+    n_a, n_b = dups
+    rows_a = free[5::2][:n_a]                     # copies of the rank-5 row, on both sides of its index
+    rows_b = free[4::2][:n_b]                     # copies of a slightly smaller row (same key bin, mostly)
+    row = wte[r5].clone()
+    wte[rows_a] = row
+    if rows_b:
+        wte[rows_b] = row * 0.97
+    eng, E = _engine(shape, w, max_seqs=64, max_seq_len=32, max_batch_tokens=1024, max_new_tokens=2)
+    slot = eng.seq_alloc(32)
+    eng.prefill([prompt], [slot])
+    logits = torch.from_numpy(eng.read_last_logits(1)[0]).double()
+    eng.seq_free(slot)
+    logits[shape.eos_token_id] = -float("inf")
+    assert (logits[rows_a] == logits[r5]).all(), "duplicated rows must give bit-identical logits"
+    # expected survivors: value descending, index ascending
+    idx = np.lexsort((np.arange(shape.vocab_size), -logits.numpy()))[:K]
+    assert len(set(idx.tolist()) & (set(rows_a) | {r5})) >= 2, "the tie must straddle the top-k boundary"
+    probs = torch.softmax(logits[idx] / T, dim=0).numpy()
+    counts = {int(i): 0 for i in idx}
+    n = 2048
+    for s0 in range(0, n, 64):
+        sp = [E.SamplingParams(max_new_tokens=1, min_new_tokens=1, temperature=T, top_k=K, seed=7000 + s0 + j)
+              for j in range(64)]
+        for toks in eng.generate([prompt] * 64, sp):
+            assert toks[0] in counts, f"sampled token {toks[0]} is not among the lowest-index top-{K} survivors"
+            counts[toks[0]] += 1
+    emp = np.array([counts[int(i)] for i in idx]) / n
+    tv = 0.5 * np.abs(emp - probs).sum()
+    assert tv < 0.06
+    eng.close()
+
+
 def test_decode_batch_larger_than_one_umma_n_tile(cuda):
     """More than 256 live sequences: decode GEMMs leave the swap-AB path (tokens on UMMA-M, no
     split-K), the LM head runs several token tiles. Tokens must equal the small-batch run."""
