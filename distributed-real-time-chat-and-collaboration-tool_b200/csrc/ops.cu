@@ -531,7 +531,11 @@ __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
   __shared__ MaxIdx red[32];
   __shared__ float top_v[kMaxTopK];
   __shared__ int top_i[kMaxTopK];
-  __shared__ TopkSmem topk_sm;
+  // The sampler's 41 KB of scratch is dynamic shared memory that only launches with sampling rows
+  // request: as a static array it kept this kernel's CTAs from becoming resident next to the LM
+  // head's (which fill their SMs' shared memory), and the greedy step paid ~8 us for it.
+  extern __shared__ __align__(16) unsigned char topk_dyn[];
+  TopkSmem& topk_sm = *reinterpret_cast<TopkSmem*>(topk_dyn);
   B200_STEP_BEGIN(3);
   pdl_wait();
   pdl_launch_dependents();
@@ -548,7 +552,7 @@ __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
   const uint64_t seed = a.seed ? a.seed[slot] : 0ull;
 
   int chosen;
-  if (temperature <= 0.0f || top_k_req <= 1) {
+  if (temperature <= 0.0f || top_k_req <= 1 || a.logits == nullptr) {
     MaxIdx m;
     m.v = -INFINITY;
     m.i = 0x7fffffff;
@@ -801,8 +805,20 @@ int select_tokens(const SelectArgs& a, cudaStream_t stream) {
   B200_CHECK_ARG(a.batch > 0 && a.vocab > 0, "select: bad shape");
   // all-greedy steps only reduce the LM head's group candidates: a small CTA has the shorter
   // reduction tree; sampling scans the whole logits row and wants every thread it can get
-  const int threads = (a.logits == nullptr && a.amax_val != nullptr) ? 256 : 1024;
-  return launch_pdl(select_kernel, dim3(a.batch), dim3(threads), stream, a.pdl, a);
+  const bool greedy_only = a.logits == nullptr && a.amax_val != nullptr;
+  const int threads = greedy_only ? 256 : 1024;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(a.batch);
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = greedy_only ? 0 : sizeof(TopkSmem);
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = a.pdl ? 1 : 0;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, select_kernel, a));
+  return kOk;
 }
 
 int argmax_rows(const float* logits, int rows, int ld, int vocab, int32_t* out,
