@@ -56,17 +56,6 @@ __global__ void embed_kernel(const float* __restrict__ wte, const float* __restr
 // thread has `n_partials` independent 16-byte loads in flight, so the reduction is bound by
 // L2 bandwidth instead of one warp's load latency; the fixed summation order keeps it
 // deterministic.
-__device__ __forceinline__ float block_sum(float v, float* red) {
-  v = warp_sum(v);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nwarps = (blockDim.x + 31) >> 5;
-  __syncthreads();  // protect `red` from the previous use
-  if (lane == 0) red[warp] = v;
-  __syncthreads();
-  float t = (lane < nwarps) ? red[lane] : 0.f;
-  return warp_sum(t);
-}
-
 __device__ __forceinline__ float2 block_sum2(float a, float b, float2* red) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -670,36 +659,6 @@ argmax_rows_kernel(const float* __restrict__ logits, int ld, int vocab, int32_t*
 }
 
 // ---------------------------------------------------------------------------------------
-// KV scatter (prefill): qkv rows -> pages  [page][head][16 tokens][64 dims]
-// ---------------------------------------------------------------------------------------
-__global__ void kv_scatter_kernel(const __nv_bfloat16* __restrict__ qkv,
-                                  const int32_t* __restrict__ row_slot,
-                                  const int32_t* __restrict__ row_pos,
-                                  const int32_t* __restrict__ page_table, int max_pages_per_seq,
-                                  __nv_bfloat16* __restrict__ k_pool,
-                                  __nv_bfloat16* __restrict__ v_pool, int n_tok, int n_head) {
-  const int d = n_head * kHeadDim;
-  const int chunks_per_row = 2 * d / 8;  // 16-byte chunks of K then V
-  const long gid = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (gid >= static_cast<long>(n_tok) * chunks_per_row) return;
-  const int t = static_cast<int>(gid / chunks_per_row);
-  const int c = static_cast<int>(gid % chunks_per_row);
-  const int is_v = c >= d / 8;
-  const int cc = is_v ? c - d / 8 : c;
-  const int head = cc / 8;
-  const int sub = cc % 8;
-  const int slot = row_slot[t];
-  const int pos = row_pos[t];
-  const int page = page_table[static_cast<size_t>(slot) * max_pages_per_seq + pos / kPageTokens];
-  const uint4 val = *reinterpret_cast<const uint4*>(qkv + static_cast<size_t>(t) * 3 * d +
-                                                   (is_v ? 2 * d : d) + head * kHeadDim + sub * 8);
-  __nv_bfloat16* pool = is_v ? v_pool : k_pool;
-  const size_t dst = ((static_cast<size_t>(page) * n_head + head) * kPageTokens + pos % kPageTokens) *
-                         kHeadDim + sub * 8;
-  *reinterpret_cast<uint4*>(pool + dst) = val;
-}
-
-// ---------------------------------------------------------------------------------------
 // Weight conversion
 // ---------------------------------------------------------------------------------------
 __global__ void convert_transpose_kernel(const float* __restrict__ src,
@@ -825,18 +784,6 @@ int argmax_rows(const float* logits, int rows, int ld, int vocab, int32_t* out,
                 cudaStream_t stream) {
   B200_CHECK_ARG(rows > 0 && vocab > 0, "argmax: bad shape");
   argmax_rows_kernel<<<rows, 1024, 0, stream>>>(logits, ld, vocab, out);
-  B200_CUDA_OK(cudaGetLastError());
-  return kOk;
-}
-
-int kv_scatter(const __nv_bfloat16* qkv, const int32_t* row_slot, const int32_t* row_pos,
-               const int32_t* page_table, int max_pages_per_seq, __nv_bfloat16* k_pool,
-               __nv_bfloat16* v_pool, int n_tok, int n_head, cudaStream_t stream) {
-  const long total = static_cast<long>(n_tok) * (2 * n_head * kHeadDim / 8);
-  const int block = 256;
-  const long grid = (total + block - 1) / block;
-  kv_scatter_kernel<<<static_cast<unsigned>(grid), block, 0, stream>>>(
-      qkv, row_slot, row_pos, page_table, max_pages_per_seq, k_pool, v_pool, n_tok, n_head);
   B200_CUDA_OK(cudaGetLastError());
   return kOk;
 }

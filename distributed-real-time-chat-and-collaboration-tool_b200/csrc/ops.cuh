@@ -85,10 +85,7 @@ int reduce_bias_gelu(const float* partials, int n_partials, int partial_rows, co
 int argmax_rows(const float* logits, int rows, int ld, int vocab, int32_t* out,
                 cudaStream_t stream);
 
-// Copy K and V of packed prefill rows from the qkv activation buffer into KV pages.
-int kv_scatter(const __nv_bfloat16* qkv, const int32_t* row_slot, const int32_t* row_pos,
-               const int32_t* page_table, int max_pages_per_seq, __nv_bfloat16* k_pool,
-               __nv_bfloat16* v_pool, int n_tok, int n_head, cudaStream_t stream);
+
 
 // Weight preparation (load time): fp32 [rows, cols] -> bf16 [cols, rows] (Conv1D [in,out] to
 // K-major [out,in]) and plain fp32 -> bf16.
