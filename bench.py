@@ -37,6 +37,7 @@ WORKLOADS = {
     "ask_large_b32": ("large", 32, 64, 256),          # configs[3] per-GPU shard (256 / 8 GPUs)
     "ask_large_b256": ("large", 256, 64, 256),        # configs[3] on one GPU
     "probe_short_ctx": ("small", 64, 16, 32),         # profiling probe: negligible KV traffic
+    "probe_b1_long": ("small", 1, 496, 32),           # profiling probe: one SmartReply request (byte-level prompt)
     "probe_long_ctx": ("small", 64, 512, 64),         # profiling probe: contexts like the byte-level gRPC stream
 }
 

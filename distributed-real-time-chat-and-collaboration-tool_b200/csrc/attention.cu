@@ -13,6 +13,7 @@
 //   by warp shuffles. Optional split-KV for long contexts with a deterministic combine pass.
 #include "attention.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -312,6 +313,23 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<const uint32_t*>(&v);
 }
 
+__device__ __forceinline__ uint32_t attn_cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void attn_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
+}
+__device__ __forceinline__ float ld_peer_smem(const float* local, uint32_t rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local)), "r"(rank));
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+  return v;
+}
+
 // Ordering argument for everything this kernel does BEFORE griddepcontrol.wait.
 // In a decode step the GEMM, LayerNorm and gelu-reduce kernels signal launch_dependents at entry;
 // the embed kernel (first of every step), this kernel and the selector signal only AFTER their own
@@ -324,9 +342,13 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 //
 // Stage layout: row = token (64 bf16 = 8 chunks of 16 B); chunk c of row r is stored at chunk
 // position c ^ (r & 7), which makes every ldmatrix phase (8 rows x 16 B) conflict-free.
+// kCluster: the KV splits of one (row, head) form a thread-block cluster and merge in the kernel
+// (a separate instantiation, so the one-split kernel of the large-batch step is not touched).
+template <bool kCluster>
 __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
   __shared__ float sm_o[4][kHeadDim];
   __shared__ float sm_ml[4][2];
+  __shared__ float sm_part[kCluster ? kHeadDim + 2 : 1];  // this CTA's merged (o, m, l) for the in-cluster combine
   __shared__ int32_t sm_pages[kMaxSmemPages];
   __shared__ __align__(16) __nv_bfloat16 sm_q[2][kHeadDim];   // this token's q: high / low bf16 parts
   __shared__ __align__(16) __nv_bfloat16 sm_kv[2][kHeadDim];  // this token's k, v (cache dtype)
@@ -651,6 +673,12 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
     }
     if (a.n_splits == 1) {
       a.out[static_cast<size_t>(b) * d + h * kHeadDim + dim] = __float2bfloat16(o / l);
+    } else if (kCluster) {
+      sm_part[dim] = o;
+      if (dim == 0) {
+        sm_part[kHeadDim] = m;
+        sm_part[kHeadDim + 1] = l;
+      }
     } else {
       float* sc = a.scratch + (static_cast<size_t>(bh) * a.n_splits + split) * kScratchStride;
       sc[dim] = o;
@@ -659,6 +687,27 @@ __global__ void __launch_bounds__(128, 6) decode_attn_kernel(DecodeAttnArgs a) {
         sc[kHeadDim + 1] = l;
       }
     }
+  }
+  if (kCluster && a.n_splits > 1) {
+    // The splits of this (row, head) are the CTAs of one cluster (same blockIdx.x). After a cluster
+    // barrier the rank-0 CTA reads every rank's (o, m, l) through distributed shared memory and
+    // merges them in rank order (deterministic); the second barrier keeps the other CTAs'
+    // shared memory alive until it has been read.
+    attn_cluster_sync();
+    if (attn_cluster_rank() == 0 && threadIdx.x < kHeadDim) {
+      const int dim = threadIdx.x;
+      float m = -INFINITY;
+      for (int r = 0; r < a.n_splits; ++r) m = fmaxf(m, ld_peer_smem(&sm_part[kHeadDim], r));
+      float l = 0.f, o = 0.f;
+      for (int r = 0; r < a.n_splits; ++r) {
+        const float mr = ld_peer_smem(&sm_part[kHeadDim], r);
+        const float f = (mr == -INFINITY) ? 0.f : exp2f(mr - m);
+        l += ld_peer_smem(&sm_part[kHeadDim + 1], r) * f;
+        o += ld_peer_smem(&sm_part[dim], r) * f;
+      }
+      a.out[static_cast<size_t>(b) * d + h * kHeadDim + dim] = __float2bfloat16(o / l);
+    }
+    attn_cluster_sync();
   }
   B200_ATRACE(6);
   B200_ATRACE_CTA(2);
@@ -786,7 +835,27 @@ int decode_attention(const DecodeAttnArgs& a, cudaStream_t stream) {
   B200_CHECK_ARG(a.n_splits == 1 || a.scratch != nullptr,
                  "decode_attention: split-KV needs a scratch buffer");
   dim3 grid(a.batch * a.n_head, a.n_splits);
-  B200_PROPAGATE(launch_with_pdl(decode_attn_kernel, grid, dim3(128), stream, a.pdl, a));
+  DecodeAttnArgs args = a;
+  if (const char* env = std::getenv("B200LLM_ATTN_CLUSTER")) args.cluster_combine = std::atoi(env);  // tests
+  if (args.n_splits < 2 || args.n_splits > 8) args.cluster_combine = 0;
+  if (args.cluster_combine != 0) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(128);
+    cfg.stream = stream;
+    cudaLaunchAttribute attrs[2];
+    attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[0].val.programmaticStreamSerializationAllowed = a.pdl ? 1 : 0;
+    attrs[1].id = cudaLaunchAttributeClusterDimension;
+    attrs[1].val.clusterDim.x = 1;
+    attrs[1].val.clusterDim.y = static_cast<unsigned>(args.n_splits);
+    attrs[1].val.clusterDim.z = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = 2;
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, decode_attn_kernel<true>, args));
+    return kOk;
+  }
+  B200_PROPAGATE(launch_with_pdl(decode_attn_kernel<false>, grid, dim3(128), stream, a.pdl, args));
   if (a.n_splits > 1) {
     B200_PROPAGATE(
         launch_with_pdl(decode_combine_kernel, dim3(a.batch * a.n_head), dim3(64), stream, a.pdl, a));

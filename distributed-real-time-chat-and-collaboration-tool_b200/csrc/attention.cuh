@@ -48,6 +48,10 @@ struct DecodeAttnArgs {
   int n_splits;                  // KV splits per (row, head); > 1 needs scratch
   float* scratch;                // n_splits > 1: [batch*n_head*n_splits*(64+2)] fp32
   int pdl;
+  // 2..8 splits only: launch the splits of one (row, head) as a thread-block cluster and merge
+  // their partial results through distributed shared memory inside the kernel (no scratch, no
+  // combine launch). The engine sets it; the operator entry points keep the scratch path.
+  int cluster_combine;
 };
 // One decode step of attention: appends this token's K/V to its pages, then attends over
 // positions 0..seq_len (inclusive).

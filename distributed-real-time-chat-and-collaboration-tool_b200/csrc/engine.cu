@@ -181,12 +181,13 @@ struct b200llm_engine {
 
   // decode graphs
   struct GraphKey {
-    int bucket, splits, logits, steps;
+    int bucket, splits, logits, steps, attn_cluster;
     bool operator<(const GraphKey& o) const {
       if (bucket != o.bucket) return bucket < o.bucket;
       if (splits != o.splits) return splits < o.splits;
       if (logits != o.logits) return logits < o.logits;
-      return steps < o.steps;
+      if (steps != o.steps) return steps < o.steps;
+      return attn_cluster < o.attn_cluster;
     }
   };
   struct GraphEntry {
@@ -202,6 +203,7 @@ struct b200llm_engine {
   // Profiling aid (env B200LLM_SKIP, bit mask): drop a class of kernels from the decode step to
   // read its in-graph cost by difference. Results are garbage when set; never set in tests.
   int skip_mask = 0;
+  int sm_count = 148;
   int steps_per_graph = 4;  // decode steps captured per CUDA graph (B200LLM_STEPS_PER_GRAPH overrides)
   int act_via_tma = 0;  // B200LLM_ACT_TMA=1: decode GEMMs fetch activations through TMA (comparison aid)
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
@@ -272,6 +274,7 @@ struct StepPlan {
   // cluster (DSMEM) split-K factors; when > 1 they take precedence over the plane splits
   int cl_qkv = 1, cl_o = 1, cl_fc = 1, cl_p = 1;
   int attn_splits = 1;
+  int live_rows = 1 << 30;  // decode: sequences in the call (the bucket's other rows are padding)
   int pdl = 0;
   int batch = 0;       // sequences (prefill) / bucket rows (decode)
   int max_len = 0;     // prefill: longest prompt
@@ -384,8 +387,14 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       a.n_splits = p.attn_splits;
       a.scratch = e->attn_scratch;
       a.pdl = pdl;
+      // small grids (a handful of rows): 2..8 splits are merged inside the kernel, no combine launch.
+      // With a thousand CTAs the co-scheduling of whole clusters costs more than the launch it saves
+      // (GPT-2 medium, 16 rows x 16 heads x 4 splits: 1148 vs 1014 us per step).
+      a.cluster_combine = (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
       if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
-      if (p.attn_splits > 1) e->launches += 1, e->launches_in_capture += 1;
+      if (p.attn_splits > 1 && !(a.cluster_combine && p.attn_splits <= 8)) {
+        e->launches += 1, e->launches_in_capture += 1;  // separate combine kernel
+      }
     } else {
       PrefillCache pc;
       pc.slots = e->slots_dev;
@@ -576,6 +585,8 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
 
   std::unique_ptr<b200llm_engine> e(new b200llm_engine());
   e->cfg = *cfg;
+  cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, e->cfg.device);
+  if (e->sm_count <= 0) e->sm_count = 148;
   if (const char* skip = std::getenv("B200LLM_SKIP")) e->skip_mask = std::atoi(skip);
   if (const char* at = std::getenv("B200LLM_ACT_TMA")) e->act_via_tma = std::atoi(at);
   if (const char* sg = std::getenv("B200LLM_STEPS_PER_GRAPH")) e->steps_per_graph = std::max(1, std::min(32, std::atoi(sg)));
@@ -976,6 +987,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   p.batch = bucket;
   p.pdl = e->cfg.use_pdl ? 1 : 0;
   p.store_logits = need_logits;
+  p.live_rows = batch;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.device);
   // auto: pick_split's rule, never more than 12 planes
@@ -1015,7 +1027,9 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     // steps is a programmatic edge (~1 us), between two graph launches it is a full drain + launch
     // (~4 us). The remainder runs on the single-step graph.
     auto get_graph = [&](int steps, b200llm_engine::GraphEntry** out) -> int {
-      b200llm_engine::GraphKey key{bucket, p.attn_splits, need_logits ? 1 : 0, steps};
+      // (the in-kernel split combine depends on the live row count, so it is part of the key)
+      const int attn_cluster = (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
+      b200llm_engine::GraphKey key{bucket, p.attn_splits, need_logits ? 1 : 0, steps, attn_cluster};
       auto it = e->graphs.find(key);
       if (it == e->graphs.end()) {
         cudaGraph_t graph = nullptr;

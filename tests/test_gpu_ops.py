@@ -247,12 +247,19 @@ def test_prefill_attention(ops, cuda, lens, n_head):
     ([126, 127, 128, 129, 143, 144, 160, 161, 255, 256, 257, 511, 640], 12, 1),
     ([62, 63, 64, 65, 191, 192, 193], 12, 1),
     ([1100, 3, 64, 700], 16, 4),
+    ([1100, 3, 64, 700], 16, 8),
+    ([40, 500], 12, 3),
     ([1100, 3, 64, 700], 16, 16),
     ([300, 299], 20, 2),
 ])
-def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits):
+@pytest.mark.parametrize("cluster", ["0", "1"])
+def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, cluster, monkeypatch):
     """seq_len[b] tokens are cached; the new token (position seq_len[b]) is appended by the
-    kernel, then attends over everything including itself."""
+    kernel, then attends over everything including itself. `cluster` = 1 makes 2..8 KV splits merge
+    inside the kernel (the engine's setting) instead of through scratch + a combine launch."""
+    if cluster == "1" and not 2 <= n_splits <= 8:
+        pytest.skip("the in-cluster combine only exists for 2..8 splits")
+    monkeypatch.setenv("B200LLM_ATTN_CLUSTER", cluster)
     d = n_head * 64
     B = len(ctx_lens)
     page = 16
