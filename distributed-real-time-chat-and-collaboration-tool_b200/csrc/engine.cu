@@ -204,6 +204,7 @@ struct b200llm_engine {
   // read its in-graph cost by difference. Results are garbage when set; never set in tests.
   int skip_mask = 0;
   int sm_count = 148;
+  int prefill_pdl = 1;  // B200LLM_PREFILL_PDL=0 disables
   int steps_per_graph = 4;  // decode steps captured per CUDA graph (B200LLM_STEPS_PER_GRAPH overrides)
   int act_via_tma = 0;  // B200LLM_ACT_TMA=1: decode GEMMs fetch activations through TMA (comparison aid)
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
@@ -588,6 +589,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, e->cfg.device);
   if (e->sm_count <= 0) e->sm_count = 148;
   if (const char* skip = std::getenv("B200LLM_SKIP")) e->skip_mask = std::atoi(skip);
+  if (const char* pp = std::getenv("B200LLM_PREFILL_PDL")) e->prefill_pdl = std::atoi(pp);
   if (const char* at = std::getenv("B200LLM_ACT_TMA")) e->act_via_tma = std::atoi(at);
   if (const char* sg = std::getenv("B200LLM_STEPS_PER_GRAPH")) e->steps_per_graph = std::max(1, std::min(32, std::atoi(sg)));
   if (const char* pair = std::getenv("B200LLM_PAIR")) e->pair_mode = std::atoi(pair);
@@ -944,7 +946,10 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   p.max_len = max_len;
   p.logits_all = logits_all_dev;
   p.store_logits = true;
-  p.pdl = 0;
+  // Programmatic launch for the kernels that wait on their grid dependency themselves (GEMMs,
+  // LayerNorm, select); prefill attention is a plain launch and so still waits for the whole QKV
+  // GEMM. A one-request prompt is ~90 tiny kernels: the launch gaps are most of its time.
+  p.pdl = (e->cfg.use_pdl && e->prefill_pdl) ? 1 : 0;
   B200_PROPAGATE(run_stack(e, p));
   e->last_batch = batch;
   return kOk;
