@@ -205,6 +205,7 @@ struct b200llm_engine {
   int skip_mask = 0;
   int sm_count = 148;
   int prefill_pdl = 1;  // B200LLM_PREFILL_PDL=0 disables
+  int prefill_split = 1;  // B200LLM_PREFILL_SPLIT=0: no split-K planes for short prompts
   int steps_per_graph = 4;  // decode steps captured per CUDA graph (B200LLM_STEPS_PER_GRAPH overrides)
   int act_via_tma = 0;  // B200LLM_ACT_TMA=1: decode GEMMs fetch activations through TMA (comparison aid)
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
@@ -590,6 +591,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   if (e->sm_count <= 0) e->sm_count = 148;
   if (const char* skip = std::getenv("B200LLM_SKIP")) e->skip_mask = std::atoi(skip);
   if (const char* pp = std::getenv("B200LLM_PREFILL_PDL")) e->prefill_pdl = std::atoi(pp);
+  if (const char* ps = std::getenv("B200LLM_PREFILL_SPLIT")) e->prefill_split = std::atoi(ps);
   if (const char* at = std::getenv("B200LLM_ACT_TMA")) e->act_via_tma = std::atoi(at);
   if (const char* sg = std::getenv("B200LLM_STEPS_PER_GRAPH")) e->steps_per_graph = std::max(1, std::min(32, std::atoi(sg)));
   if (const char* pair = std::getenv("B200LLM_PAIR")) e->pair_mode = std::atoi(pair);
@@ -950,6 +952,25 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   // LayerNorm, select); prefill attention is a plain launch and so still waits for the whole QKV
   // GEMM. A one-request prompt is ~90 tiny kernels: the launch gaps are most of its time.
   p.pdl = (e->cfg.use_pdl && e->prefill_pdl) ? 1 : 0;
+  // Short prompts (a single chat request): the two projections back to d have only
+  // ceil(n_tok / 128) * d / 128 tiles, a fraction of the SMs, and the MLP one runs 4d / 64
+  // k-blocks per tile. Split K into partial planes (reduced by the LayerNorm that follows, like
+  // in a decode step) when the decode-sized plane buffer can hold them.
+  if (n_tok <= 1024 && e->prefill_split) {
+    const int tiles = ((n_tok + 127) / 128) * ((e->d + 127) / 128);
+    auto pick = [&](int kb) {
+      int best = 1;
+      for (int sp = 2; sp <= 4; ++sp) {
+        if (kb % sp == 0 && tiles * sp <= e->sm_count &&
+            static_cast<size_t>(sp) * n_tok * e->d <= e->partials_floats) {
+          best = sp;
+        }
+      }
+      return best;
+    };
+    p.split_o = pick(e->d / 64);
+    p.split_p = pick(4 * e->d / 64);
+  }
   B200_PROPAGATE(run_stack(e, p));
   e->last_batch = batch;
   return kOk;

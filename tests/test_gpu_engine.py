@@ -257,6 +257,35 @@ def test_temperature_topk_sampling_matches_the_softmax_distribution(cuda):
     eng.close()
 
 
+@pytest.mark.parametrize("n_tok", [300, 700])
+def test_short_prompt_prefill_uses_split_k_planes(cuda, n_tok):
+    """One prompt of 257..1024 tokens (a single chat request): the out-projection and MLP
+    down-projection of the prefill run split-K into partial planes that the following LayerNorm
+    reduces. All-position logits must stay within the tolerance of the oracle, and greedy decoding
+    must continue from the cache that this prefill filled."""
+    shape = O.GPT2Shape(n_layer=2, n_head=4, d_model=256, vocab_size=1000, n_positions=1024, eos_token_id=999)
+    w = O.synthetic_weights(shape, seed=5)
+    N = 6
+    ids = O.synthetic_prompts(1, n_tok, vocab=998, seed=17)
+    ref_tok, ref_logits, margins = O.greedy_generate(shape, w, ids, N, min_new_tokens=N)
+    eng, E = _engine(shape, w, max_seqs=64, max_seq_len=1024, max_batch_tokens=1024, max_new_tokens=N + 1)
+    logits = torch.zeros(n_tok, shape.vocab_size, device=cuda)
+    slot = eng.seq_alloc(n_tok + N + 1)
+    eng.prefill(ids.tolist(), [slot], logits_all_ptr=logits.data_ptr())
+    eng.sync()
+    full = O.forward(shape, w, ids)[0]
+    err = (logits.cpu() - full).abs().max().item()
+    print(f"{n_tok}-token prompt: max |dlogit| over all positions = {err:.4f}")
+    assert err <= LOGIT_TOL
+    eng.seq_free(slot)
+    out = np.array(eng.generate(ids.tolist(), E.SamplingParams(max_new_tokens=N, min_new_tokens=N)))
+    ref = ref_tok.numpy()
+    same_prefix = np.cumprod(np.concatenate([np.ones((1, 1), bool), out[:, :-1] == ref[:, :-1]], 1), 1).astype(bool)
+    decisive = margins.numpy() > 2 * LOGIT_TOL
+    assert (out[same_prefix & decisive] == ref[same_prefix & decisive]).all()
+    eng.close()
+
+
 @pytest.mark.parametrize("dups", [(10, 0), (3000, 2500), (5000, 0)], ids=["short-list", "long-path", "tie-overflow"])
 def test_topk_sampling_with_tied_logits(cuda, dups):
     """Exact ties at the top-k boundary: rows of the tied embedding / LM-head matrix are duplicated,
