@@ -37,6 +37,7 @@ class _Request:
     t_submit: float = field(default_factory=time.perf_counter)
     t_start: float = 0.0
     slot: int = -1
+    n_done: int = 1  # tokens generated so far (prefill selects the first one), refreshed at every status read
 
 
 class EngineWorker(threading.Thread):
@@ -144,6 +145,7 @@ class EngineWorker(threading.Thread):
         eos = self.engine.shape.eos_token_id
         for req, n, fin in zip(self.active, counts, finished):
             if not fin:
+                req.n_done = int(n)
                 still.append(req)
                 continue
             tokens, _ = self.engine.read_tokens(req.slot, int(n))
@@ -180,7 +182,11 @@ class EngineWorker(threading.Thread):
                 t2 = clock()
                 self.phase_s["admit"] += t2 - t1
                 if self.active:
-                    self.engine.decode([r.slot for r in self.active], self.decode_burst)
+                    # no more steps than the longest remaining generation needs (a lone 32-token
+                    # request runs 8 + 8 + 8 + 7 steps, not 4 x 8)
+                    cap = self.engine.cfg.max_new_tokens
+                    left = max(min(r.sampling.max_new_tokens, cap) - r.n_done for r in self.active)
+                    self.engine.decode([r.slot for r in self.active], max(1, min(self.decode_burst, left)))
                     t3 = clock()
                     self._retire()
                     t4 = clock()

@@ -28,6 +28,17 @@ def test_concurrent_requests_are_batched_and_all_complete():
     r.shutdown()
 
 
+def test_a_lone_request_runs_no_more_decode_steps_than_it_needs():
+    """32 new tokens = 1 from prefill + 31 decode steps: bursts of 8 + 8 + 8 + 7, not 4 x 8."""
+    eng = FakeEngine(max_seqs=4, max_seq_len=128, max_new_tokens=64)
+    r = _router(eng, decode_burst=8)
+    res = r.generate([1, 2, 3], SamplingParams(max_new_tokens=32), timeout=10)
+    assert len(res.tokens) == 32
+    steps = [c[2] for c in eng.calls if c[0] == "decode"]
+    assert sum(steps) == 31 and max(steps) <= 8, steps
+    r.shutdown()
+
+
 def test_eos_ends_a_request_early_with_finish_reason_stop():
     eng = FakeEngine(max_seqs=4, max_new_tokens=16, eos_every=7)
     r = _router(eng)
