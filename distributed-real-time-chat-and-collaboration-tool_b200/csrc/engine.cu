@@ -473,6 +473,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
     g.act_rows_alloc = e->max_rows;
     g.force_orientation = 1;
     g.pdl = pdl;
+    g.amax_groups_alloc = e->n_groups;
     g.amax_val = e->amax_val;
     g.amax_idx = e->amax_idx;
     g.eos_logit = e->eos_logit;
@@ -488,7 +489,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
   s.amax_val = e->amax_val;
   s.amax_idx = e->amax_idx;
   s.eos_logit = e->eos_logit;
-  s.n_groups = e->n_groups;
+  s.n_groups = std::min(e->n_groups, gemm_argmax_groups(e->V, head_rows));
   s.ld_amax = e->logits_rows;
   s.active_slots = p.decode ? e->active_dev : e->slots_dev;
   s.batch = head_rows;
@@ -731,9 +732,17 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   E_CUDA(cudaMemsetAsync(e->x, 0, R * d * sizeof(float), st));
   e->logits_rows = dec_rows;
   E_TRY(dev_alloc_t(e.get(), &e->logits, static_cast<size_t>(e->logits_rows) * V));
-  e->n_groups = ((V + 127) / 128) * 4;
+  // candidate groups of the LM head's fused argmax: whole-tile layout or balanced row ranges,
+  // depending on the row count of a launch (gemm_argmax_groups); the arrays hold the larger and
+  // start at -inf, which is what a group that a layout leaves out must contain
+  e->n_groups = std::max(((V + 127) / 128) * 4, gemm_argmax_groups(V, 1));
   E_TRY(dev_alloc_t(e.get(), &e->amax_val, static_cast<size_t>(e->n_groups) * e->logits_rows));
   E_TRY(dev_alloc_t(e.get(), &e->amax_idx, static_cast<size_t>(e->n_groups) * e->logits_rows));
+  {
+    std::vector<float> ninf(static_cast<size_t>(e->n_groups) * e->logits_rows, -INFINITY);
+    E_CUDA(cudaMemcpy(e->amax_val, ninf.data(), ninf.size() * sizeof(float), cudaMemcpyHostToDevice));
+    E_CUDA(cudaMemset(e->amax_idx, 0, ninf.size() * sizeof(int32_t)));
+  }
   E_TRY(dev_alloc_t(e.get(), &e->eos_logit, static_cast<size_t>(e->logits_rows)));
   e->slot_samples.assign(cfg->max_seqs, 0);
   // split-K planes: at most 32 splits of [decode rows, d]

@@ -91,6 +91,14 @@ struct KernelArgs {
   // operand tiles complete on full_bar[0], the MMA thread waits once and issues one uninterrupted
   // chain (the per-k-block wait + fence + commit costs more than the MMAs of a 16..64-token tile).
   int single_pass;
+  // BAL instantiation (swapped orientation, one token tile, more weight tiles than CTAs -- the LM
+  // head: 393 tiles on 148 SMs): instead of striding whole 128-row tiles (97 CTAs get three, 51 get
+  // two, and the launch takes as long as three everywhere), CTA c owns rows
+  // [c * bal_rows, (c + 1) * bal_rows) and cuts them into 128-row tiles plus a tail of
+  // bal_tail_rows, loaded with a smaller TMA box (the third tensor map). bal_rows is a multiple of
+  // 32 so a warp's 32 rows stay an aligned group.
+  int bal_rows;
+  int bal_tail_rows;  // bal_rows % 128 (0 = no tail tile)
 };
 
 template <int N>
@@ -120,7 +128,7 @@ __device__ __forceinline__ void tmem_ld_cols<16>(uint32_t taddr, uint32_t (&r)[3
 // tile hit 32 different cache lines per instruction and made the prefill GEMMs epilogue-bound.
 constexpr int kEpiBoxBytes = kBlockM * 128;  // one staging box: 128 rows x 128 B
 
-template <int BLOCK_N, int EPI, bool TRANS, bool TMA_EPI>
+template <int BLOCK_N, int EPI, bool TRANS, bool TMA_EPI, bool BAL = false>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
             const __grid_constant__ CUtensorMap map_out, const KernelArgs args) {
@@ -147,7 +155,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
 
   const int num_m_blocks = (args.a_rows + kBlockM - 1) / kBlockM;
   const int num_n_blocks = (args.b_rows + BLOCK_N - 1) / BLOCK_N;
-  const int num_tiles = num_m_blocks * num_n_blocks;
+  // BAL: this CTA's row range and tile count; `num_tiles` is then chosen so that the strided loops
+  // below (tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) run exactly bal_my_tiles times
+  const int bal_begin = BAL ? static_cast<int>(blockIdx.x) * args.bal_rows : 0;
+  const int bal_end = BAL ? min(bal_begin + args.bal_rows, args.a_rows) : 0;
+  const int bal_my_tiles = (BAL && bal_end > bal_begin) ? (bal_end - bal_begin + kBlockM - 1) / kBlockM : 0;
+  const int bal_tiles_per_cta = BAL ? (args.bal_rows + kBlockM - 1) / kBlockM : 0;
+  const int num_tiles =
+      BAL ? (bal_my_tiles > 0 ? static_cast<int>(blockIdx.x) + (bal_my_tiles - 1) * static_cast<int>(gridDim.x) + 1 : 0)
+          : num_m_blocks * num_n_blocks;
   const int split = blockIdx.y;
   const int kb_begin = split * args.k_blocks_per_split;
   int kb_end = kb_begin + args.k_blocks_per_split;
@@ -203,6 +219,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         const int kb = kb_begin + it % num_kb;
         const int m_blk = tile % num_m_blocks;
         uint8_t* sa = ring + it * Cfg::kStageBytes;
+        if constexpr (BAL) {
+          const int row0 = bal_begin + (it / num_kb) * kBlockM;
+          const bool tail = args.bal_tail_rows > 0 && bal_end - row0 <= args.bal_tail_rows;
+          mbar_arrive_expect_tx(&full_bar[it], (tail ? static_cast<uint32_t>(args.bal_tail_rows) * 128u
+                                                     : static_cast<uint32_t>(Cfg::kABytes)) +
+                                                   static_cast<uint32_t>(Cfg::kStageBytes - Cfg::kABytes));
+          tma_load_2d(sa, tail ? &map_out : &map_a, &full_bar[it], kb * kBlockK, row0, kEvictFirst);
+          continue;
+        }
         if (!single) mbar_arrive_expect_tx(&full_bar[it], Cfg::kStageBytes);
         tma_load_2d(sa, &map_a, &full_bar[single ? 0 : it], kb * kBlockK, m_blk * kBlockM, kEvictFirst);
       }
@@ -212,7 +237,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       for (int it = 0; it < pre; ++it) {
         const int tile = blockIdx.x + (it / num_kb) * gridDim.x;
         const int kb = kb_begin + it % num_kb;
-        const int n_blk = tile / num_m_blocks;
+        const int n_blk = BAL ? 0 : tile / num_m_blocks;
         uint8_t* sb = ring + it * Cfg::kStageBytes + Cfg::kABytes;
         tma_load_2d(sb, &map_b, &full_bar[single ? 0 : it], kb * kBlockK, n_blk * BLOCK_N, kEvictLast);
       }
@@ -222,10 +247,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         const int tile = blockIdx.x + (it / num_kb) * gridDim.x;
         const int kb = kb_begin + it % num_kb;
         const int m_blk = tile % num_m_blocks;
-        const int n_blk = tile / num_m_blocks;
+        const int n_blk = BAL ? 0 : tile / num_m_blocks;
         mbar_wait(&empty_bar[stage], phase ^ 1u);
         uint8_t* sa = ring + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kABytes;
+        if constexpr (BAL) {
+          const int row0 = bal_begin + (it / num_kb) * kBlockM;
+          const bool tail = args.bal_tail_rows > 0 && bal_end - row0 <= args.bal_tail_rows;
+          mbar_arrive_expect_tx(&full_bar[stage], (tail ? static_cast<uint32_t>(args.bal_tail_rows) * 128u
+                                                        : static_cast<uint32_t>(Cfg::kABytes)) +
+                                                      static_cast<uint32_t>(Cfg::kStageBytes - Cfg::kABytes));
+          tma_load_2d(sa, tail ? &map_out : &map_a, &full_bar[stage], kb * kBlockK, row0, kEvictFirst);
+          tma_load_2d(sb, &map_b, &full_bar[stage], kb * kBlockK, 0, kEvictLast);
+          continue;
+        }
         mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
         tma_load_2d(sa, &map_a, &full_bar[stage], kb * kBlockK, m_blk * kBlockM,
                     TRANS ? kEvictFirst : kEvictNormal);
@@ -327,12 +362,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     pdl_wait();  // residual / output buffers may be read by the upstream kernel
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile % num_m_blocks;
-      const int n_blk = tile / num_m_blocks;
+      const int n_blk = BAL ? 0 : tile / num_m_blocks;
       mbar_wait(&tmem_full_bar[astage], aphase);
       if (threadIdx.x == 128) B200_TRACE(6);
       tc_fence_after();
-      const int a_row = m_blk * kBlockM + q * 32 + lane;  // row of the 128-row operand
-      const bool a_ok = a_row < args.a_rows;
+      const int bal_i = BAL ? (tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x) : 0;
+      const int a_row = (BAL ? bal_begin + bal_i * kBlockM : m_blk * kBlockM) + q * 32 + lane;  // row of the 128-row operand
+      const bool a_ok = BAL ? (a_row < bal_end) : (a_row < args.a_rows);
+      const int group0 = BAL ? (static_cast<int>(blockIdx.x) * bal_tiles_per_cta + bal_i) * 4 : m_blk * 4;
 
       float bias_lane = 0.0f;
       if (TRANS && EPI != kEpiF32 && EPI != kEpiPartialF32 && EPI != kEpiLogitsArgmax && a_ok &&
@@ -510,7 +547,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           const int col = (kChunk == 32) ? lane : (lane & 15);
           const int token = b_row0 + col;
           if ((kChunk == 32 || lane < 16) && token < args.b_rows) {
-            const size_t pidx = static_cast<size_t>(m_blk * 4 + q) * args.ld_amax + token;
+            const size_t pidx = static_cast<size_t>(group0 + q) * args.ld_amax + token;
             args.amax_val[pidx] = v[0];
             args.amax_idx[pidx] = idx[0];
           }
@@ -1254,6 +1291,18 @@ int num_sms() {
   return n;
 }
 
+// Rows per CTA for the balanced swap-AB layout, or 0 when whole tiles are as good: one token tile,
+// no split-K, more 128-row weight tiles than SMs, and a smaller per-CTA maximum than striding gives.
+int balanced_rows(int a_rows, int b_rows, int block_n, int split) {
+  const int sms = num_sms();
+  const int num_m = (a_rows + kBlockM - 1) / kBlockM;
+  if (split > 1 || b_rows > block_n || num_m <= sms) return 0;
+  const int rows = (((a_rows + sms - 1) / sms) + 31) / 32 * 32;
+  const int strided_max = ((num_m + sms - 1) / sms) * kBlockM;
+  return rows < strided_max ? rows : 0;
+}
+int balanced_groups(int bal_rows) { return num_sms() * ((bal_rows + kBlockM - 1) / kBlockM) * 4; }
+
 template <int BLOCK_N, int EPI, bool TRANS, bool TMA_EPI = false>
 int launch(const GemmArgs& g, cudaStream_t stream) {
   using Cfg = TileCfg<BLOCK_N>;
@@ -1315,6 +1364,27 @@ int launch(const GemmArgs& g, cudaStream_t stream) {
     B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       Cfg::smem_bytes(Cfg::kMaxStages) + kEpiBytes));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  // balanced row ranges (KernelArgs::bal_rows): LM-head shaped launches only, own instantiation
+  ka.bal_rows = 0;
+  ka.bal_tail_rows = 0;
+  if constexpr (TRANS && !TMA_EPI && (EPI == kEpiF32 || EPI == kEpiLogitsArgmax)) {
+    const int bal = g.act_via_tma ? 0 : balanced_rows(a_rows, b_rows, BLOCK_N, split);
+    if (bal > 0 && !ka.single_pass &&
+        (EPI != kEpiLogitsArgmax || balanced_groups(bal) <= g.amax_groups_alloc)) {
+      ka.bal_rows = bal;
+      ka.bal_tail_rows = bal % kBlockM;
+      if (ka.bal_tail_rows > 0) {
+        B200_PROPAGATE(get_tensor_map(a_ptr, a_rows_map, g.k, ka.bal_tail_rows, &map_out));
+      }
+      kernel = gemm_kernel<BLOCK_N, EPI, TRANS, TMA_EPI, true>;
+      static bool bal_attr_set[64] = {};
+      if (dev < 0 || dev >= 64 || !bal_attr_set[dev]) {
+        B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          Cfg::smem_bytes(Cfg::kMaxStages) + kEpiBytes));
+        if (dev >= 0 && dev < 64) bal_attr_set[dev] = true;
+      }
+    }
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid_x, split, 1);
@@ -1490,6 +1560,16 @@ B200_DEFINE_STEP_TRACE_SETTER(step_trace_set_gemm)
 void gemm_clear_tensor_map_cache() {
   std::lock_guard<std::mutex> lock(map_mutex());
   map_cache().clear();
+}
+
+int gemm_argmax_groups(int features, int tokens) {
+  int block_n = 256;
+  if (tokens <= 16) block_n = 16;
+  else if (tokens <= 32) block_n = 32;
+  else if (tokens <= 64) block_n = 64;
+  else if (tokens <= 128) block_n = 128;
+  const int bal = balanced_rows(features, tokens, block_n, 1);
+  return bal > 0 ? balanced_groups(bal) : ((features + kBlockM - 1) / kBlockM) * 4;
 }
 
 int gemm_bf16(const GemmArgs& g, cudaStream_t stream) {

@@ -51,10 +51,16 @@ struct GemmArgs {
   // swap-AB launches whose CTAs keep all their k-blocks in the ring copy the activation operand
   // with ordinary loads; 1 forces the TMA path for it (A/B comparisons, tests)
   int act_via_tma;
+  int amax_groups_alloc;  // kEpiLogitsArgmax: group rows the amax arrays can hold (see gemm_argmax_groups)
 };
 
 // Enqueue one GEMM on `stream`. Returns 0 or an error code (see common.cuh Status).
 int gemm_bf16(const GemmArgs& args, cudaStream_t stream);
+
+// kEpiLogitsArgmax: number of candidate groups (rows of amax_val / amax_idx) a launch with this
+// shape writes or leaves untouched; untouched ones must hold -inf (the arrays start that way and
+// no launch shape ever writes a group another shape leaves out).
+int gemm_argmax_groups(int features, int tokens);
 
 // Drop cached tensor maps (engine teardown / tests).
 void gemm_clear_tensor_map_cache();
