@@ -746,7 +746,10 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   E_TRY(dev_alloc_t(e.get(), &e->eos_logit, static_cast<size_t>(e->logits_rows)));
   e->slot_samples.assign(cfg->max_seqs, 0);
   // split-K planes: at most 32 splits of [decode rows, d]
-  e->partials_floats = static_cast<size_t>(32) * dec_rows * d;
+  // decode planes (up to 32 per row of the largest bucket), and room for the 2..4 planes of a
+  // short-prompt prefill (<= 1024 rows) whatever max_seqs is
+  e->partials_floats = std::max(static_cast<size_t>(32) * dec_rows * d,
+                                static_cast<size_t>(4) * std::min(1024, e->cfg.max_batch_tokens) * d);
   E_TRY(dev_alloc_t(e.get(), &e->partials, e->partials_floats));
   e->attn_scratch_floats = decode_attention_scratch_floats(dec_rows, H, 16);
   E_TRY(dev_alloc_t(e.get(), &e->attn_scratch, e->attn_scratch_floats));
