@@ -10,6 +10,7 @@ requests across the per-GPU workers by in-flight token count -- replicas only, n
 """
 from __future__ import annotations
 
+import os
 import queue
 import threading
 import time
@@ -48,7 +49,8 @@ class EngineWorker(threading.Thread):
     def __init__(self, engine, *, decode_burst: int = 8, name: str = "b200llm-worker"):
         super().__init__(name=name, daemon=True)
         self.engine = engine
-        self.decode_burst = decode_burst
+        # B200LLM_DECODE_BURST overrides the steps per burst (throughput / admission-latency trade-off)
+        self.decode_burst = int(os.environ.get("B200LLM_DECODE_BURST", decode_burst))
         self.inbox: "queue.Queue[_Request | None]" = queue.Queue()
         self.active: list[_Request] = []
         self.waiting: list[_Request] = []
