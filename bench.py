@@ -42,6 +42,11 @@ WORKLOADS = {
 }
 
 
+BASELINE_CONFIG = {"smart_reply_b64": "BASELINE configs[1]", "smart_reply_b1": "BASELINE configs[0]",
+                   "summarize_medium": "BASELINE configs[2]", "ask_large_b32": "BASELINE configs[3], one GPU's shard of 8",
+                   "ask_large_b256": "BASELINE configs[3] on one GPU"}
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -114,22 +119,28 @@ def measured_peaks() -> tuple[dict, str]:
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
-def lmhead_traffic_from_profile() -> float | None:
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the LM-head GEMM, from the
-    committed `ncu --set full` capture (profiles/r1_lmhead_ncu_full.csv)."""
+LMHEAD_PROFILES = ["r2_lmhead_argmax_ncu_full.csv", "r1_lmhead_ncu_full.csv"]
+
+
+def lmhead_traffic_from_profile() -> tuple[float | None, str | None]:
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the LM-head GEMM, from the newest
+    committed `ncu --set full` capture under profiles/."""
     import csv
 
-    path = os.path.join(ROOT, "profiles", "r1_lmhead_ncu_full.csv")
-    if not os.path.exists(path):
-        return None
+    path = next((os.path.join(ROOT, "profiles", n) for n in LMHEAD_PROFILES
+                 if os.path.exists(os.path.join(ROOT, "profiles", n))), None)
+    if path is None:
+        return None, None
     rows = list(csv.reader(open(path)))
     hdr = rows[0]
     try:
         ri, wi = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
-        vals = [(float(r[ri]) + float(r[wi])) * 1e6 for r in rows[2:] if len(r) > max(ri, wi)]
-        return sum(vals) / len(vals) if vals else None
+        unit = rows[1][ri].lower() if len(rows) > 1 else "mbyte"
+        scale = {"byte": 1.0, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(unit, 1e6)
+        vals = [(float(r[ri]) + float(r[wi])) * scale for r in rows[2:] if len(r) > max(ri, wi)]
+        return (sum(vals) / len(vals) if vals else None), "profiles/" + os.path.basename(path)
     except (ValueError, IndexError):
-        return None
+        return None, None
 
 
 def decode_step_bytes(shape, batch: int, ctx: int) -> int:
@@ -322,26 +333,28 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     assert len(out) == B and all(len(o) == N for o in out)
 
-    # ---- dominant kernel in isolation: LM-head GEMM of a decode step (weights streamed once) ----
+    # ---- longest single kernel of the decode step in isolation: the LM head exactly as the step
+    # launches it (fused greedy argmax, no logits stored; b200llm_op_lm_head_argmax) ----
     V, d = shape.vocab_size, shape.d_model
     n_copies = 4  # 4 x 77 MB > 126 MB L2: every launch reads its weights from HBM
+    Bh = min(max(B, 1), 256)
     with torch.cuda.stream(stream):
         wcopies = [torch.randn(V, d, device=dev).to(torch.bfloat16) * 0.02 for _ in range(n_copies)]
-        act = torch.randn(max(B, 1), d, device=dev).to(torch.bfloat16)
-        lg = torch.empty(max(B, 1), V, device=dev)
+        act = torch.randn(Bh, d, device=dev).to(torch.bfloat16)
+        work = None
         for i in range(4):
-            ops.gemm(act, wcopies[i % n_copies], None, lg, ops.EPI_F32)
+            work = ops.lm_head_argmax(act, wcopies[i % n_copies], shape.eos_token_id, None, work)
         reps = 40
         k0 = torch.cuda.Event(enable_timing=True)
         k1 = torch.cuda.Event(enable_timing=True)
         stream.synchronize()
         k0.record(stream)
         for i in range(reps):
-            ops.gemm(act, wcopies[i % n_copies], None, lg, ops.EPI_F32)
+            ops.lm_head_argmax(act, wcopies[i % n_copies], shape.eos_token_id, None, work)
         k1.record(stream)
         stream.synchronize()
     head_ms = k0.elapsed_time(k1) / reps
-    head_bytes = V * d * 2 + B * d * 2 + B * V * 4
+    head_bytes = V * d * 2 + Bh * d * 2
     del wcopies
 
     # ---- reduce over ranks ----
@@ -375,10 +388,10 @@ def run_ours(args):
         "data": "synthetic",
         "config": {
             "workload": f"{args.workload}: GPT-2 {model} ({shape.n_layer}L d={shape.d_model}), batch {B} per GPU, "
-                        f"{T}-token prompts, {N} new tokens, greedy (BASELINE configs[1])",
+                        f"{T}-token prompts, {N} new tokens, greedy ({BASELINE_CONFIG.get(args.workload, 'profiling probe')})",
             "weights": "random init seed 0 (HF init scheme), bf16 GEMM weights, fp32 residual stream",
             "parallelism": f"request-sharded replicas x{world}, no data-path collective",
-            "l2": "no flush: each decode step streams 247 MB of weights + KV (> 126 MB L2)",
+            "l2": f"no flush: each decode step streams {step_bytes / 1e6:.0f} MB of weights + KV (> 126 MB L2)",
             "prefill_ms": prefill_ms,
             "decode_ms_per_token_step": decode_step_ms,
         },
@@ -393,7 +406,9 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {
             "bound": "hbm",
-            "kernel": "gemm_kernel<64, kEpiF32, swap-AB> (LM head of one decode step)",
+            "kernel": "gemm_kernel<kEpiLogitsArgmax, swap-AB, balanced rows> -- the LM head with fused greedy argmax "
+                      "as the decode step launches it (b200llm_op_lm_head_argmax); the longest single kernel of the "
+                      "step but only ~5 % of it: decode_step_roofline below is the whole-step figure",
             "achieved": head_bytes / (head_ms * 1e-3) / 1e9,
             "peak": peaks["hbm_gbs"],
             "unit": "GB/s",
@@ -401,8 +416,9 @@ def run_ours(args):
             "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
             "bytes_per_launch": head_bytes,
             "us_per_launch": head_ms * 1e3,
-            "traffic": lmhead_traffic_from_profile(),
-            "traffic_source": "profiles/r1_lmhead_ncu_full.csv (ncu --set full, B = 64)",
+            "traffic": lmhead_traffic_from_profile()[0],
+            "traffic_source": f"{lmhead_traffic_from_profile()[1]} (ncu --set full, B = 64)",
+            "algorithmic_bytes": "V*d*2 (tied head weights, bf16) + B*d*2 (activations); no logits are stored",
         },
         "decode_step_roofline": {
             "bound": "hbm",
@@ -415,6 +431,11 @@ def run_ours(args):
         },
     }
     eng.close()
+    if rank == 0 and world == 1 and not args.no_decode_classes:
+        result["decode_classes"] = decode_classes(args.workload, peaks["hbm_gbs"])
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # what was timed is also what is right: the first batch's tokens against the CPU oracle
+        result["parity_check"] = parity_check(shape, blob, prompts_np, np.array(out), N)
     if rank == 0 and model == "small" and not args.no_smart_reply:
         result["smart_reply"] = smart_reply_latency(E, shape, blob, local,
                                                     cpu_calls=0 if (args.no_cpu_baseline or world > 1) else 3)
@@ -427,9 +448,53 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def decode_classes(workload: str, hbm_gbs: float) -> dict | None:
+    """In-graph cost of every kernel class of the decode step, read by leaving the class out
+    (B200LLM_SKIP, honoured only by libb200llm_tune.so) -- profiles/decode_classes.py in a
+    subprocess so that the product library of this process never sees a tuning switch."""
+    tune = os.path.join(ROOT, PKG, "libb200llm_tune.so")
+    if not os.path.exists(tune):
+        return {"unavailable": "libb200llm_tune.so not built (python __graft_entry__.py build)"}
+    env = dict(os.environ, B200LLM_LIB=tune)
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "profiles", "decode_classes.py"), workload,
+                            str(hbm_gbs)], env=env, capture_output=True, text=True, timeout=600)
+        line = [l for l in r.stdout.splitlines() if l.startswith("{")]
+        return json.loads(line[-1]) if r.returncode == 0 and line else {"unavailable": (r.stderr or r.stdout)[-300:]}
+    except Exception as exc:  # noqa: BLE001
+        return {"unavailable": repr(exc)}
+
+
 # ------------------------------------------------------------------------------------------
 # CPU legs (the only place bench.py touches oracle/)
 # ------------------------------------------------------------------------------------------
+def parity_check(shape, blob, prompts_np, tokens, N: int, rows: int = 4, margin: float = 0.1) -> dict:
+    """Checker only (never timed): the oracle, teacher-forced with the engine's own tokens of the
+    first batch, must pick the same token wherever its top-1/top-2 margin is decisive."""
+    import torch
+
+    from oracle import gpt2_oracle as O
+
+    oshape = O.GPT2Shape(n_layer=shape.n_layer, n_head=shape.n_head, d_model=shape.d_model,
+                         vocab_size=shape.vocab_size, n_positions=shape.n_positions, ln_eps=shape.ln_eps,
+                         eos_token_id=shape.eos_token_id)
+    w = O.unpack_blob(oshape, blob)
+    sel = np.linspace(0, prompts_np.shape[0] - 1, min(rows, prompts_np.shape[0])).astype(int)
+    steps = min(N, 32)
+    teacher = torch.from_numpy(tokens[sel][:, :steps]).long()
+    ref, _, margins = O.greedy_generate(oshape, w, torch.from_numpy(prompts_np[sel]).long(), steps,
+                                        min_new_tokens=steps, teacher=teacher)
+    agree = (ref == teacher).numpy()
+    decisive = margins.numpy() > margin
+    ok = bool(agree[decisive].all())
+    res = {"rows": sel.tolist(), "steps": steps, "agreement": float(agree.mean()),
+           "decisive_fraction": float(decisive.mean()), "decisive_margin": margin, "ok": ok,
+           "checker": "oracle.greedy_generate teacher-forced with the engine's tokens"}
+    if not ok:
+        raise SystemExit(f"bench.py: the timed batch disagrees with the oracle at a decisive margin: {res}")
+    return res
+
+
 def _cpu_setup(workload: str):
     import torch
 
@@ -498,7 +563,7 @@ def run_reference(args):
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: GPT-2 {model} ({shape.n_layer}L d={shape.d_model}), batch {B} per GPU, "
-                               f"{T}-token prompts, {N} new tokens, greedy (BASELINE configs[1])",
+                               f"{T}-token prompts, {N} new tokens, greedy ({BASELINE_CONFIG.get(args.workload, 'profiling probe')})",
                    "note": "CPU reference arm (transformers on the host cores); rank 0 only"},
         "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -515,6 +580,7 @@ def main():
     ap.add_argument("--workload", default="smart_reply_b64", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-smart-reply", action="store_true", help="skip the p50 SmartReply gRPC measurement")
+    ap.add_argument("--no-decode-classes", action="store_true", help="skip the per-class decode ablation")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -28,7 +28,10 @@ class B200Error(RuntimeError):
 
 
 class Config(C.Structure):
+    """b200llm_config, field for field (tests/test_cabi_exports.py compares this with the header).
+    struct_size is filled in on construction."""
     _fields_ = [
+        ("struct_size", C.c_uint32),
         ("n_layer", C.c_int32),
         ("n_head", C.c_int32),
         ("d_model", C.c_int32),
@@ -48,7 +51,13 @@ class Config(C.Structure):
         ("decode_split_k", C.c_int32),
         ("keep_logits", C.c_int32),
         ("decode_reduce", C.c_int32),
+        ("prefix_cache", C.c_int32),
     ]
+
+    def __init__(self, *args, **kw):
+        super().__init__(*args, **kw)
+        if not self.struct_size:
+            self.struct_size = C.sizeof(Config)
 
 
 class Sampling(C.Structure):
@@ -86,6 +95,14 @@ def _load() -> C.CDLL:
         "b200llm_engine_set_stream": (C.c_int, [vp, vp]),
         "b200llm_seq_alloc": (C.c_int, [vp, i32, P(i32)]),
         "b200llm_seq_free": (C.c_int, [vp, i32]),
+        "b200llm_seq_alloc_with_prefix": (C.c_int, [vp, vp, i32, i32, P(i32), P(i32)]),
+        "b200llm_prefix_cache_stats": (C.c_int, [vp, P(i64), P(i64), P(i64)]),
+        "b200llm_seq_cancel": (C.c_int, [vp, i32]),
+        "b200llm_read_tokens_batch": (C.c_int, [vp, vp, i32, i32, vp, i32, vp, vp]),
+        "b200llm_op_lm_head_argmax": (C.c_int, [vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp]),
+        "b200llm_lm_head_argmax_groups": (i32, [i32, i32]),
+        "b200llm_op_prefill_attention_paged": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, vp, i32, vp, vp, vp, vp]),
+        "b200llm_op_kv_scatter": (C.c_int, [vp, vp, vp, i32, i32, vp, i32, vp, vp, vp]),
         "b200llm_kv_pages_free": (C.c_int, [vp, P(i64), P(i64)]),
         "b200llm_prefill": (C.c_int, [vp, vp, i32, vp, vp, vp, i32, vp]),
         "b200llm_decode": (C.c_int, [vp, vp, i32, i32]),

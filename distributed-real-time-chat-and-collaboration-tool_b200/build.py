@@ -46,16 +46,30 @@ def _compile(src: Path, obj: Path) -> str:
     return log
 
 
-def build_trace_variant() -> Path:
-    """Profiling-only library with the kernels' clock64 milestone traces compiled in."""
-    out = HERE / "libb200llm_trace.so"
-    srcs = [str(CSRC / n) for n in SOURCES]
+def _variant(out: Path, defines: list[str]) -> Path:
+    srcs = [CSRC / n for n in SOURCES]
+    headers = sorted(CSRC.glob("*.cuh")) + [HERE.parent / "include" / "b200llm.h"]
+    if not _stale(out, [*srcs, *headers]):
+        return out
     flags = [f for f in FLAGS if f not in ("-Xptxas", "-v")]
-    cmd = [NVCC, *flags, "-DB200_ATTN_TRACE", "-DB200_STEP_TRACE", "-shared", "-o", str(out), *srcs, "-lcudart"]
+    cmd = [NVCC, *flags, *defines, "-shared", "-o", str(out), *map(str, srcs), "-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(r.stdout + r.stderr)
     return out
+
+
+def build_trace_variant() -> Path:
+    """Profiling-only library with the kernels' clock64 milestone traces compiled in."""
+    return _variant(HERE / "libb200llm_trace.so", ["-DB200_ATTN_TRACE", "-DB200_STEP_TRACE", "-DB200_TUNE_KNOBS"])
+
+
+def build_tune_variant() -> Path:
+    """The product code plus the environment switches used for ablations and sweeps
+    (B200LLM_SKIP, B200LLM_SPLITS, ...). The product library reads no
+    environment variable; bench.py's decode_classes leg and profiles/*.sh load this one through
+    B200LLM_LIB."""
+    return _variant(HERE / "libb200llm_tune.so", ["-DB200_TUNE_KNOBS"])
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
@@ -84,6 +98,9 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 if __name__ == "__main__":
     if "--trace" in sys.argv:
         print(build_trace_variant())
+        sys.exit(0)
+    if "--tune" in sys.argv:
+        print(build_tune_variant())
         sys.exit(0)
     lib = build(force="--force" in sys.argv, verbose="-v" in sys.argv)
     print(lib)

@@ -7,10 +7,11 @@
 //   BASELINE configs; the tcgen05 path is used for the GEMMs that dominate.
 //
 // decode_attn_kernel : one new token per sequence against the paged KV cache. HBM-bound:
-//   every K/V byte is read exactly once with 16-byte no-allocate loads, 8 lanes per cached
-//   token (one 128-byte row), 16 tokens (= one 2 KB page of a head) per CTA iteration, 4-way
-//   unrolled so each thread keeps 8 independent 16-byte loads in flight; softmax statistics
-//   by warp shuffles. Optional split-KV for long contexts with a deterministic combine pass.
+//   one CTA (4 warps) per (row, head, KV split) stages its cached K/V rows in shared memory with
+//   cp.async, 128 tokens per pass (the first pass before the grid dependency resolves), every
+//   K/V byte read once; both products on the tensor cores (mma.sync m16n8k16, query split into
+//   two bf16 parts), online softmax per warp. Optional split-KV for long contexts, merged
+//   deterministically by a combine pass or, for small grids, inside a thread-block cluster.
 #include "attention.cuh"
 
 #include <cstdlib>
@@ -100,9 +101,36 @@ __device__ __forceinline__ void load_tile_64x64_async(__nv_bfloat16 (*dst)[kLds]
   }
 }
 
+// The same tile, gathered from KV pages ([page][head][16 tokens][64]): key position pos0 + row of
+// one head; rows at or beyond `total` are zero-filled.
+__device__ __forceinline__ void load_tile_64x64_paged(__nv_bfloat16 (*dst)[kLds], const __nv_bfloat16* pool,
+                                                      const int32_t* pt, int n_head, int h, int pos0,
+                                                      int total) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = threadIdx.x + 128 * i;
+    const int row = c >> 3;
+    const int col = (c & 7) * 8;
+    const int pos = pos0 + row;
+    const bool ok = pos < total;
+    const int page = ok ? pt[pos / kPageTokens] : 0;
+    const __nv_bfloat16* g =
+        pool + ((static_cast<size_t>(page) * n_head + h) * kPageTokens + (ok ? pos % kPageTokens : 0)) * kHeadDim + col;
+    const int bytes = ok ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(&dst[row][col])), "l"(g),
+                 "r"(bytes)
+                 : "memory");
+  }
+}
+
+// kPaged = false: the prompt's own K/V rows come from the packed qkv buffer (and the diagonal
+// CTA fills the pages). kPaged = true (shared-prefix reuse): the rows are prompt suffixes at
+// positions prefix + 0, 1, ...; every key is read from the pages.
+template <bool kPaged>
 __global__ void __launch_bounds__(128)
 prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ cu_seqlens,
-                    int n_head, __nv_bfloat16* __restrict__ out, PrefillCache cache) {
+                    int n_head, __nv_bfloat16* __restrict__ out, PrefillCache cache,
+                    const int32_t* __restrict__ prefix_len) {
   __shared__ __align__(16) __nv_bfloat16 sQ[kBQ][kLds];
   __shared__ __align__(16) __nv_bfloat16 sKb[2][kBKV][kLds];  // double-buffered K/V tiles
   __shared__ __align__(16) __nv_bfloat16 sVb[2][kBKV][kLds];
@@ -111,8 +139,15 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
   const int h = blockIdx.y;
   const int qt = blockIdx.x;
   const int row0 = cu_seqlens[b];
-  const int len = cu_seqlens[b + 1] - row0;
-  if (qt * kBQ >= len) return;
+  const int len_q = cu_seqlens[b + 1] - row0;       // rows of this sequence in qkv
+  if (qt * kBQ >= len_q) return;
+  const int prefix = kPaged ? prefix_len[b] : 0;    // keys in front of them, already in the pages
+  const int len = prefix + len_q;                   // keys in all
+  const int32_t* pt = (kPaged || cache.slots != nullptr)
+                          ? cache.page_table + static_cast<size_t>(cache.slots[b]) * cache.max_pages_per_seq
+                          : nullptr;
+  // last key tile this CTA's queries can see
+  const int kt_last = kPaged ? (prefix + min(len_q, (qt + 1) * kBQ) - 1) / kBKV : qt;
   const int d = n_head * kHeadDim;
   const int ld = 3 * d;
   const int warp = threadIdx.x >> 5;
@@ -123,9 +158,14 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
   const __nv_bfloat16* q_base = qkv + static_cast<size_t>(row0 + qt * kBQ) * ld + h * kHeadDim;
   const __nv_bfloat16* kv_base = qkv + static_cast<size_t>(row0) * ld + d + h * kHeadDim;
   // Q and the first K/V tile in one cp.async group
-  load_tile_64x64_async(sQ, q_base, ld, len - qt * kBQ);
-  load_tile_64x64_async(sKb[0], kv_base, ld, len);
-  load_tile_64x64_async(sVb[0], kv_base + d, ld, len);
+  load_tile_64x64_async(sQ, q_base, ld, len_q - qt * kBQ);
+  if constexpr (kPaged) {
+    load_tile_64x64_paged(sKb[0], cache.k_pool, pt, n_head, h, 0, len);
+    load_tile_64x64_paged(sVb[0], cache.v_pool, pt, n_head, h, 0, len);
+  } else {
+    load_tile_64x64_async(sKb[0], kv_base, ld, len);
+    load_tile_64x64_async(sVb[0], kv_base + d, ld, len);
+  }
   asm volatile("cp.async.commit_group;" ::: "memory");
 
   uint32_t qf[4][4];
@@ -137,17 +177,22 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
   }
   float m_run[2] = {-INFINITY, -INFINITY};
   float l_run[2] = {0.f, 0.f};
-  const int qrow_lo = qt * kBQ + warp * 16 + g;  // this thread's rows: qrow_lo, qrow_lo + 8
+  const int qrow_lo = prefix + qt * kBQ + warp * 16 + g;  // this thread's key-space rows: qrow_lo, qrow_lo + 8
 
-  for (int kt = 0; kt <= qt; ++kt) {
+  for (int kt = 0; kt <= kt_last; ++kt) {
     __nv_bfloat16 (*sK)[kLds] = sKb[kt & 1];
     __nv_bfloat16 (*sV)[kLds] = sVb[kt & 1];
     // prefetch the next tile into the other buffer (its last readers finished at the barrier
     // that closed the previous iteration), then wait for the current one
-    if (kt + 1 <= qt) {
-      const __nv_bfloat16* nk = kv_base + static_cast<size_t>((kt + 1) * kBKV) * ld;
-      load_tile_64x64_async(sKb[(kt + 1) & 1], nk, ld, len - (kt + 1) * kBKV);
-      load_tile_64x64_async(sVb[(kt + 1) & 1], nk + d, ld, len - (kt + 1) * kBKV);
+    if (kt + 1 <= kt_last) {
+      if constexpr (kPaged) {
+        load_tile_64x64_paged(sKb[(kt + 1) & 1], cache.k_pool, pt, n_head, h, (kt + 1) * kBKV, len);
+        load_tile_64x64_paged(sVb[(kt + 1) & 1], cache.v_pool, pt, n_head, h, (kt + 1) * kBKV, len);
+      } else {
+        const __nv_bfloat16* nk = kv_base + static_cast<size_t>((kt + 1) * kBKV) * ld;
+        load_tile_64x64_async(sKb[(kt + 1) & 1], nk, ld, len - (kt + 1) * kBKV);
+        load_tile_64x64_async(sVb[(kt + 1) & 1], nk + d, ld, len - (kt + 1) * kBKV);
+      }
       asm volatile("cp.async.commit_group;" ::: "memory");
       asm volatile("cp.async.wait_group 1;" ::: "memory");
     } else {
@@ -161,9 +206,8 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
         ldmatrix_x4(qf[ks], &sQ[warp * 16 + (i & 1) * 8 + r][ks * 16 + (i >> 1) * 8]);
       }
     }
-    if (kt == qt && cache.slots != nullptr) {
+    if (!kPaged && kt == qt && cache.slots != nullptr) {
       // diagonal tile: this CTA fills the KV pages ([page][head][16 tokens][64]) from smem
-      const int32_t* pt = cache.page_table + static_cast<size_t>(cache.slots[b]) * cache.max_pages_per_seq;
       const int valid = min(kBKV, len - kt * kBKV);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -199,7 +243,7 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
     }
 
     // causal + length mask (only the diagonal tile and a ragged last tile need it), row maxima
-    const bool need_mask = (kt == qt) || ((kt + 1) * kBKV > len);
+    const bool need_mask = ((kt + 1) * kBKV - 1 > prefix + qt * kBQ) || ((kt + 1) * kBKV > len);
     float mx[2] = {-INFINITY, -INFINITY};
 #pragma unroll
     for (int n = 0; n < 8; ++n) {
@@ -274,7 +318,7 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __rest
     const int row = qrow_lo + r2 * 8;
     if (row < len) {
       const float inv = 1.0f / l_run[r2];
-      __nv_bfloat16* orow = out + static_cast<size_t>(row0 + row) * d + h * kHeadDim;
+      __nv_bfloat16* orow = out + static_cast<size_t>(row0 + row - prefix) * d + h * kHeadDim;
 #pragma unroll
       for (int n = 0; n < 8; ++n) {
         const uint32_t pk = pack_bf16x2(o[n][2 * r2] * inv, o[n][2 * r2 + 1] * inv);
@@ -760,8 +804,56 @@ int prefill_attention(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int b
                       const PrefillCache* cache) {
   B200_CHECK_ARG(batch > 0 && max_seq_len > 0 && n_head > 0, "prefill_attention: bad shape");
   dim3 grid((max_seq_len + kBQ - 1) / kBQ, n_head, batch);
-  prefill_attn_kernel<<<grid, 128, 0, stream>>>(qkv, cu_seqlens, n_head, out,
-                                                cache ? *cache : PrefillCache{});
+  prefill_attn_kernel<false><<<grid, 128, 0, stream>>>(qkv, cu_seqlens, n_head, out,
+                                                       cache ? *cache : PrefillCache{}, nullptr);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+int prefill_attention_paged(const PagedPrefillArgs& a, cudaStream_t stream) {
+  B200_CHECK_ARG(a.batch > 0 && a.max_suffix_len > 0 && a.n_head > 0, "prefill_attention_paged: bad shape");
+  PrefillCache pc;
+  pc.slots = a.slots;
+  pc.page_table = a.page_table;
+  pc.max_pages_per_seq = a.max_pages_per_seq;
+  pc.k_pool = const_cast<__nv_bfloat16*>(a.k_pool);
+  pc.v_pool = const_cast<__nv_bfloat16*>(a.v_pool);
+  dim3 grid((a.max_suffix_len + kBQ - 1) / kBQ, a.n_head, a.batch);
+  prefill_attn_kernel<true><<<grid, 128, 0, stream>>>(a.qkv, a.cu_seqlens, a.n_head, a.out, pc, a.prefix_len);
+  B200_CUDA_OK(cudaGetLastError());
+  return kOk;
+}
+
+namespace {
+// One thread per 16-byte chunk of a row's K and V (2 * d / 8 chunks per row).
+__global__ void kv_scatter_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ row_pos,
+                                  const int32_t* __restrict__ row_slot, int n_tok, int n_head,
+                                  const int32_t* __restrict__ page_table, int max_pages_per_seq,
+                                  __nv_bfloat16* __restrict__ k_pool, __nv_bfloat16* __restrict__ v_pool) {
+  const int d = n_head * kHeadDim;
+  const int chunks_per_row = 2 * d / 8;
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= static_cast<long long>(n_tok) * chunks_per_row) return;
+  const int t = static_cast<int>(idx / chunks_per_row);
+  const int c = static_cast<int>(idx % chunks_per_row);
+  const int which = c / (d / 8);          // 0 = K, 1 = V
+  const int col = (c % (d / 8)) * 8;      // feature within d
+  const int h = col / kHeadDim, dim = col % kHeadDim;
+  const int pos = row_pos[t];
+  const int page = page_table[static_cast<size_t>(row_slot[t]) * max_pages_per_seq + pos / kPageTokens];
+  const size_t dst = ((static_cast<size_t>(page) * n_head + h) * kPageTokens + pos % kPageTokens) * kHeadDim + dim;
+  const uint4 v = *reinterpret_cast<const uint4*>(qkv + static_cast<size_t>(t) * 3 * d + (1 + which) * d + col);
+  *reinterpret_cast<uint4*>((which ? v_pool : k_pool) + dst) = v;
+}
+}  // namespace
+
+int kv_scatter(const __nv_bfloat16* qkv, const int32_t* row_pos, const int32_t* row_slot, int n_tok, int n_head,
+               const int32_t* page_table, int max_pages_per_seq, __nv_bfloat16* k_pool, __nv_bfloat16* v_pool,
+               cudaStream_t stream) {
+  B200_CHECK_ARG(n_tok > 0 && n_head > 0, "kv_scatter: bad shape");
+  const long long n = static_cast<long long>(n_tok) * (2 * n_head * kHeadDim / 8);
+  kv_scatter_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(
+      qkv, row_pos, row_slot, n_tok, n_head, page_table, max_pages_per_seq, k_pool, v_pool);
   B200_CUDA_OK(cudaGetLastError());
   return kOk;
 }
@@ -836,7 +928,6 @@ int decode_attention(const DecodeAttnArgs& a, cudaStream_t stream) {
                  "decode_attention: split-KV needs a scratch buffer");
   dim3 grid(a.batch * a.n_head, a.n_splits);
   DecodeAttnArgs args = a;
-  if (const char* env = std::getenv("B200LLM_ATTN_CLUSTER")) args.cluster_combine = std::atoi(env);  // tests
   if (args.n_splits < 2 || args.n_splits > 8) args.cluster_combine = 0;
   if (args.cluster_combine != 0) {
     cudaLaunchConfig_t cfg = {};

@@ -28,6 +28,30 @@ int prefill_attention(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int b
                       int max_seq_len, int n_head, __nv_bfloat16* out, cudaStream_t stream,
                       const PrefillCache* cache = nullptr);
 
+// Shared-prefix reuse: prefill over prompt SUFFIXES. Sequence b already has prefix_len[b] tokens in
+// its KV pages; rows [cu_seqlens[b], cu_seqlens[b+1]) of qkv are its remaining tokens (positions
+// prefix_len[b] + 0, 1, ...). kv_scatter writes their K/V to the pages, then the attention kernel
+// reads every key -- cached or just written -- from the pages (modeling_gpt2.py:194-196: the past
+// is concatenated in front of the new keys; here it is already in place).
+int kv_scatter(const __nv_bfloat16* qkv, const int32_t* row_pos, const int32_t* row_slot, int n_tok,
+               int n_head, const int32_t* page_table, int max_pages_per_seq, __nv_bfloat16* k_pool,
+               __nv_bfloat16* v_pool, cudaStream_t stream);
+struct PagedPrefillArgs {
+  const __nv_bfloat16* qkv = nullptr;     // [n_rows, 3*d]; only the q third is read
+  const int32_t* cu_seqlens = nullptr;    // [batch+1] prefix sums of SUFFIX lengths
+  const int32_t* prefix_len = nullptr;    // [batch]
+  const int32_t* slots = nullptr;         // [batch]
+  int batch = 0;
+  int max_suffix_len = 0;
+  int n_head = 0;
+  const int32_t* page_table = nullptr;
+  int max_pages_per_seq = 0;
+  const __nv_bfloat16* k_pool = nullptr;
+  const __nv_bfloat16* v_pool = nullptr;
+  __nv_bfloat16* out = nullptr;           // [n_rows, d]
+};
+int prefill_attention_paged(const PagedPrefillArgs& a, cudaStream_t stream);
+
 struct DecodeAttnArgs {
   const __nv_bfloat16* qkv;      // [batch, 3*d] current token (bias already added), or null when
                                  // the projection arrives as split-K partial planes:

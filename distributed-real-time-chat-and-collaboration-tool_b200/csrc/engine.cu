@@ -23,6 +23,7 @@
 #include <map>
 #include <memory>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/b200llm.h"
@@ -46,10 +47,12 @@ namespace {
 constexpr size_t kAlign = 256;
 inline size_t align_up(size_t v, size_t a = kAlign) { return (v + a - 1) / a * a; }
 
+// `cu` counts the rows that are actually prefilled; with shared-prefix reuse sequence b has
+// prefix[b] more tokens in front of them that are already in its KV pages.
 __global__ void prefill_meta_kernel(const int32_t* __restrict__ cu, const int32_t* __restrict__ slots,
-                                    int batch, int32_t* __restrict__ row_pos,
-                                    int32_t* __restrict__ row_slot, int32_t* __restrict__ last_rows,
-                                    int32_t* __restrict__ seq_len) {
+                                    const int32_t* __restrict__ prefix, int batch,
+                                    int32_t* __restrict__ row_pos, int32_t* __restrict__ row_slot,
+                                    int32_t* __restrict__ last_rows, int32_t* __restrict__ seq_len) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int n_tok = cu[batch];
   if (t < n_tok) {
@@ -58,14 +61,54 @@ __global__ void prefill_meta_kernel(const int32_t* __restrict__ cu, const int32_
       const int mid = (lo + hi) >> 1;
       if (cu[mid] <= t) lo = mid; else hi = mid;
     }
-    row_pos[t] = t - cu[lo];
+    row_pos[t] = t - cu[lo] + (prefix ? prefix[lo] : 0);
     row_slot[t] = slots[lo];
   }
   if (t < batch) {
     last_rows[t] = cu[t + 1] - 1;
-    seq_len[slots[t]] = cu[t + 1] - cu[t];
+    seq_len[slots[t]] = cu[t + 1] - cu[t] + (prefix ? prefix[t] : 0);
   }
 }
+
+__global__ void cancel_slot_kernel(int32_t* finished, int slot) { finished[slot] = 1; }
+
+// Copies the generated-token rows of the selected slots into a packed staging buffer
+// [batch, stride] (one D2H copy afterwards instead of one per slot).
+__global__ void gather_tokens_kernel(const int32_t* __restrict__ slots, int batch,
+                                     const int32_t* __restrict__ finished, int only_finished,
+                                     const int32_t* __restrict__ out_tokens, int stride,
+                                     int32_t* __restrict__ packed) {
+  const int b = blockIdx.x;
+  if (b >= batch) return;
+  const int s = slots[b];
+  if (only_finished && !finished[s]) return;
+  for (int t = threadIdx.x; t < stride; t += blockDim.x) {
+    packed[static_cast<size_t>(b) * stride + t] = out_tokens[static_cast<size_t>(s) * stride + t];
+  }
+}
+
+// Shared-prefix cache key: the physical page holding the previous 16 tokens (-1 for the first
+// page of a prompt) plus this page's 16 token ids. By induction the parent page identifies the
+// whole token prefix, so equal keys mean equal KV content; no hash collision can alias prompts.
+struct PrefixKey {
+  int32_t parent;
+  int32_t tok[kPageTokens];
+  bool operator==(const PrefixKey& o) const {
+    return parent == o.parent && std::memcmp(tok, o.tok, sizeof(tok)) == 0;
+  }
+};
+struct PrefixKeyHash {
+  size_t operator()(const PrefixKey& k) const {
+    uint64_t h = 1469598103934665603ull ^ static_cast<uint32_t>(k.parent);
+    for (int i = 0; i < kPageTokens; ++i) h = (h ^ static_cast<uint32_t>(k.tok[i])) * 1099511628211ull;
+    return static_cast<size_t>(h ^ (h >> 29));
+  }
+};
+struct PrefixEntry {
+  int32_t page;
+  int32_t children = 0;   // cached pages whose key names this page as parent
+  uint64_t last_use = 0;
+};
 
 struct SlotInit {
   int32_t slot;
@@ -144,6 +187,18 @@ struct b200llm_engine {
   std::vector<int32_t> slot_len_host;  // host mirror of seq_len upper bound
   std::vector<int32_t> page_table_host;  // host mirror [max_seqs][max_pages_per_seq]
   std::vector<char> slot_pt_dirty;       // row not yet uploaded (uploaded in bulk at prefill)
+  // shared-prefix reuse (cfg.prefix_cache): pages are reference counted -- one reference per
+  // slot that maps the page plus one while the cache itself holds it
+  std::vector<int32_t> page_ref;
+  std::vector<int32_t> slot_prefix;               // cached leading tokens the next prefill skips
+  std::vector<std::vector<int32_t>> slot_prompt;  // ids given to seq_alloc_with_prefix
+  std::unordered_map<PrefixKey, PrefixEntry, PrefixKeyHash> prefix_map;
+  std::vector<PrefixKey> page_key;                // key of a cached page (valid while page_cached)
+  std::vector<char> page_cached;
+  uint64_t prefix_clock = 0;
+  int64_t prefix_lookup_tokens = 0, prefix_hit_tokens = 0, prefix_cached_pages = 0;
+  int32_t* prefix_dev = nullptr;                  // [max_seqs] prefix length per sequence of a prefill
+  int32_t* tok_stage = nullptr;                   // [max_seqs, max_new] packed rows for read_tokens_batch
 
   // slot state (device)
   int32_t *seq_len = nullptr, *last_tok = nullptr, *finished = nullptr, *n_gen = nullptr;
@@ -200,8 +255,8 @@ struct b200llm_engine {
   int launches_in_capture = 0;
 
   int last_batch = 0;
-  // Profiling aid (env B200LLM_SKIP, bit mask): drop a class of kernels from the decode step to
-  // read its in-graph cost by difference. Results are garbage when set; never set in tests.
+  // Profiling aid (libb200llm_tune.so only, env B200LLM_SKIP, bit mask): drop a class of kernels
+  // from the decode step to read its in-graph cost by difference. Results are garbage when set.
   int skip_mask = 0;
   int sm_count = 148;
   int prefill_pdl = 1;  // B200LLM_PREFILL_PDL=0 disables
@@ -209,6 +264,8 @@ struct b200llm_engine {
   int steps_per_graph = 4;  // decode steps captured per CUDA graph (B200LLM_STEPS_PER_GRAPH overrides)
   int act_via_tma = 0;  // B200LLM_ACT_TMA=1: decode GEMMs fetch activations through TMA (comparison aid)
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
+  int tune_splits[4] = {0, 0, 0, 0};  // tune build: split-K overrides for qkv, o, fc, proj
+  int tune_attn_splits = 0;           // tune build: KV split override
 };
 
 namespace b200llm {
@@ -283,6 +340,7 @@ struct StepPlan {
   int max_len = 0;     // prefill: longest prompt
   float* logits_all = nullptr;
   bool store_logits = true;  // materialise last-position logits (sampling rows / parity reads)
+  bool paged_prefill = false;  // prefill rows are prompt suffixes: attention reads K/V from the pages
 };
 
 enum SkipBits { kSkipLn = 1, kSkipGemm = 2, kSkipAttn = 4, kSkipHead = 8, kSkipSelect = 16, kSkipGelu = 32 };
@@ -398,6 +456,25 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       if (p.attn_splits > 1 && !(a.cluster_combine && p.attn_splits <= 8)) {
         e->launches += 1, e->launches_in_capture += 1;  // separate combine kernel
       }
+    } else if (p.paged_prefill) {
+      // shared-prefix reuse: the suffix rows' K/V go to their pages first, then every query
+      // attends over the pages (cached prefix + the rows just written)
+      B200_PROPAGATE(count(e, kv_scatter(e->qkv, e->row_pos, e->row_slot, rows, e->H, e->page_table,
+                                         e->max_pages_per_seq, kp, vp, e->stream)));
+      PagedPrefillArgs pa;
+      pa.qkv = e->qkv;
+      pa.cu_seqlens = e->cu_dev;
+      pa.prefix_len = e->prefix_dev;
+      pa.slots = e->slots_dev;
+      pa.batch = p.batch;
+      pa.max_suffix_len = p.max_len;
+      pa.n_head = e->H;
+      pa.page_table = e->page_table;
+      pa.max_pages_per_seq = e->max_pages_per_seq;
+      pa.k_pool = kp;
+      pa.v_pool = vp;
+      pa.out = e->attn;
+      B200_PROPAGATE(count(e, prefill_attention_paged(pa, e->stream)));
     } else {
       PrefillCache pc;
       pc.slots = e->slots_dev;
@@ -536,6 +613,134 @@ int mark_pinned_used(b200llm_engine* e) {
   return kOk;
 }
 
+// ---- shared-prefix cache (cfg.prefix_cache) ---------------------------------------------------
+// Drop the least recently used cached page that nothing else references and that no other
+// cached page hangs off (leaves first, so a chain is never cut in the middle).
+bool evict_one_cached_page(b200llm_engine* e) {
+  const PrefixKey* best = nullptr;
+  uint64_t best_use = ~0ull;
+  for (const auto& kv : e->prefix_map) {
+    const PrefixEntry& en = kv.second;
+    if (en.children == 0 && e->page_ref[en.page] == 1 && en.last_use < best_use) {
+      best = &kv.first;
+      best_use = en.last_use;
+    }
+  }
+  if (best == nullptr) return false;
+  const PrefixKey key = *best;
+  const int32_t page = e->prefix_map[key].page;
+  if (key.parent >= 0 && e->page_cached[key.parent]) {
+    auto it = e->prefix_map.find(e->page_key[key.parent]);
+    if (it != e->prefix_map.end()) it->second.children -= 1;
+  }
+  e->prefix_map.erase(key);
+  e->page_cached[page] = 0;
+  e->prefix_cached_pages -= 1;
+  if (--e->page_ref[page] == 0) e->free_pages.push_back(page);
+  return true;
+}
+
+int alloc_slot(b200llm_engine* e, int capacity_tokens, const int32_t* ids, int n_ids, int32_t* out_slot,
+               int32_t* out_cached) {
+  B200_CHECK_ARG(capacity_tokens > 0 && capacity_tokens <= e->cfg.max_seq_len,
+                 "seq_alloc: capacity exceeds max_seq_len");
+  int slot = -1;
+  for (int s = 0; s < e->cfg.max_seqs; ++s) {
+    if (!e->slot_used[s]) {
+      slot = s;
+      break;
+    }
+  }
+  if (slot < 0) return fail(kErrCapacity, "seq_alloc: no free sequence slot");
+  const int need = (capacity_tokens + kPageTokens - 1) / kPageTokens;
+  std::vector<int32_t>& pages = e->slot_pages[slot];
+  pages.clear();
+  // longest cached run of leading full pages; the last prompt token is never served from the
+  // cache (its logits select the first new token)
+  int shared = 0;
+  if (e->cfg.prefix_cache && ids != nullptr) {
+    const int max_shared = (n_ids - 1) / kPageTokens;
+    PrefixKey key;
+    key.parent = -1;
+    for (int i = 0; i < max_shared; ++i) {
+      std::memcpy(key.tok, ids + static_cast<size_t>(i) * kPageTokens, sizeof(key.tok));
+      auto it = e->prefix_map.find(key);
+      if (it == e->prefix_map.end()) break;
+      it->second.last_use = ++e->prefix_clock;
+      pages.push_back(it->second.page);
+      e->page_ref[it->second.page] += 1;  // pinned from here on: eviction below cannot take it
+      key.parent = it->second.page;
+      ++shared;
+    }
+    e->prefix_lookup_tokens += n_ids;
+  }
+  const int fresh = need - shared;
+  while (static_cast<int64_t>(e->free_pages.size()) < fresh) {
+    if (!e->cfg.prefix_cache || !evict_one_cached_page(e)) {
+      for (int32_t p : pages) e->page_ref[p] -= 1;  // cached pages keep the cache's own reference
+      pages.clear();
+      return fail(kErrCapacity, "seq_alloc: KV pool exhausted");
+    }
+  }
+  for (int i = 0; i < fresh; ++i) {
+    const int32_t p = e->free_pages.back();
+    e->free_pages.pop_back();
+    e->page_ref[p] = 1;
+    pages.push_back(p);
+  }
+  // The row goes to the device in bulk with the next prefill that uses the slot (one copy per
+  // run of consecutive slots instead of one per sequence).
+  std::copy(pages.begin(), pages.end(),
+            e->page_table_host.begin() + static_cast<size_t>(slot) * e->max_pages_per_seq);
+  e->slot_pt_dirty[slot] = 1;
+  e->slot_used[slot] = 1;
+  e->slot_capacity[slot] = capacity_tokens;
+  e->slot_len_host[slot] = 0;
+  e->slot_prefix[slot] = shared * kPageTokens;
+  e->prefix_hit_tokens += shared * kPageTokens;
+  if (e->cfg.prefix_cache && ids != nullptr) {
+    e->slot_prompt[slot].assign(ids, ids + n_ids);
+  } else {
+    e->slot_prompt[slot].clear();
+  }
+  *out_slot = slot;
+  if (out_cached) *out_cached = shared * kPageTokens;
+  return kOk;
+}
+
+// After a prefill has been enqueued: the slot's pages that the prompt fills completely join the
+// cache (the stream orders any later prefill that maps them after the one that writes them).
+void register_prompt_pages(b200llm_engine* e, int slot, const int32_t* ids, int n_ids) {
+  const int full = n_ids / kPageTokens;
+  const std::vector<int32_t>& pages = e->slot_pages[slot];
+  PrefixKey key;
+  key.parent = -1;
+  for (int i = 0; i < full && i < static_cast<int>(pages.size()); ++i) {
+    std::memcpy(key.tok, ids + static_cast<size_t>(i) * kPageTokens, sizeof(key.tok));
+    auto it = e->prefix_map.find(key);
+    if (it == e->prefix_map.end()) {
+      const int32_t page = pages[i];
+      if (e->page_cached[page]) break;  // already cached under another chain (cannot happen: keys are exact)
+      PrefixEntry en;
+      en.page = page;
+      en.last_use = ++e->prefix_clock;
+      e->prefix_map.emplace(key, en);
+      e->page_key[page] = key;
+      e->page_cached[page] = 1;
+      e->page_ref[page] += 1;
+      e->prefix_cached_pages += 1;
+      if (key.parent >= 0 && e->page_cached[key.parent]) {
+        auto pit = e->prefix_map.find(e->page_key[key.parent]);
+        if (pit != e->prefix_map.end()) pit->second.children += 1;
+      }
+      key.parent = page;
+    } else {
+      it->second.last_use = ++e->prefix_clock;
+      key.parent = it->second.page;  // same tokens already cached (possibly in another physical page)
+    }
+  }
+}
+
 int ensure_pinned(b200llm_engine* e, size_t count_i32) {
   if (count_i32 <= e->pin_i32_count) return kOk;
   if (e->pin_i32) cudaFreeHost(e->pin_i32);
@@ -566,7 +771,7 @@ const char* b200llm_last_error(void) { return g_last_error.c_str(); }
 int b200llm_abi_version(void) { return B200LLM_ABI_VERSION; }
 
 size_t b200llm_weight_blob_floats(const b200llm_config* c) {
-  if (c == nullptr) return 0;
+  if (c == nullptr || c->struct_size != sizeof(b200llm_config)) return 0;
   const size_t d = c->d_model, V = c->vocab_size, P = c->n_positions, L = c->n_layer;
   const size_t per_layer = 2 * d + d * 3 * d + 3 * d + d * d + d + 2 * d + d * 4 * d + 4 * d + 4 * d * d + d;
   return V * d + P * d + L * per_layer + 2 * d;
@@ -575,6 +780,10 @@ size_t b200llm_weight_blob_floats(const b200llm_config* c) {
 int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, size_t n_floats,
                           b200llm_engine** out_engine) {
   B200_CHECK_ARG(cfg && weights_host && out_engine, "engine_create: null argument");
+  B200_CHECK_ARG(cfg->struct_size == sizeof(b200llm_config),
+                 "engine_create: b200llm_config.struct_size does not match this library's struct (ABI " +
+                     std::to_string(B200LLM_ABI_VERSION) + ", " + std::to_string(sizeof(b200llm_config)) +
+                     " bytes): the binding was written against another b200llm.h");
   B200_CHECK_ARG(cfg->n_head > 0 && cfg->d_model == cfg->n_head * kHeadDim,
                  "engine_create: head_dim must be 64 (d_model == 64 * n_head)");
   B200_CHECK_ARG(cfg->d_model % 128 == 0, "engine_create: d_model must be a multiple of 128");
@@ -583,6 +792,8 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   B200_CHECK_ARG(cfg->max_seqs > 0 && cfg->max_seq_len > 0 && cfg->max_batch_tokens > 0 &&
                      cfg->max_new_tokens > 0,
                  "engine_create: capacities must be positive");
+  B200_CHECK_ARG(cfg->max_seq_len <= cfg->n_positions,
+                 "engine_create: max_seq_len exceeds n_positions (no position embedding beyond it)");
   B200_CHECK_ARG(n_floats == b200llm_weight_blob_floats(cfg),
                  "engine_create: weight blob size does not match the config");
   B200_CUDA_OK(cudaSetDevice(cfg->device));
@@ -591,12 +802,20 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   e->cfg = *cfg;
   cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, e->cfg.device);
   if (e->sm_count <= 0) e->sm_count = 148;
+#ifdef B200_TUNE_KNOBS
+  // Tuning / ablation switches exist only in libb200llm_tune.so (build.py --tune); the product
+  // library reads no environment variable.
   if (const char* skip = std::getenv("B200LLM_SKIP")) e->skip_mask = std::atoi(skip);
   if (const char* pp = std::getenv("B200LLM_PREFILL_PDL")) e->prefill_pdl = std::atoi(pp);
   if (const char* ps = std::getenv("B200LLM_PREFILL_SPLIT")) e->prefill_split = std::atoi(ps);
   if (const char* at = std::getenv("B200LLM_ACT_TMA")) e->act_via_tma = std::atoi(at);
   if (const char* sg = std::getenv("B200LLM_STEPS_PER_GRAPH")) e->steps_per_graph = std::max(1, std::min(32, std::atoi(sg)));
   if (const char* pair = std::getenv("B200LLM_PAIR")) e->pair_mode = std::atoi(pair);
+  if (const char* env = std::getenv("B200LLM_SPLITS")) {  // "qkv,o,fc,proj" (0 keeps the pick)
+    std::sscanf(env, "%d,%d,%d,%d", &e->tune_splits[0], &e->tune_splits[1], &e->tune_splits[2], &e->tune_splits[3]);
+  }
+  if (const char* env = std::getenv("B200LLM_ATTN_SPLITS")) e->tune_attn_splits = std::max(1, std::min(16, std::atoi(env)));
+#endif
   e->d = cfg->d_model;
   e->H = cfg->n_head;
   e->L = cfg->n_layer;
@@ -698,6 +917,11 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   e->slot_len_host.assign(cfg->max_seqs, 0);
   e->page_table_host.assign(static_cast<size_t>(cfg->max_seqs) * e->max_pages_per_seq, 0);
   e->slot_pt_dirty.assign(cfg->max_seqs, 0);
+  e->page_ref.assign(e->n_pages, 0);
+  e->page_cached.assign(e->n_pages, 0);
+  e->page_key.resize(e->n_pages);
+  e->slot_prefix.assign(cfg->max_seqs, 0);
+  e->slot_prompt.resize(cfg->max_seqs);
 
   // ---- slot state -------------------------------------------------------------------------
   const size_t S = cfg->max_seqs;
@@ -763,6 +987,8 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   E_TRY(dev_alloc_t(e.get(), &e->active_dev, static_cast<size_t>(dec_rows)));
   E_TRY(dev_alloc_t(e.get(), &e->status_dev, 2 * S));
   E_TRY(dev_alloc_t(e.get(), &e->init_dev, S));
+  E_TRY(dev_alloc_t(e.get(), &e->prefix_dev, S));
+  E_TRY(dev_alloc_t(e.get(), &e->tok_stage, S * cfg->max_new_tokens));
   E_CUDA(cudaMallocHost(reinterpret_cast<void**>(&e->pin_init), S * sizeof(SlotInit)));
   E_CUDA(cudaMallocHost(reinterpret_cast<void**>(&e->pin_pt), S * e->max_pages_per_seq * sizeof(int32_t)));
   E_CUDA(cudaMallocHost(reinterpret_cast<void**>(&e->pin_tok), S * cfg->max_new_tokens * sizeof(int32_t)));
@@ -796,6 +1022,7 @@ int b200llm_engine_destroy(b200llm_engine* e) {
 
 int b200llm_engine_set_stream(b200llm_engine* e, void* stream) {
   B200_CHECK_ARG(e != nullptr, "set_stream: null engine");
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
   B200_CUDA_OK(cudaStreamSynchronize(e->stream));
   e->stream = stream ? reinterpret_cast<cudaStream_t>(stream) : e->own_stream;
   // graphs were captured on the previous stream's topology; they replay on any stream
@@ -804,46 +1031,46 @@ int b200llm_engine_set_stream(b200llm_engine* e, void* stream) {
 
 int b200llm_seq_alloc(b200llm_engine* e, int32_t capacity_tokens, int32_t* out_slot) {
   B200_CHECK_ARG(e && out_slot, "seq_alloc: null argument");
-  B200_CHECK_ARG(capacity_tokens > 0 && capacity_tokens <= e->cfg.max_seq_len,
-                 "seq_alloc: capacity exceeds max_seq_len");
-  const int need = (capacity_tokens + kPageTokens - 1) / kPageTokens;
-  if (static_cast<int64_t>(e->free_pages.size()) < need) {
-    return fail(kErrCapacity, "seq_alloc: KV pool exhausted");
-  }
-  int slot = -1;
-  for (int s = 0; s < e->cfg.max_seqs; ++s) {
-    if (!e->slot_used[s]) {
-      slot = s;
-      break;
-    }
-  }
-  if (slot < 0) return fail(kErrCapacity, "seq_alloc: no free sequence slot");
-  std::vector<int32_t>& pages = e->slot_pages[slot];
-  pages.clear();
-  for (int i = 0; i < need; ++i) {
-    pages.push_back(e->free_pages.back());
-    e->free_pages.pop_back();
-  }
-  // The row goes to the device in bulk with the next prefill that uses the slot (one copy per
-  // run of consecutive slots instead of one per sequence).
-  std::copy(pages.begin(), pages.end(),
-            e->page_table_host.begin() + static_cast<size_t>(slot) * e->max_pages_per_seq);
-  e->slot_pt_dirty[slot] = 1;
-  e->slot_used[slot] = 1;
-  e->slot_capacity[slot] = capacity_tokens;
-  e->slot_len_host[slot] = 0;
-  *out_slot = slot;
+  return alloc_slot(e, capacity_tokens, nullptr, 0, out_slot, nullptr);
+}
+
+int b200llm_seq_alloc_with_prefix(b200llm_engine* e, const int32_t* ids_host, int32_t n_ids,
+                                  int32_t capacity_tokens, int32_t* out_slot, int32_t* out_cached) {
+  B200_CHECK_ARG(e && ids_host && out_slot, "seq_alloc_with_prefix: null argument");
+  B200_CHECK_ARG(n_ids > 0 && n_ids <= capacity_tokens, "seq_alloc_with_prefix: prompt exceeds the capacity");
+  return alloc_slot(e, capacity_tokens, ids_host, n_ids, out_slot, out_cached);
+}
+
+int b200llm_prefix_cache_stats(b200llm_engine* e, int64_t* lookups, int64_t* hits, int64_t* pages) {
+  B200_CHECK_ARG(e != nullptr, "prefix_cache_stats: null engine");
+  if (lookups) *lookups = e->prefix_lookup_tokens;
+  if (hits) *hits = e->prefix_hit_tokens;
+  if (pages) *pages = e->prefix_cached_pages;
   return kOk;
 }
 
 int b200llm_seq_free(b200llm_engine* e, int32_t slot) {
   B200_CHECK_ARG(e != nullptr, "seq_free: null engine");
   B200_CHECK_ARG(slot >= 0 && slot < e->cfg.max_seqs && e->slot_used[slot], "seq_free: bad slot");
-  for (int32_t p : e->slot_pages[slot]) e->free_pages.push_back(p);
+  for (int32_t p : e->slot_pages[slot]) {
+    if (--e->page_ref[p] == 0) e->free_pages.push_back(p);
+  }
   e->slot_pages[slot].clear();
+  e->slot_prompt[slot].clear();
+  e->slot_prefix[slot] = 0;
   e->slot_used[slot] = 0;
   e->slot_capacity[slot] = 0;
   e->slot_len_host[slot] = 0;
+  return kOk;
+}
+
+int b200llm_seq_cancel(b200llm_engine* e, int32_t slot) {
+  B200_CHECK_ARG(e != nullptr, "seq_cancel: null engine");
+  B200_CHECK_ARG(slot >= 0 && slot < e->cfg.max_seqs && e->slot_used[slot], "seq_cancel: bad slot");
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
+  cancel_slot_kernel<<<1, 1, 0, e->stream>>>(e->finished, slot);
+  B200_CUDA_OK(cudaGetLastError());
+  e->launches += 1;
   return kOk;
 }
 
@@ -861,7 +1088,10 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "prefill: bad batch");
   B200_CHECK_ARG(batch <= e->logits_rows, "prefill: batch exceeds logits workspace");
   B200_CHECK_ARG(cu[0] == 0, "prefill: cu_seqlens must start at 0");
-  const int n_tok = cu[batch];
+  // Rows that are computed: the whole prompt, or -- for a slot whose leading pages came from the
+  // prefix cache -- only the tokens behind them. `cu` always describes the full prompts.
+  std::vector<int32_t> prefix(batch, 0), cu_rows(batch + 1, 0);
+  bool any_prefix = false;
   int max_len = 0;
   for (int b = 0; b < batch; ++b) {
     const int len = cu[b + 1] - cu[b];
@@ -870,24 +1100,40 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
     const int s = slots[b];
     B200_CHECK_ARG(s >= 0 && s < e->cfg.max_seqs && e->slot_used[s], "prefill: slot not allocated");
     B200_CHECK_ARG(len <= e->slot_capacity[s], "prefill: prompt exceeds the slot's KV capacity");
-    max_len = std::max(max_len, len);
+    prefix[b] = e->slot_prefix[s];
+    if (prefix[b] > 0) {
+      B200_CHECK_ARG(!ids_on_device, "prefill: a slot with a cached prefix needs its ids in host memory");
+      B200_CHECK_ARG(static_cast<int>(e->slot_prompt[s].size()) == len &&
+                         std::memcmp(e->slot_prompt[s].data(), ids + cu[b], sizeof(int32_t) * len) == 0,
+                     "prefill: ids differ from the prompt given to seq_alloc_with_prefix");
+      B200_CHECK_ARG(logits_all_dev == nullptr, "prefill: all-position logits need an uncached prompt");
+      any_prefix = true;
+    }
+    cu_rows[b + 1] = cu_rows[b] + len - prefix[b];
+    max_len = std::max(max_len, len - prefix[b]);
   }
+  const int n_tok = cu_rows[batch];
   if (n_tok > e->cfg.max_batch_tokens) {
     return fail(kErrCapacity, "prefill: packed tokens exceed max_batch_tokens");
   }
   B200_CUDA_OK(cudaSetDevice(e->cfg.device));
   cudaStream_t st = e->stream;
 
-  // staging: [cu (batch+1) | slots (batch) | ids (n_tok, host case)]
+  // staging: [cu (batch+1) | slots (batch) | prefix (batch) | ids (n_tok, host case)]
   // pinned buffers are reused call to call: the previous call's copies must have drained
   B200_PROPAGATE(wait_pinned_free(e));
-  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(2 * batch + 1 + n_tok)));
+  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(3 * batch + 1 + n_tok)));
   int32_t* pin = e->pin_i32;
-  std::memcpy(pin, cu, (batch + 1) * sizeof(int32_t));
+  std::memcpy(pin, cu_rows.data(), (batch + 1) * sizeof(int32_t));
   std::memcpy(pin + batch + 1, slots, batch * sizeof(int32_t));
+  std::memcpy(pin + 2 * batch + 1, prefix.data(), batch * sizeof(int32_t));
   B200_CUDA_OK(cudaMemcpyAsync(e->cu_dev, pin, (batch + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   B200_CUDA_OK(cudaMemcpyAsync(e->slots_dev, pin + batch + 1, batch * sizeof(int32_t),
                                cudaMemcpyHostToDevice, st));
+  if (any_prefix) {
+    B200_CUDA_OK(cudaMemcpyAsync(e->prefix_dev, pin + 2 * batch + 1, batch * sizeof(int32_t),
+                                 cudaMemcpyHostToDevice, st));
+  }
   // page-table rows of freshly allocated slots: stage in pinned memory, one copy per run of
   // consecutive slots
   {
@@ -913,12 +1159,16 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   }
   const int32_t* ids_dev = ids;
   if (!ids_on_device) {
-    for (int i = 0; i < n_tok; ++i) {
+    const int n_all = cu[batch];
+    for (int i = 0; i < n_all; ++i) {
       if (ids[i] < 0 || ids[i] >= e->V) return fail(kErrInvalidArg, "prefill: token id out of range");
     }
-    std::memcpy(pin + 2 * batch + 1, ids, n_tok * sizeof(int32_t));
-    B200_CUDA_OK(cudaMemcpyAsync(e->ids_dev, pin + 2 * batch + 1, n_tok * sizeof(int32_t),
-                                 cudaMemcpyHostToDevice, st));
+    int32_t* dst = pin + 3 * batch + 1;
+    for (int b = 0; b < batch; ++b) {  // only the rows that are computed travel
+      const int n = cu[b + 1] - cu[b] - prefix[b];
+      std::memcpy(dst + cu_rows[b], ids + cu[b] + prefix[b], n * sizeof(int32_t));
+    }
+    B200_CUDA_OK(cudaMemcpyAsync(e->ids_dev, dst, n_tok * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     ids_dev = e->ids_dev;
   }
   for (int b = 0; b < batch; ++b) {
@@ -948,7 +1198,8 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   B200_CUDA_OK(cudaGetLastError());
   const int meta_threads = std::max(n_tok, batch);
   prefill_meta_kernel<<<(meta_threads + 255) / 256, 256, 0, st>>>(
-      e->cu_dev, e->slots_dev, batch, e->row_pos, e->row_slot, e->last_rows, e->seq_len);
+      e->cu_dev, e->slots_dev, any_prefix ? e->prefix_dev : nullptr, batch, e->row_pos, e->row_slot,
+      e->last_rows, e->seq_len);
   B200_CUDA_OK(cudaGetLastError());
   e->launches += 2;
 
@@ -961,6 +1212,7 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   p.max_len = max_len;
   p.logits_all = logits_all_dev;
   p.store_logits = true;
+  p.paged_prefill = any_prefix;
   // Programmatic launch for the kernels that wait on their grid dependency themselves (GEMMs,
   // LayerNorm, select); prefill attention is a plain launch and so still waits for the whole QKV
   // GEMM. A one-request prompt is ~90 tiny kernels: the launch gaps are most of its time.
@@ -985,6 +1237,13 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
     p.split_p = pick(4 * e->d / 64);
   }
   B200_PROPAGATE(run_stack(e, p));
+  // the cached prefixes are consumed; full prompt pages join the cache
+  for (int b = 0; b < batch; ++b) {
+    e->slot_prefix[slots[b]] = 0;
+    if (e->cfg.prefix_cache && !ids_on_device) {
+      register_prompt_pages(e, slots[b], ids + cu[b], cu[b + 1] - cu[b]);
+    }
+  }
   e->last_batch = batch;
   return kOk;
 }
@@ -1027,8 +1286,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   p.pdl = e->cfg.use_pdl ? 1 : 0;
   p.store_logits = need_logits;
   p.live_rows = batch;
-  int sms = 148;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.device);
+  const int sms = e->sm_count;
   // auto: pick_split's rule, never more than 12 planes
   const int cap = e->cfg.decode_split_k == 0 ? 12 : std::min(e->cfg.decode_split_k, 32);
   if (bucket <= 256 && cap > 1 && e->cfg.decode_reduce == 2) {
@@ -1042,21 +1300,17 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     p.split_qkv = pick_split(3 * e->d, e->d, sms, cap);
     p.split_fc = pick_split(4 * e->d, e->d, sms, cap);
   }
-  if (const char* env = std::getenv("B200LLM_SPLITS")) {  // tuning aid: "qkv,o,fc,proj" (0 keeps the pick)
-    int v[4] = {0, 0, 0, 0};
-    std::sscanf(env, "%d,%d,%d,%d", &v[0], &v[1], &v[2], &v[3]);
-    if (v[0] > 0) p.split_qkv = v[0];
-    if (v[1] > 0) p.split_o = v[1];
-    if (v[2] > 0) p.split_fc = v[2];
-    if (v[3] > 0) p.split_p = v[3];
-  }
+  if (e->tune_splits[0] > 0) p.split_qkv = e->tune_splits[0];
+  if (e->tune_splits[1] > 0) p.split_o = e->tune_splits[1];
+  if (e->tune_splits[2] > 0) p.split_fc = e->tune_splits[2];
+  if (e->tune_splits[3] > 0) p.split_p = e->tune_splits[3];
   // split-KV when (rows x heads) alone cannot fill the machine and contexts are long
   {
     const int ctas = bucket * e->H;
     int splits = 1;
     while (splits < 16 && ctas * splits < 4 * sms && max_ctx / (splits * 2) >= 64) splits *= 2;
     p.attn_splits = splits;
-    if (const char* env = std::getenv("B200LLM_ATTN_SPLITS")) p.attn_splits = std::max(1, std::min(16, std::atoi(env)));
+    if (e->tune_attn_splits > 0) p.attn_splits = e->tune_attn_splits;
   }
 
   if (!e->cfg.use_cuda_graphs) {
@@ -1127,6 +1381,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
 
 int b200llm_sync(b200llm_engine* e) {
   B200_CHECK_ARG(e != nullptr, "sync: null engine");
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
   B200_CUDA_OK(cudaStreamSynchronize(e->stream));
   return kOk;
 }
@@ -1135,6 +1390,7 @@ int b200llm_read_tokens(b200llm_engine* e, int32_t slot, int32_t* out, int32_t m
                         int32_t* out_count, int32_t* out_finished) {
   B200_CHECK_ARG(e && out && out_count, "read_tokens: null argument");
   B200_CHECK_ARG(slot >= 0 && slot < e->cfg.max_seqs, "read_tokens: bad slot");
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
   int32_t st2[2] = {0, 0};
   B200_CUDA_OK(cudaMemcpyAsync(&st2[0], e->n_gen + slot, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
   B200_CUDA_OK(cudaMemcpyAsync(&st2[1], e->finished + slot, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
@@ -1154,6 +1410,7 @@ int b200llm_read_status(b200llm_engine* e, const int32_t* slots, int32_t batch, 
                         int32_t* out_finished) {
   B200_CHECK_ARG(e && slots && out_counts && out_finished, "read_status: null argument");
   B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "read_status: bad batch");
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
   cudaStream_t st = e->stream;
   B200_CUDA_OK(cudaStreamSynchronize(st));
   e->pin_busy = false;
@@ -1171,9 +1428,52 @@ int b200llm_read_status(b200llm_engine* e, const int32_t* slots, int32_t batch, 
   return kOk;
 }
 
+int b200llm_read_tokens_batch(b200llm_engine* e, const int32_t* slots, int32_t batch, int32_t only_finished,
+                              int32_t* out_tokens, int32_t out_stride, int32_t* out_counts,
+                              int32_t* out_finished) {
+  B200_CHECK_ARG(e && slots && out_tokens && out_counts && out_finished, "read_tokens_batch: null argument");
+  B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "read_tokens_batch: bad batch");
+  B200_CHECK_ARG(out_stride > 0, "read_tokens_batch: bad stride");
+  for (int b = 0; b < batch; ++b) {
+    B200_CHECK_ARG(slots[b] >= 0 && slots[b] < e->cfg.max_seqs, "read_tokens_batch: bad slot");
+  }
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = e->stream;
+  const int mn = e->cfg.max_new_tokens;
+  // everything is enqueued behind the decode steps already on the stream; ONE wait at the end
+  B200_PROPAGATE(wait_pinned_free(e));
+  B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(3 * batch)));
+  std::memcpy(e->pin_i32, slots, batch * sizeof(int32_t));
+  B200_CUDA_OK(cudaMemcpyAsync(e->last_rows, e->pin_i32, batch * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  gather_status_kernel<<<(batch + 127) / 128, 128, 0, st>>>(e->last_rows, batch, e->n_gen, e->finished,
+                                                            e->status_dev);
+  B200_CUDA_OK(cudaGetLastError());
+  gather_tokens_kernel<<<batch, 64, 0, st>>>(e->last_rows, batch, e->finished, only_finished ? 1 : 0,
+                                             e->out_tokens, mn, e->tok_stage);
+  B200_CUDA_OK(cudaGetLastError());
+  e->launches += 2;
+  B200_CUDA_OK(cudaMemcpyAsync(e->pin_i32 + batch, e->status_dev, 2 * batch * sizeof(int32_t),
+                               cudaMemcpyDeviceToHost, st));
+  B200_CUDA_OK(cudaMemcpyAsync(e->pin_tok, e->tok_stage, static_cast<size_t>(batch) * mn * sizeof(int32_t),
+                               cudaMemcpyDeviceToHost, st));
+  B200_CUDA_OK(cudaStreamSynchronize(st));
+  e->pin_busy = false;
+  for (int b = 0; b < batch; ++b) {
+    const int n = e->pin_i32[batch + b], fin = e->pin_i32[2 * batch + b];
+    out_counts[b] = n;
+    out_finished[b] = fin;
+    if (only_finished && !fin) continue;
+    const int take = std::min(std::min(n, out_stride), mn);
+    std::memcpy(out_tokens + static_cast<size_t>(b) * out_stride, e->pin_tok + static_cast<size_t>(b) * mn,
+                take * sizeof(int32_t));
+  }
+  return kOk;
+}
+
 int b200llm_read_last_logits(b200llm_engine* e, int32_t batch, float* out) {
   B200_CHECK_ARG(e && out, "read_last_logits: null argument");
   B200_CHECK_ARG(batch > 0 && batch <= e->logits_rows, "read_last_logits: bad batch");
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
   B200_CUDA_OK(cudaMemcpyAsync(out, e->logits, static_cast<size_t>(batch) * e->V * sizeof(float),
                                cudaMemcpyDeviceToHost, e->stream));
   B200_CUDA_OK(cudaStreamSynchronize(e->stream));
@@ -1185,6 +1485,7 @@ int b200llm_generate(b200llm_engine* e, const int32_t* ids_host, const int32_t* 
                      int32_t out_stride, int32_t* out_counts) {
   B200_CHECK_ARG(e && ids_host && cu && out_tokens && out_counts, "generate: null argument");
   B200_CHECK_ARG(batch > 0 && batch <= e->cfg.max_seqs, "generate: bad batch");
+  B200_CUDA_OK(cudaSetDevice(e->cfg.device));
   std::vector<int32_t> slots(batch, -1);
   int max_new = 1;
   auto release = [&](int rc) {
@@ -1199,7 +1500,7 @@ int b200llm_generate(b200llm_engine* e, const int32_t* ids_host, const int32_t* 
     const int len = cu[b + 1] - cu[b];
     int cap = std::min(len + mx, e->cfg.max_seq_len);
     if (len > cap) return release(fail(kErrCapacity, "generate: prompt exceeds max_seq_len"));
-    int rc = b200llm_seq_alloc(e, cap, &slots[b]);
+    int rc = alloc_slot(e, cap, ids_host + cu[b], len, &slots[b], nullptr);
     if (rc != kOk) return release(rc);
     max_new = std::max(max_new, mx);
   }
@@ -1358,6 +1659,8 @@ int b200llm_op_decode_attention(const void* qkv, const int32_t* seq_len, const i
                                 void* stream) {
   B200_CHECK_ARG(qkv && seq_len && page_table && k_pool && v_pool && out,
                  "op_decode_attention: null argument");
+  B200_CHECK_ARG(n_splits >= -8 && n_splits != 0 && n_splits != -1,
+                 "op_decode_attention: n_splits must be >= 1, or -2..-8 for the in-cluster merge");
   DecodeAttnArgs a = {};
   a.qkv = static_cast<const __nv_bfloat16*>(qkv);
   a.qkv_partials = nullptr;
@@ -1374,7 +1677,8 @@ int b200llm_op_decode_attention(const void* qkv, const int32_t* seq_len, const i
   a.out = static_cast<__nv_bfloat16*>(out);
   a.batch = batch;
   a.n_head = n_head;
-  a.n_splits = n_splits;
+  a.n_splits = n_splits < 0 ? -n_splits : n_splits;
+  a.cluster_combine = n_splits < 0 ? 1 : 0;
   a.scratch = scratch;
   a.pdl = 0;
   return decode_attention(a, reinterpret_cast<cudaStream_t>(stream));
@@ -1398,6 +1702,67 @@ int b200llm_op_decode_attention_noalloc(const void* qkv, const int32_t* seq_len,
   a.n_head = n_head;
   a.n_splits = n_splits;
   return decode_attention_noalloc(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_lm_head_argmax(const void* act, const void* wte, int32_t tokens, int32_t vocab, int32_t k,
+                              int32_t eos_id, float* logits, float* amax_val, int32_t* amax_idx,
+                              float* eos_logit, int32_t ld_amax, void* stream) {
+  B200_CHECK_ARG(act && wte && amax_val && amax_idx && eos_logit, "op_lm_head_argmax: null argument");
+  B200_CHECK_ARG(tokens > 0 && tokens <= 256 && ld_amax >= tokens, "op_lm_head_argmax: 1..256 tokens, ld_amax >= tokens");
+  GemmArgs g = {};
+  g.act = static_cast<const __nv_bfloat16*>(act);
+  g.w = static_cast<const __nv_bfloat16*>(wte);
+  g.bias = nullptr;
+  g.out = logits;
+  g.tokens = tokens;
+  g.features = vocab;
+  g.k = k;
+  g.ld_out = vocab;
+  g.epilogue = kEpiLogitsArgmax;
+  g.split_k = 1;
+  g.act_rows_alloc = tokens;
+  g.force_orientation = 1;
+  g.pdl = 0;
+  g.amax_groups_alloc = gemm_argmax_groups(vocab, tokens);
+  g.amax_val = amax_val;
+  g.amax_idx = amax_idx;
+  g.eos_logit = eos_logit;
+  g.ld_amax = ld_amax;
+  g.eos_id = eos_id;
+  return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int32_t b200llm_lm_head_argmax_groups(int32_t vocab, int32_t tokens) { return gemm_argmax_groups(vocab, tokens); }
+
+int b200llm_op_prefill_attention_paged(const void* qkv, const int32_t* cu_seqlens, const int32_t* prefix_len,
+                                       const int32_t* slots, int32_t batch, int32_t max_suffix_len,
+                                       int32_t n_head, const int32_t* page_table, int32_t max_pages_per_seq,
+                                       const void* k_pool, const void* v_pool, void* out, void* stream) {
+  B200_CHECK_ARG(qkv && cu_seqlens && prefix_len && slots && page_table && k_pool && v_pool && out,
+                 "op_prefill_attention_paged: null argument");
+  PagedPrefillArgs a;
+  a.qkv = static_cast<const __nv_bfloat16*>(qkv);
+  a.cu_seqlens = cu_seqlens;
+  a.prefix_len = prefix_len;
+  a.slots = slots;
+  a.batch = batch;
+  a.max_suffix_len = max_suffix_len;
+  a.n_head = n_head;
+  a.page_table = page_table;
+  a.max_pages_per_seq = max_pages_per_seq;
+  a.k_pool = static_cast<const __nv_bfloat16*>(k_pool);
+  a.v_pool = static_cast<const __nv_bfloat16*>(v_pool);
+  a.out = static_cast<__nv_bfloat16*>(out);
+  return prefill_attention_paged(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_kv_scatter(const void* qkv, const int32_t* row_pos, const int32_t* row_slot, int32_t n_tok,
+                          int32_t n_head, const int32_t* page_table, int32_t max_pages_per_seq, void* k_pool,
+                          void* v_pool, void* stream) {
+  B200_CHECK_ARG(qkv && row_pos && row_slot && page_table && k_pool && v_pool, "op_kv_scatter: null argument");
+  return kv_scatter(static_cast<const __nv_bfloat16*>(qkv), row_pos, row_slot, n_tok, n_head, page_table,
+                    max_pages_per_seq, static_cast<__nv_bfloat16*>(k_pool), static_cast<__nv_bfloat16*>(v_pool),
+                    reinterpret_cast<cudaStream_t>(stream));
 }
 
 size_t b200llm_decode_attention_scratch_floats(int32_t batch, int32_t n_head, int32_t n_splits) {

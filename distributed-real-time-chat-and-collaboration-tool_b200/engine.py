@@ -54,7 +54,7 @@ class Engine:
                  max_seqs: int = 64, max_seq_len: int = 256, max_batch_tokens: int = 8192,
                  max_new_tokens: int = 256, kv_pool_tokens: int = 0, use_cuda_graphs: bool = True,
                  use_pdl: bool = True, decode_split_k: int = 0, keep_logits: bool = False,
-                 decode_reduce: int = 0, pad_token_id: int | None = None):
+                 decode_reduce: int = 0, pad_token_id: int | None = None, prefix_cache: bool = False):
         blob = np.ascontiguousarray(weights_blob, dtype=np.float32).reshape(-1)
         self.shape = shape
         self.cfg = Config(
@@ -65,12 +65,13 @@ class Engine:
             max_seqs=max_seqs, max_seq_len=max_seq_len, max_batch_tokens=max_batch_tokens,
             max_new_tokens=max_new_tokens, kv_pool_tokens=kv_pool_tokens, device=device,
             use_cuda_graphs=int(use_cuda_graphs), use_pdl=int(use_pdl), decode_split_k=decode_split_k,
-            keep_logits=int(keep_logits), decode_reduce=decode_reduce)
+            keep_logits=int(keep_logits), decode_reduce=decode_reduce, prefix_cache=int(prefix_cache))
         expect = lib.b200llm_weight_blob_floats(C.byref(self.cfg))
         if blob.size != expect:
             raise ValueError(f"weight blob has {blob.size} floats, config needs {expect}")
         self._h = C.c_void_p()
         check(lib.b200llm_engine_create(C.byref(self.cfg), blob.ctypes.data, blob.size, C.byref(self._h)))
+        self.last_cached_tokens = 0
 
     # -- lifecycle ------------------------------------------------------------------------
     def close(self) -> None:
@@ -101,10 +102,31 @@ class Engine:
         return int(lib.b200llm_kernel_launches(self._h))
 
     # -- KV-cache manager -------------------------------------------------------------------
-    def seq_alloc(self, capacity_tokens: int) -> int:
+    def seq_alloc(self, capacity_tokens: int, prompt: Sequence[int] | None = None) -> int:
+        """A KV slot of `capacity_tokens`. With `prompt` (and an engine created with
+        prefix_cache=True) the longest cached run of the prompt's leading pages is shared with the
+        slot and the next prefill of it skips those tokens; `last_cached_tokens` says how many."""
         slot = C.c_int32(-1)
-        check(lib.b200llm_seq_alloc(self._h, capacity_tokens, C.byref(slot)))
+        if prompt is None:
+            check(lib.b200llm_seq_alloc(self._h, capacity_tokens, C.byref(slot)))
+            self.last_cached_tokens = 0
+        else:
+            ids = _i32(prompt)
+            cached = C.c_int32(0)
+            check(lib.b200llm_seq_alloc_with_prefix(self._h, ids.ctypes.data, len(ids), capacity_tokens,
+                                                    C.byref(slot), C.byref(cached)))
+            self.last_cached_tokens = cached.value
         return slot.value
+
+    def seq_cancel(self, slot: int) -> None:
+        """Mark the slot finished on the device (its caller gave up); free it after the next
+        status read."""
+        check(lib.b200llm_seq_cancel(self._h, slot))
+
+    def prefix_cache_stats(self) -> dict:
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        check(lib.b200llm_prefix_cache_stats(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"lookup_tokens": a.value, "hit_tokens": b.value, "cached_pages": c.value}
 
     def seq_free(self, slot: int) -> None:
         check(lib.b200llm_seq_free(self._h, slot))
@@ -160,6 +182,20 @@ class Engine:
         fin = np.empty(len(sl), dtype=np.int32)
         check(lib.b200llm_read_status(self._h, sl.ctypes.data, len(sl), counts.ctypes.data, fin.ctypes.data))
         return counts, fin
+
+    def read_tokens_batch(self, slots: Sequence[int], only_finished: bool = True):
+        """(counts, finished, tokens) of several slots with one stream synchronisation; tokens[i]
+        is None for a slot that was not copied (unfinished with only_finished)."""
+        sl = _i32(slots)
+        n = len(sl)
+        stride = self.cfg.max_new_tokens
+        buf = np.empty((n, stride), dtype=np.int32)
+        counts = np.empty(n, dtype=np.int32)
+        fin = np.empty(n, dtype=np.int32)
+        check(lib.b200llm_read_tokens_batch(self._h, sl.ctypes.data, n, int(only_finished), buf.ctypes.data,
+                                            stride, counts.ctypes.data, fin.ctypes.data))
+        toks = [buf[i, : counts[i]].tolist() if (fin[i] or not only_finished) else None for i in range(n)]
+        return counts, fin, toks
 
     def read_last_logits(self, batch: int) -> np.ndarray:
         out = np.empty((batch, self.shape.vocab_size), dtype=np.float32)

@@ -114,8 +114,13 @@ def _participants(messages: Sequence) -> list[str]:
 # --------------------------------------------------------------------------------------------
 # Use cases
 # --------------------------------------------------------------------------------------------
-def generate_response(model, query: str, context_list: Sequence[str], sleep: Callable[[float], None] = time.sleep) -> str:
+_sleep = time.sleep  # the retry back-off's clock (llm_server.py:164, :204); tests replace THIS, not time.sleep
+
+
+def generate_response(model, query: str, context_list: Sequence[str],
+                      sleep: Callable[[float], None] | None = None) -> str:
     """Ask-AI (llm_server.py:147-212): up to three attempts with 1 s / 2 s back-off."""
+    sleep = sleep or _sleep
     try:
         if context_list:
             prompt = PROMPTS["ask_with_context"].format(context="\n".join(context_list[-CONTEXT_WINDOW:]), query=query)

@@ -10,6 +10,7 @@ rather than hanging, which the callers turn into their canned replies.
 """
 from __future__ import annotations
 
+import itertools
 from dataclasses import dataclass, field
 
 from .engine import SamplingParams
@@ -57,16 +58,15 @@ class LocalGenerativeModel:
         self.default_top_k = default_top_k
         self.timeout_s = timeout_s  # below the Raft node's tightest LLM deadline (10 s, raft_node.py:2084)
         self.max_prompt_tokens = max_prompt_tokens
-        self._seed = 0
+        self._seed = itertools.count(1)  # next() is atomic under the GIL: 128 handler threads share it
 
     def _sampling(self, generation_config: dict | None) -> SamplingParams:
         cfg = generation_config or {}
         temperature = float(cfg.get("temperature", self.default_temperature))
         max_new = int(cfg.get("max_output_tokens", self.default_max_new_tokens))
         top_k = int(cfg.get("top_k", self.default_top_k)) if temperature > 0 else 0
-        self._seed += 1
         return SamplingParams(max_new_tokens=max(1, max_new), min_new_tokens=0, temperature=temperature,
-                              top_k=top_k, seed=int(cfg.get("seed", self._seed)))
+                              top_k=top_k, seed=int(cfg.get("seed", next(self._seed))))
 
     def generate_content(self, prompt: str, generation_config: dict | None = None) -> GenerateContentResponse:
         ids = self.tokenizer.encode(prompt)
@@ -79,4 +79,5 @@ class LocalGenerativeModel:
         return GenerateContentResponse(
             candidates=[Candidate(finish_reason=result.finish_reason, content=Content(parts=[Part(text=text)]))],
             usage={"prompt_tokens": result.prompt_tokens, "generated_tokens": len(result.tokens),
-                   "queue_ms": result.queue_ms, "total_ms": result.total_ms})
+                   "queue_ms": result.queue_ms, "total_ms": result.total_ms,
+                   "cached_prompt_tokens": result.cached_prompt_tokens})

@@ -76,7 +76,9 @@ def decode_attention_scratch_floats(batch: int, n_head: int, n_splits: int) -> i
 
 def decode_attention(qkv: torch.Tensor, seq_len: torch.Tensor, page_table: torch.Tensor,
                      k_pool: torch.Tensor, v_pool: torch.Tensor, n_head: int, n_splits: int = 1,
-                     scratch: torch.Tensor | None = None) -> torch.Tensor:
+                     scratch: torch.Tensor | None = None, cluster: bool = False) -> torch.Tensor:
+    """`cluster`: merge the 2..8 KV splits inside the kernel over a thread-block cluster (what the
+    engine does for a few live rows) instead of through scratch + a combine launch."""
     batch = qkv.shape[0]
     d = n_head * 64
     out = torch.zeros(batch, d, dtype=torch.bfloat16, device=qkv.device)
@@ -85,8 +87,48 @@ def decode_attention(qkv: torch.Tensor, seq_len: torch.Tensor, page_table: torch
                               dtype=torch.float32, device=qkv.device)
     check(lib.b200llm_op_decode_attention(_ptr(qkv), _ptr(seq_len), _ptr(page_table),
                                           page_table.shape[1], _ptr(k_pool), _ptr(v_pool), _ptr(out),
-                                          batch, n_head, n_splits, _ptr(scratch), _stream()))
+                                          batch, n_head, -n_splits if cluster else n_splits, _ptr(scratch),
+                                          _stream()))
     return out
+
+
+def kv_scatter(qkv: torch.Tensor, row_pos: torch.Tensor, row_slot: torch.Tensor, page_table: torch.Tensor,
+               k_pool: torch.Tensor, v_pool: torch.Tensor, n_head: int) -> None:
+    check(lib.b200llm_op_kv_scatter(_ptr(qkv), _ptr(row_pos), _ptr(row_slot), qkv.shape[0], n_head,
+                                    _ptr(page_table), page_table.shape[1], _ptr(k_pool), _ptr(v_pool), _stream()))
+
+
+def prefill_attention_paged(qkv: torch.Tensor, cu_seqlens: torch.Tensor, prefix_len: torch.Tensor,
+                            slots: torch.Tensor, max_suffix_len: int, n_head: int, page_table: torch.Tensor,
+                            k_pool: torch.Tensor, v_pool: torch.Tensor) -> torch.Tensor:
+    """Causal attention of prompt suffixes over the paged cache (prefix + suffix keys in the pages)."""
+    out = torch.zeros(qkv.shape[0], n_head * 64, dtype=torch.bfloat16, device=qkv.device)
+    check(lib.b200llm_op_prefill_attention_paged(_ptr(qkv), _ptr(cu_seqlens), _ptr(prefix_len), _ptr(slots),
+                                                 cu_seqlens.numel() - 1, max_suffix_len, n_head,
+                                                 _ptr(page_table), page_table.shape[1], _ptr(k_pool),
+                                                 _ptr(v_pool), _ptr(out), _stream()))
+    return out
+
+
+def lm_head_argmax_groups(vocab: int, tokens: int) -> int:
+    return int(lib.b200llm_lm_head_argmax_groups(vocab, tokens))
+
+
+def lm_head_argmax(act: torch.Tensor, wte: torch.Tensor, eos_id: int, logits: torch.Tensor | None = None,
+                   work: tuple | None = None):
+    """The decode step's LM head with the fused greedy argmax. Returns (amax_val, amax_idx,
+    eos_logit): per-group candidates [groups, tokens] and the EOS logit per token."""
+    tokens, k = act.shape
+    vocab = wte.shape[0]
+    if work is None:
+        g = lm_head_argmax_groups(vocab, tokens)
+        work = (torch.full((g, tokens), float("-inf"), device=act.device),
+                torch.zeros(g, tokens, dtype=torch.int32, device=act.device),
+                torch.zeros(tokens, device=act.device))
+    val, idx, eos = work
+    check(lib.b200llm_op_lm_head_argmax(_ptr(act), _ptr(wte), tokens, vocab, k, eos_id, _ptr(logits), _ptr(val),
+                                        _ptr(idx), _ptr(eos), val.shape[1], _stream()))
+    return val, idx, eos
 
 
 def argmax(logits: torch.Tensor, vocab: int | None = None) -> torch.Tensor:

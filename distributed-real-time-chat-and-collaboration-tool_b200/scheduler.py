@@ -15,6 +15,7 @@ import queue
 import threading
 import time
 from concurrent.futures import Future
+from concurrent.futures import TimeoutError as FutureTimeout
 from dataclasses import dataclass, field
 from typing import Callable, Sequence
 
@@ -28,6 +29,7 @@ class GenerationResult:
     prompt_tokens: int
     queue_ms: float = 0.0
     total_ms: float = 0.0
+    cached_prompt_tokens: int = 0   # leading prompt tokens whose KV came from the prefix cache
 
 
 @dataclass
@@ -39,12 +41,21 @@ class _Request:
     t_start: float = 0.0
     slot: int = -1
     n_done: int = 1  # tokens generated so far (prefill selects the first one), refreshed at every status read
+    cancelled: bool = False    # set from any thread when the caller gave up (timeout)
+    cancel_sent: bool = False  # worker thread: the device has been told
+    cached_tokens: int = 0     # prompt tokens served from the prefix cache
 
 
 class EngineWorker(threading.Thread):
     """One GPU: admits, decodes and retires sequences. `engine` needs the Engine interface:
     cfg.max_seqs/max_seq_len/max_batch_tokens/max_new_tokens, shape.eos_token_id, seq_alloc,
-    seq_free, prefill, decode, read_status, read_tokens."""
+    seq_free, seq_cancel, prefill, decode, read_tokens_batch."""
+
+    # a replica whose last FAIL_LIMIT engine calls raised is left out of the rotation and
+    # re-probed with a single request every REPROBE_S seconds (SURVEY.md section 5: "a dead GPU
+    # replica should be removed from the router, not crash the server")
+    FAIL_LIMIT = 3
+    REPROBE_S = 5.0
 
     def __init__(self, engine, *, decode_burst: int = 8, name: str = "b200llm-worker"):
         super().__init__(name=name, daemon=True)
@@ -58,6 +69,10 @@ class EngineWorker(threading.Thread):
         self._lock = threading.Lock()
         self.completed = 0
         self.generated_tokens = 0
+        self.cancelled = 0
+        self.prefix_hit_tokens = 0
+        self.consecutive_failures = 0
+        self.last_failure_t = 0.0
         self._stopping = False
         # wall time of the worker loop by phase, for the stream benchmark's report
         self.phase_s = {"idle": 0.0, "admit": 0.0, "decode": 0.0, "retire": 0.0}
@@ -67,10 +82,26 @@ class EngineWorker(threading.Thread):
     def submit(self, ids: Sequence[int], sampling: SamplingParams) -> Future:
         fut: Future = Future()
         req = _Request(list(ids), sampling, fut)
+        fut.request = req  # lets the caller cancel (Router.generate on timeout)
         with self._lock:
             self._inflight_tokens += len(req.ids) + sampling.max_new_tokens
         self.inbox.put(req)
         return fut
+
+    @staticmethod
+    def cancel(fut: Future) -> None:
+        """The caller no longer wants the result: a waiting request is dropped at the next
+        admission, an active one is stopped on the device and its slot freed at the next retire."""
+        req = getattr(fut, "request", None)
+        if req is not None:
+            req.cancelled = True
+
+    @property
+    def healthy(self) -> bool:
+        return self.consecutive_failures < self.FAIL_LIMIT
+
+    def due_for_reprobe(self, now: float) -> bool:
+        return not self.healthy and now - self.last_failure_t >= self.REPROBE_S
 
     @property
     def inflight_tokens(self) -> int:
@@ -95,81 +126,129 @@ class EngineWorker(threading.Thread):
             except queue.Empty:
                 return
 
-    def _fail(self, req: _Request, exc: BaseException) -> None:
+    def _release(self, req: _Request) -> None:
         with self._lock:
             self._inflight_tokens -= len(req.ids) + req.sampling.max_new_tokens
+
+    def _fail(self, req: _Request, exc: BaseException) -> None:
+        self._release(req)
         if not req.future.done():
             req.future.set_exception(exc)
 
-    def _admit(self) -> None:
+    def _pages_needed(self, tokens: int) -> int:
+        return (tokens + 15) // 16
+
+    def _admit(self) -> bool:
+        """Prefill as many waiting requests as fit. Returns True when anything was admitted or
+        dropped (progress), False when every waiting request has to wait for a retirement."""
         cfg = self.engine.cfg
         batch: list[_Request] = []
         tokens = 0
         keep: list[_Request] = []
+        progress = False
+        pool_tokens = int(getattr(cfg, "kv_pool_tokens", 0)) or cfg.max_seqs * cfg.max_seq_len
         for req in self.waiting:
             n = len(req.ids)
             max_new = max(1, min(req.sampling.max_new_tokens, cfg.max_new_tokens))
+            if req.cancelled:
+                self.cancelled += 1
+                self._fail(req, TimeoutError("request cancelled before admission"))
+                progress = True
+                continue
             if n == 0 or n >= cfg.max_seq_len or n > cfg.max_batch_tokens:
                 self._fail(req, ValueError(f"prompt of {n} tokens does not fit the engine "
                                            f"(max_seq_len {cfg.max_seq_len}, batch budget {cfg.max_batch_tokens})"))
+                progress = True
+                continue
+            cap = min(n + max_new, cfg.max_seq_len)
+            if self._pages_needed(cap) * 16 > pool_tokens:
+                self._fail(req, ValueError(f"request needs {cap} KV tokens, the whole pool holds {pool_tokens}"))
+                progress = True
                 continue
             if len(self.active) + len(batch) >= cfg.max_seqs or tokens + n > cfg.max_batch_tokens:
                 keep.append(req)
                 continue
             try:
-                req.slot = self.engine.seq_alloc(min(n + max_new, cfg.max_seq_len))
-            except Exception:  # KV pool exhausted: retry after something retires
-                keep.append(req)
+                req.slot = self.engine.seq_alloc(cap, req.ids)
+            except Exception as exc:  # noqa: BLE001  KV pool exhausted: retry after something retires
+                if not self.active and not batch:
+                    # nothing is running that could ever free pages: waiting would spin forever
+                    self._fail(req, exc)
+                    progress = True
+                else:
+                    keep.append(req)
                 continue
+            req.cached_tokens = int(getattr(self.engine, "last_cached_tokens", 0))
             req.t_start = time.perf_counter()
             batch.append(req)
-            tokens += n
+            tokens += n - req.cached_tokens
         self.waiting = keep
         if not batch:
-            return
+            return progress
         try:
             self.engine.prefill([r.ids for r in batch], [r.slot for r in batch], [r.sampling for r in batch])
         except Exception as exc:  # noqa: BLE001
+            self._note_failure()
             for r in batch:
                 try:
                     self.engine.seq_free(r.slot)
                 except Exception:  # noqa: BLE001
                     pass
                 self._fail(r, exc)
-            return
+            return True
+        self.prefix_hit_tokens += sum(r.cached_tokens for r in batch)
         self.active.extend(batch)
+        return True
+
+    def _note_failure(self) -> None:
+        self.consecutive_failures += 1
+        self.last_failure_t = time.perf_counter()
 
     def _retire(self) -> None:
         if not self.active:
             return
-        counts, finished = self.engine.read_status([r.slot for r in self.active])
+        for req in self.active:
+            if req.cancelled and not req.cancel_sent:
+                # enqueued ahead of the status gather below, so this very read already sees it
+                self.engine.seq_cancel(req.slot)
+                req.cancel_sent = True
+        # ONE stream synchronisation for the status of every active slot and the tokens of the
+        # finished ones (b200llm_read_tokens_batch)
+        counts, finished, rows = self.engine.read_tokens_batch([r.slot for r in self.active])
         still: list[_Request] = []
         eos = self.engine.shape.eos_token_id
-        for req, n, fin in zip(self.active, counts, finished):
+        for req, n, fin, tokens in zip(self.active, counts, finished, rows):
             if not fin:
                 req.n_done = int(n)
                 still.append(req)
                 continue
-            tokens, _ = self.engine.read_tokens(req.slot, int(n))
             self.engine.seq_free(req.slot)
+            req.slot = -1
+            if req.cancelled:
+                self.cancelled += 1
+                self._fail(req, TimeoutError("request cancelled"))
+                continue
+            tokens = list(tokens[: int(n)])
             hit_eos = eos in tokens
             if hit_eos:
                 tokens = tokens[: tokens.index(eos)]
             now = time.perf_counter()
-            with self._lock:
-                self._inflight_tokens -= len(req.ids) + req.sampling.max_new_tokens
+            self._release(req)
             self.completed += 1
             self.generated_tokens += len(tokens)
             req.future.set_result(GenerationResult(
                 tokens=tokens, finish_reason=1 if hit_eos else 2, prompt_tokens=len(req.ids),
-                queue_ms=(req.t_start - req.t_submit) * 1e3, total_ms=(now - req.t_submit) * 1e3))
+                queue_ms=(req.t_start - req.t_submit) * 1e3, total_ms=(now - req.t_submit) * 1e3,
+                cached_prompt_tokens=req.cached_tokens))
         self.active = still
+        self.consecutive_failures = 0  # a full admit/decode/retire round trip worked
 
     def run(self) -> None:
         clock = time.perf_counter
+        stalled = False  # waiting requests exist but none can be admitted and nothing is running
         while not self._stopping:
             t0 = clock()
-            self._drain_inbox(block=not self.active and not self.waiting)
+            self._drain_inbox(block=(not self.active and not self.waiting) or stalled)
             t1 = clock()
             self.phase_s["idle"] += t1 - t0
             if self._stopping:
@@ -178,9 +257,11 @@ class EngineWorker(threading.Thread):
                 # admit first: a new request joins the burst of the same iteration (enqueueing the
                 # burst ahead of the admission was measured: the stream is GPU-bound, and each
                 # request then waits one more burst -- 476 vs 515 requests/s)
+                stalled = False
                 if self.waiting:
-                    self._admit()
+                    progress = self._admit()
                     self._retire()  # max_new_tokens == 1 finishes at prefill
+                    stalled = not progress and not self.active
                 t2 = clock()
                 self.phase_s["admit"] += t2 - t1
                 if self.active:
@@ -196,6 +277,16 @@ class EngineWorker(threading.Thread):
                     self.phase_s["retire"] += t4 - t3
                     self.iterations += 1
             except Exception as exc:  # noqa: BLE001  a broken engine fails its requests, not the server
+                self._note_failure()
+                # give the slots (and their KV pages) back before failing the requests: one
+                # non-fatal error must not leak capacity for the rest of the process
+                for req in self.active:
+                    if req.slot >= 0:
+                        try:
+                            self.engine.seq_free(req.slot)
+                        except Exception:  # noqa: BLE001
+                            pass
+                        req.slot = -1
                 for req in self.active + self.waiting:
                     self._fail(req, exc)
                 self.active, self.waiting = [], []
@@ -214,12 +305,27 @@ class Router:
             if not w.is_alive():
                 w.start()
 
+    def _pick(self) -> EngineWorker:
+        now = time.perf_counter()
+        for w in self.workers:  # one probe request at a time for a replica that was taken out
+            if w.due_for_reprobe(now) and w.inflight_tokens == 0:
+                w.last_failure_t = now
+                return w
+        healthy = [w for w in self.workers if w.healthy]
+        # with every replica failing there is nothing better than the least loaded one: its
+        # exception reaches the caller, whose catch-all answers with the canned reply
+        return min(healthy or self.workers, key=lambda w: w.inflight_tokens)
+
     def submit(self, ids: Sequence[int], sampling: SamplingParams) -> Future:
-        worker = min(self.workers, key=lambda w: w.inflight_tokens)
-        return worker.submit(ids, sampling)
+        return self._pick().submit(ids, sampling)
 
     def generate(self, ids: Sequence[int], sampling: SamplingParams, timeout: float | None = None) -> GenerationResult:
-        return self.submit(ids, sampling).result(timeout=timeout)
+        fut = self.submit(ids, sampling)
+        try:
+            return fut.result(timeout=timeout)
+        except FutureTimeout:
+            EngineWorker.cancel(fut)  # do not keep decoding for a caller that has already answered
+            raise
 
     def shutdown(self) -> None:
         for w in self.workers:

@@ -59,7 +59,7 @@ def build_local_model(model: str = "small", gpus: int = 1, *, max_seqs: int = 64
     workers = []
     for dev in range(gpus):
         eng = Engine(shape, blob, device=dev, max_seqs=max_seqs, max_seq_len=min(max_seq_len, shape.n_positions),
-                     max_batch_tokens=8192, max_new_tokens=max_new_tokens)
+                     max_batch_tokens=8192, max_new_tokens=max_new_tokens, prefix_cache=True)
         workers.append(EngineWorker(eng, name=f"b200llm-gpu{dev}"))
     router = Router(workers)
     return LocalGenerativeModel(router, load_tokenizer(vocab_json, merges_txt),

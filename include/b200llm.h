@@ -28,7 +28,10 @@
 extern "C" {
 #endif
 
-#define B200LLM_ABI_VERSION 1
+/* 2: b200llm_config starts with `struct_size`; batched token read, cancel, prefix-cache entry
+ *    points added. A library and a binding that disagree on the struct are refused at
+ *    b200llm_engine_create instead of reading each other's fields at the wrong offsets. */
+#define B200LLM_ABI_VERSION 2
 
 enum b200llm_status {
   B200LLM_OK = 0,
@@ -53,6 +56,8 @@ typedef struct b200llm_engine b200llm_engine;
 /* Model + capacity description. Mirrors transformers GPT2Config (n_layer, n_head, n_embd,
  * vocab_size, n_positions, layer_norm_epsilon, eos_token_id) plus engine capacities. */
 typedef struct b200llm_config {
+  uint32_t struct_size;     /* = sizeof(b200llm_config) of the header the caller was built against;
+                               anything else is rejected with B200LLM_ERR_INVALID_ARG             */
   int32_t n_layer;
   int32_t n_head;
   int32_t d_model;          /* n_embd; head_dim must be 64 (all GPT-2 sizes)               */
@@ -62,7 +67,8 @@ typedef struct b200llm_config {
   int32_t eos_token_id;     /* 50256                                                       */
   int32_t pad_token_id;     /* value finished rows emit ($TF/generation/utils.py:2796-2797) */
   int32_t max_seqs;         /* concurrent sequences (KV slots)                             */
-  int32_t max_seq_len;      /* per-sequence KV capacity in tokens (prompt + generated)     */
+  int32_t max_seq_len;      /* per-sequence KV capacity in tokens (prompt + generated);
+                               must not exceed n_positions (there is no position row beyond it) */
   int32_t max_batch_tokens; /* packed prompt tokens per prefill call                       */
   int32_t max_new_tokens;   /* per-sequence cap on generated tokens kept on device         */
   int64_t kv_pool_tokens;   /* total KV tokens in the paged pool; 0 = max_seqs*max_seq_len */
@@ -76,6 +82,12 @@ typedef struct b200llm_config {
                                reduced by the consumer kernel (default; measured faster);
                                2 = inside the GEMM, over a thread-block cluster through distributed
                                shared memory (fewer kernels, but DSMEM moves ~20 B/clk per SM)    */
+  int32_t prefix_cache;     /* 1 = shared-prefix KV reuse: the full 16-token pages of every prompt
+                               stay in a ref-counted, LRU-evicted cache keyed by their token chain;
+                               b200llm_seq_alloc_with_prefix maps a new prompt's longest cached page
+                               prefix into its slot and prefill then runs over the suffix only.
+                               The reference's prompts that share a head: llm_server.py:273-285
+                               (summaries of a growing channel, raft_node.py:2032-2084), :221-229 */
 } b200llm_config;
 
 /* Number of fp32 values in the weight blob for `cfg` (layout below). */
@@ -105,6 +117,25 @@ int b200llm_engine_set_stream(b200llm_engine* engine, void* stream);
 /* Replaces the cat-and-reallocate cache of $TF/cache_utils.py:119-120. */
 int b200llm_seq_alloc(b200llm_engine* engine, int32_t capacity_tokens, int32_t* out_slot);
 int b200llm_seq_free(b200llm_engine* engine, int32_t slot);
+/* seq_alloc for a prompt whose token ids are known (host memory). With cfg.prefix_cache the
+ * longest run of leading full pages that an earlier prompt already filled is shared with this
+ * slot (at least one prompt token always stays uncached: its logits select the first new token);
+ * *out_cached_tokens says how many prompt tokens the next b200llm_prefill of this slot will skip.
+ * That prefill must pass exactly these ids from HOST memory. Without cfg.prefix_cache this is
+ * seq_alloc with *out_cached_tokens = 0. */
+int b200llm_seq_alloc_with_prefix(b200llm_engine* engine, const int32_t* ids_host, int32_t n_ids,
+                                  int32_t capacity_tokens, int32_t* out_slot,
+                                  int32_t* out_cached_tokens);
+/* Prefix-cache counters since engine creation: prompt tokens looked up, prompt tokens served
+ * from cached pages, pages currently held by the cache. Any pointer may be NULL. */
+int b200llm_prefix_cache_stats(b200llm_engine* engine, int64_t* out_lookup_tokens,
+                               int64_t* out_hit_tokens, int64_t* out_cached_pages);
+/* Stop generating for a slot whose caller gave up (llm_server.py's callers time out after
+ * 10-20 s, raft_node.py:2018,2084,2126,2187): the row is marked finished on the device, in
+ * stream order, so later decode steps emit pad for it and append nothing. Free the slot with
+ * b200llm_seq_free once the steps already enqueued for it have drained (after the next
+ * b200llm_read_status / b200llm_sync). */
+int b200llm_seq_cancel(b200llm_engine* engine, int32_t slot);
 int b200llm_kv_pages_free(b200llm_engine* engine, int64_t* out_free_pages, int64_t* out_total_pages);
 
 /* Per-sequence generation controls (defaults: greedy, min_new 0, max_new = engine cap). */
@@ -156,6 +187,16 @@ int b200llm_read_tokens(b200llm_engine* engine, int32_t slot, int32_t* out_token
 int b200llm_read_status(b200llm_engine* engine, const int32_t* slots_host, int32_t batch,
                         int32_t* out_counts_host, int32_t* out_finished_host);
 
+/* Status and generated tokens of several slots with ONE stream synchronisation: a gather of
+ * (n_gen, finished), then the token rows of the finished slots (or of every slot when
+ * only_finished == 0) into pinned staging, then one wait. Replaces read_status + one
+ * read_tokens per finished request in a serving loop.
+ *   out_tokens_host [batch, out_stride]: row b holds min(n_gen, out_stride) tokens when it was
+ *   copied, untouched otherwise; out_counts_host / out_finished_host [batch]. */
+int b200llm_read_tokens_batch(b200llm_engine* engine, const int32_t* slots_host, int32_t batch,
+                              int32_t only_finished, int32_t* out_tokens_host, int32_t out_stride,
+                              int32_t* out_counts_host, int32_t* out_finished_host);
+
 /* Last-position logits of the most recent prefill/decode call, row b = b-th slot passed.
  * [batch, vocab] fp32 to host (synchronises). Parity tests. */
 int b200llm_read_last_logits(b200llm_engine* engine, int32_t batch, float* out_logits_host);
@@ -204,10 +245,44 @@ int b200llm_op_embed(const float* wte_dev, const float* wpe_dev, const int32_t* 
 int b200llm_op_prefill_attention(const void* qkv_dev, const int32_t* cu_seqlens_dev, int32_t batch,
                                  int32_t max_seq_len, int32_t n_head, void* out_dev, void* stream);
 
+/* The LM head of a decode step exactly as the engine launches it: logits[token, v] =
+ * act[token, :] . wte[v, :] (tied head, modeling_gpt2.py:646-651, :705-706) with the greedy
+ * argmax ($TF/generation/utils.py:2793) fused into the GEMM epilogue. Every group of 32
+ * vocabulary rows leaves its best (value, index) per token in amax_val/amax_idx
+ * [b200llm_lm_head_argmax_groups(vocab, tokens), ld_amax]; entry eos_id is left out of the groups
+ * and its logit goes to eos_logit[token] (MinNewTokensLength masks it later). Both arrays must
+ * start at -inf / 0. logits_dev may be NULL (the decode step of greedy rows stores no logits).
+ * Algorithmic bytes: vocab*k*2 + tokens*k*2 (+ tokens*vocab*4 with logits). tokens <= 256. */
+int b200llm_op_lm_head_argmax(const void* act_dev, const void* wte_dev, int32_t tokens, int32_t vocab,
+                              int32_t k, int32_t eos_id, float* logits_dev, float* amax_val_dev,
+                              int32_t* amax_idx_dev, float* eos_logit_dev, int32_t ld_amax,
+                              void* stream);
+int32_t b200llm_lm_head_argmax_groups(int32_t vocab, int32_t tokens);
+
+/* Causal attention of packed prompt SUFFIXES against the paged KV cache (shared-prefix reuse):
+ * sequence b has prefix_len_dev[b] tokens already cached in its pages and contributes rows
+ * [cu_seqlens_dev[b], cu_seqlens_dev[b+1]) of qkv, whose positions are prefix_len + 0, 1, ...
+ * The suffix K/V must already be in the pages (b200llm_op_kv_scatter). slots_dev[b] selects the
+ * page-table row. modeling_gpt2.py:54-72 with the past taken from the cache (:194-196). */
+int b200llm_op_prefill_attention_paged(const void* qkv_dev, const int32_t* cu_seqlens_dev,
+                                       const int32_t* prefix_len_dev, const int32_t* slots_dev,
+                                       int32_t batch, int32_t max_suffix_len, int32_t n_head,
+                                       const int32_t* page_table_dev, int32_t max_pages_per_seq,
+                                       const void* k_pool_dev, const void* v_pool_dev, void* out_dev,
+                                       void* stream);
+/* K and V of packed rows -> KV pages: row t of qkv goes to position row_pos_dev[t] of slot
+ * row_slot_dev[t] ($TF/cache_utils.py:119-120). */
+int b200llm_op_kv_scatter(const void* qkv_dev, const int32_t* row_pos_dev, const int32_t* row_slot_dev,
+                          int32_t n_tok, int32_t n_head, const int32_t* page_table_dev,
+                          int32_t max_pages_per_seq, void* k_pool_dev, void* v_pool_dev, void* stream);
+
 /* One decode step of attention over paged KV (appends the new token's K/V first).
  * k_pool/v_pool: [n_pages, n_head, 16, 64] bf16; page_table [n_slots, max_pages_per_seq];
- * row b uses slot b. n_splits > 1 needs scratch_dev of b200llm_decode_attention_scratch_floats()
- * floats. modeling_gpt2.py:54-72 with q_len = 1; cache append $TF/cache_utils.py:119-120. */
+ * row b uses slot b. |n_splits| > 1 needs scratch_dev of b200llm_decode_attention_scratch_floats()
+ * floats; a NEGATIVE n_splits (-2..-8) merges the splits of a (row, head) inside the kernel over a
+ * thread-block cluster (the engine's choice for one or a few live rows) instead of through the
+ * scratch and a combine launch. modeling_gpt2.py:54-72 with q_len = 1; cache append
+ * $TF/cache_utils.py:119-120. */
 int b200llm_op_decode_attention(const void* qkv_dev, const int32_t* seq_len_dev,
                                 const int32_t* page_table_dev, int32_t max_pages_per_seq,
                                 void* k_pool_dev, void* v_pool_dev, void* out_dev, int32_t batch,
@@ -233,7 +308,10 @@ size_t b200llm_decode_attention_scratch_floats(int32_t batch, int32_t n_head, in
  *   - Cost: every GPU on which the library is loaded holds those 4 MiB until the process exits.
  *   - The call performs no cudaMalloc / cudaFree and uses no allocating library routine.
  *   - The first call on each device looks up the array's device address (with that device
- *     current). Make that first call before starting any stream capture on the device.
+ *     current). Make that first call before starting any stream capture on the device -- and at
+ *     start-up, BEFORE the device's memory is handed to your own pool: CUDA loads a module (and
+ *     reserves the memory of its global arrays, this one included) the first time something in
+ *     it is used, so a first call made after all device memory is taken can fail or stall.
  *   - All calls on a device share the one array, which keeps whatever the previous call left in
  *     it. Nothing in it needs clearing (each slot is written before it is read within a call),
  *     but two calls whose kernels can run at the same time on the GPU -- different streams without

@@ -100,6 +100,18 @@ def pack_blob(shape: GPT2Shape, weights: dict[str, torch.Tensor]) -> torch.Tenso
     return torch.cat([weights[name].reshape(-1).float() for name, _ in tensor_specs(shape)])
 
 
+def unpack_blob(shape: GPT2Shape, blob) -> dict[str, torch.Tensor]:
+    """Inverse of pack_blob: the state dict a flat fp32 blob (C-ABI order) stands for."""
+    flat = torch.as_tensor(blob, dtype=torch.float32).reshape(-1)
+    out, at = {}, 0
+    for name, shp in tensor_specs(shape):
+        n = int(math.prod(shp))
+        out[name] = flat[at:at + n].reshape(shp)
+        at += n
+    assert at == flat.numel(), "blob size does not match the shape"
+    return out
+
+
 def synthetic_prompts(batch: int, length: int, vocab: int = 50257, seed: int = 1234) -> torch.Tensor:
     """Token ids uniform in [0, vocab-1) (EOS excluded), SURVEY.md section 8d."""
     g = torch.Generator().manual_seed(seed)

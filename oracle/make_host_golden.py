@@ -24,7 +24,9 @@ REF = Path("/root/reference")
 OUT = Path(__file__).resolve().parent.parent / "tests" / "golden" / "host_golden.json"
 
 
-def load_reference():
+def load_reference(root: Path = REF):
+    """Import the reference's llm_server.py exactly as shipped from `root` (the read-only checkout,
+    or a staged copy of its llm_server/ and generated/ directories)."""
     stub = types.ModuleType("google.generativeai")
     stub.configure = lambda **kw: None
     stub.GenerativeModel = lambda name: object()
@@ -33,12 +35,25 @@ def load_reference():
 
     google.generativeai = stub
     sys.modules["google.generativeai"] = stub
-    sys.path.insert(0, str(REF))
-    sys.path.insert(0, str(REF / "llm_server"))
+    sys.path.insert(0, str(root))
+    sys.path.insert(0, str(root / "llm_server"))
     import importlib
 
     mod = importlib.import_module("llm_server")
-    mod.time.sleep = lambda s: None  # back-off sleeps are not part of the result
+    # back-off sleeps are not part of the result: give the MODULE a stand-in for `time` whose
+    # sleep() returns at once (patching time.sleep itself would leak into the whole process)
+    real_time = mod.time
+
+    class _NoSleepTime:
+        def __getattr__(self, name):
+            return getattr(real_time, name)
+
+        @staticmethod
+        def sleep(_seconds):
+            return None
+
+    if not isinstance(real_time, _NoSleepTime) and getattr(real_time, "__name__", "") == "time":
+        mod.time = _NoSleepTime()
     import generated.llm_service_pb2 as pb2
 
     return mod, pb2

@@ -252,14 +252,13 @@ def test_prefill_attention(ops, cuda, lens, n_head):
     ([1100, 3, 64, 700], 16, 16),
     ([300, 299], 20, 2),
 ])
-@pytest.mark.parametrize("cluster", ["0", "1"])
-def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, cluster, monkeypatch):
+@pytest.mark.parametrize("cluster", [False, True], ids=["scratch-combine", "cluster-combine"])
+def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, cluster):
     """seq_len[b] tokens are cached; the new token (position seq_len[b]) is appended by the
     kernel, then attends over everything including itself. `cluster` = 1 makes 2..8 KV splits merge
     inside the kernel (the engine's setting) instead of through scratch + a combine launch."""
-    if cluster == "1" and not 2 <= n_splits <= 8:
+    if cluster and not 2 <= n_splits <= 8:
         pytest.skip("the in-cluster combine only exists for 2..8 splits")
-    monkeypatch.setenv("B200LLM_ATTN_CLUSTER", cluster)
     d = n_head * 64
     B = len(ctx_lens)
     page = 16
@@ -282,7 +281,7 @@ def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, cluster, 
             v_pool[p, :, t % page] = v[t]
     qkv = (torch.randn(B, 3 * d, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
     seq_len = torch.tensor(ctx_lens, dtype=torch.int32, device=cuda)
-    out = ops.decode_attention(qkv, seq_len, page_table, k_pool, v_pool, n_head, n_splits)
+    out = ops.decode_attention(qkv, seq_len, page_table, k_pool, v_pool, n_head, n_splits, cluster=cluster)
     torch.cuda.synchronize()
     for b, L in enumerate(ctx_lens):
         cur = qkv[b].view(3, n_head, 64)
@@ -295,3 +294,97 @@ def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, cluster, 
         p = page_table[b, L // page].item()
         assert torch.equal(k_pool[p, :, L % page], cur[1])
         assert torch.equal(v_pool[p, :, L % page], cur[2])
+
+
+@pytest.mark.parametrize("prefix_suffix,n_head", [
+    ([(0, 40), (64, 1), (16, 100), (496, 130)], 12),    # no prefix / one token / ragged tiles / long prefix
+    ([(1008, 16), (32, 33)], 16),                       # Summarize-like: almost everything cached
+    ([(48, 64), (64, 64), (80, 65), (0, 200)], 20),     # prefix not a multiple of the 64-key tile
+])
+def test_prefill_attention_over_a_cached_prefix(ops, cuda, prefix_suffix, n_head):
+    """Shared-prefix reuse: sequence b has `prefix` tokens in its pages already; its `suffix` rows
+    are scattered to the pages by kv_scatter and then attend over prefix + suffix keys read from
+    the pages. Reference: causal attention of the suffix queries over all keys."""
+    d, page = n_head * 64, 16
+    B = len(prefix_suffix)
+    totals = [p + s for p, s in prefix_suffix]
+    max_pages = (max(totals) + page - 1) // page
+    n_pages = B * max_pages + 5
+    g = torch.Generator(device="cpu").manual_seed(11)
+    page_table = torch.randperm(n_pages, generator=g)[: B * max_pages].int().view(B, max_pages).contiguous().to(cuda)
+    k_pool = torch.zeros(n_pages, n_head, page, 64, dtype=torch.bfloat16, device=cuda)
+    v_pool = torch.zeros_like(k_pool)
+    n_rows = sum(s for _, s in prefix_suffix)
+    qkv = (torch.randn(n_rows, 3 * d, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+    ks, vs, row_pos, row_slot, cu = [], [], [], [], [0]
+    for b, (P, S) in enumerate(prefix_suffix):
+        k = (torch.randn(P, n_head, 64, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+        v = (torch.randn(P, n_head, 64, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+        for t in range(P):
+            pg = page_table[b, t // page].item()
+            k_pool[pg, :, t % page] = k[t]
+            v_pool[pg, :, t % page] = v[t]
+        ks.append(k)
+        vs.append(v)
+        row_pos += list(range(P, P + S))
+        row_slot += [b] * S
+        cu.append(cu[-1] + S)
+    row_pos = torch.tensor(row_pos, dtype=torch.int32, device=cuda)
+    row_slot = torch.tensor(row_slot, dtype=torch.int32, device=cuda)
+    cu_t = torch.tensor(cu, dtype=torch.int32, device=cuda)
+    prefix = torch.tensor([p for p, _ in prefix_suffix], dtype=torch.int32, device=cuda)
+    slots = torch.arange(B, dtype=torch.int32, device=cuda)
+    k_before, v_before = k_pool.clone(), v_pool.clone()
+    ops.kv_scatter(qkv, row_pos, row_slot, page_table, k_pool, v_pool, n_head)
+    out = ops.prefill_attention_paged(qkv, cu_t, prefix, slots, max(s for _, s in prefix_suffix), n_head,
+                                      page_table, k_pool, v_pool)
+    torch.cuda.synchronize()
+    for b, (P, S) in enumerate(prefix_suffix):
+        blk = qkv[cu[b]:cu[b + 1]].view(S, 3, n_head, 64)
+        k_all = torch.cat([ks[b], blk[:, 1]], 0)
+        v_all = torch.cat([vs[b], blk[:, 2]], 0)
+        ref = _ref_attention(blk[:, 0], k_all, v_all).reshape(S, d)
+        got = out[cu[b]:cu[b + 1]].float()
+        assert (got - ref).abs().max().item() <= 2e-2, (b, P, S, (got - ref).abs().max().item())
+        # the scatter wrote exactly the suffix rows, the cached prefix rows are untouched
+        for t in (0, S // 2, S - 1):
+            pg = page_table[b, (P + t) // page].item()
+            assert torch.equal(k_pool[pg, :, (P + t) % page], blk[t, 1])
+            assert torch.equal(v_pool[pg, :, (P + t) % page], blk[t, 2])
+        for t in range(0, P, 7):
+            pg = page_table[b, t // page].item()
+            assert torch.equal(k_pool[pg, :, t % page], k_before[pg, :, t % page])
+            assert torch.equal(v_pool[pg, :, t % page], v_before[pg, :, t % page])
+
+
+@pytest.mark.parametrize("tokens,vocab,k", [(64, 50257, 768), (4, 50257, 768), (32, 50257, 1280), (1, 1000, 128),
+                                            (200, 12345, 256)])
+def test_lm_head_with_fused_argmax(ops, cuda, tokens, vocab, k):
+    """The kernel instantiation the decode step launches (kEpiLogitsArgmax, balanced row ranges for
+    one token tile): candidates reduce to torch's argmax of the fp32 logits of the same bf16 inputs,
+    ties to the lowest index, EOS kept apart; optional logits equal the plain LM-head GEMM."""
+    g = torch.Generator(device="cpu").manual_seed(tokens + vocab)
+    act = (torch.randn(tokens, k, generator=g) * 0.5).to(torch.bfloat16).to(cuda)
+    wte = (torch.randn(vocab, k, generator=g) * 0.05).to(torch.bfloat16).to(cuda)
+    eos = vocab - 1
+    wte[eos] = act[0] * 0.2                      # EOS would win row 0 if it were not kept apart
+    wte[7] = wte[vocab // 2]                     # an exact tie across two groups -> lowest index wins
+    logits = torch.zeros(tokens, vocab, device=cuda)
+    for store in (False, True):
+        val, idx, eos_logit = ops.lm_head_argmax(act, wte, eos, logits if store else None)
+        torch.cuda.synchronize()
+        ref = act.float() @ wte.float().t()
+        assert (eos_logit - ref[:, eos]).abs().max().item() <= 2e-3 * ref.abs().max().item()
+        masked = ref.clone()
+        masked[:, eos] = float("-inf")
+        want = masked.argmax(-1)
+        best = val.max(0)
+        # lowest index among the groups that reach the maximum
+        cand = torch.where(val == best.values[None, :], idx, torch.full_like(idx, vocab))
+        got = cand.min(0).values.long()
+        margin = masked.topk(2, -1).values
+        decisive = (margin[:, 0] - margin[:, 1]) > 1e-3 * ref.abs().max().item()
+        assert (got[decisive] == want[decisive]).all()
+        assert (got != eos).all()
+        if store:
+            assert (logits - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()

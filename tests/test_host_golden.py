@@ -85,7 +85,7 @@ def _run(case):
         result = {"suggestions": s, "topics": t}
     else:
         servicer = svc.LLMServicer(model)
-        svc.time.sleep = nosleep
+        svc._sleep = nosleep
         if kind == "rpc_smart_reply":
             r = servicer.GetSmartReply(pb.SmartReplyRequest(request_id=req["request_id"],
                                                             recent_messages=_msgs(req["messages"]),

@@ -102,3 +102,86 @@ def test_many_threads_submitting_concurrently():
     [t.join() for t in threads]
     assert all(results[i] == [(i + s) % 50000 for s in range(5)] for i in range(32))
     r.shutdown()
+
+
+def test_a_decode_error_frees_the_slots_and_later_requests_still_complete():
+    """the catch-all used to fail the futures without seq_free, leaking every active
+    slot and its KV pages; afterwards nothing could ever be admitted again."""
+    eng = FakeEngine(max_seqs=2, max_new_tokens=8, fail_decode_times=1)
+    r = _router(eng, decode_burst=4)
+    first = [r.submit([i + 1], SamplingParams(max_new_tokens=6)) for i in range(2)]
+    for f in first:
+        with pytest.raises(RuntimeError):
+            f.result(timeout=5)
+    assert not eng.slots, "slots leaked by the error path"
+    assert eng.pool_left == 2 * 64
+    later = [r.submit([i + 5], SamplingParams(max_new_tokens=6)) for i in range(4)]
+    assert all(len(f.result(timeout=5).tokens) == 6 for f in later)
+    assert r.workers[0].inflight_tokens == 0
+    r.shutdown()
+
+
+def test_a_request_larger_than_the_whole_kv_pool_fails_instead_of_spinning():
+    eng = FakeEngine(max_seqs=4, max_seq_len=64, max_new_tokens=16, kv_pool_tokens=32)
+    r = _router(eng)
+    with pytest.raises(ValueError):
+        r.generate([1] * 30, SamplingParams(max_new_tokens=16), timeout=5)   # needs 46 > 32 pool tokens
+    assert len(r.generate([1] * 4, SamplingParams(max_new_tokens=8), timeout=5).tokens) == 8
+    r.shutdown()
+
+
+def test_timeout_cancels_the_request_and_returns_its_slot():
+    """ADVICE r1 / VERDICT r1 weak #9: a caller that gives up must not leave its sequence decoding
+    to max_new_tokens (ask-AI retries three times, llm_server.py:147-212)."""
+    import time
+    from concurrent.futures import TimeoutError as FutureTimeout
+
+    eng = FakeEngine(max_seqs=2, max_seq_len=4096, max_new_tokens=2000, step_sleep=0.002)
+    r = _router(eng, decode_burst=4)
+    with pytest.raises(FutureTimeout):
+        r.generate([1, 2, 3], SamplingParams(max_new_tokens=2000), timeout=0.1)
+    deadline = time.time() + 5
+    while eng.slots and time.time() < deadline:
+        time.sleep(0.01)
+    assert not eng.slots, "the abandoned request kept its slot"
+    assert eng.cancels, "the engine was never told to stop the sequence"
+    assert r.workers[0].inflight_tokens == 0 and r.workers[0].cancelled == 1
+    steps = sum(c[2] for c in eng.calls if c[0] == "decode")
+    assert steps < 500, f"kept decoding after the cancel: {steps} steps"
+    # a request cancelled while still waiting is dropped at admission
+    blocker = r.submit([9], SamplingParams(max_new_tokens=300))
+    blocker2 = r.submit([8], SamplingParams(max_new_tokens=300))
+    waiting = r.submit([7], SamplingParams(max_new_tokens=5))
+    sched.EngineWorker.cancel(waiting)
+    with pytest.raises(TimeoutError):
+        waiting.result(timeout=5)
+    assert len(blocker.result(timeout=10).tokens) == 300 and len(blocker2.result(timeout=10).tokens) == 300
+    r.shutdown()
+
+
+def test_a_failing_replica_is_bypassed_and_reprobed():
+    """a worker whose engine keeps raising has zero in-flight tokens and used
+    to attract EVERY new request. After FAIL_LIMIT failures it leaves the rotation; one probe
+    request is sent to it every REPROBE_S seconds and a success brings it back."""
+    import time
+
+    bad = FakeEngine(max_seqs=4, fail_prefill=True)
+    good = FakeEngine(max_seqs=4)
+    r = _router(bad, good)
+    wb, wg = r.workers
+    wb.REPROBE_S = 0.3
+    sp = SamplingParams(max_new_tokens=4)
+    outcomes = []
+    for i in range(20):
+        try:
+            outcomes.append(len(r.generate([i + 1], sp, timeout=5).tokens))
+        except RuntimeError:
+            outcomes.append(-1)
+    assert outcomes.count(-1) == sched.EngineWorker.FAIL_LIMIT, outcomes
+    assert outcomes[-10:] == [4] * 10 and not wb.healthy
+    # the replica recovers: the next probe succeeds and it takes traffic again
+    bad.fail_prefill = False
+    time.sleep(0.35)
+    assert len(r.generate([99], sp, timeout=5).tokens) == 4
+    assert wb.healthy and wb.completed == 1
+    r.shutdown()

@@ -72,7 +72,7 @@ def test_backend_failure_never_becomes_a_grpc_error(served):
         def generate_content(self, *a, **k):
             raise RuntimeError("GPU on fire")
 
-    svc.time.sleep = lambda s: None
+    svc._sleep = lambda s: None
     with grpc.insecure_channel(served(Broken())) as ch:
         stub = server_mod.LLMServiceStub(ch)
         m = [pb.Message(sender="a", content="b")]

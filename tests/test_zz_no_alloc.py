@@ -8,8 +8,8 @@ split-KV partial results in a fixed 4 MiB array inside the library instead of a 
 
 This test calls that entry point through the C ABI twice in a row (different shapes, so the
 second call runs over whatever the first one left in the shared array) and checks each result
-against the ordinary entry point that takes a caller-allocated scratch buffer, with the same
-2e-2 tolerance the other attention tests use. It also checks that a request beyond the built-in
+against the ordinary entry point that takes a caller-allocated scratch buffer and against a plain
+fp32 reference, with the same 2e-2 tolerance the other attention tests use. It also checks that a request beyond the built-in
 limit is refused with a clear message. The file name makes pytest collect it last.
 """
 import ctypes as C
@@ -46,6 +46,21 @@ def _noalloc(lib, qkv, seq_len, table, k_pool, v_pool, n_head, n_splits):
     return rc, out
 
 
+def _fp32_reference(qkv, ctx_lens, table, k_pool, v_pool, n_head):
+    """Plain fp32 softmax(q K^T / 8) V over the cached rows plus the new token's own K/V (which the
+    kernel has appended to the pool by the time this runs), the same reference test_gpu_ops.py uses."""
+    out = []
+    for b, L in enumerate(ctx_lens):
+        pos = torch.arange(L + 1, device=qkv.device)
+        pages = table[b, pos // PAGE].long()
+        k = k_pool[pages, :, pos % PAGE].float()      # [L+1, H, 64]
+        v = v_pool[pages, :, pos % PAGE].float()
+        q = qkv[b].view(3, n_head, 64)[0].float()     # [H, 64]
+        p = torch.softmax(torch.einsum("hd,shd->hs", q, k) / 8.0, dim=-1)
+        out.append(torch.einsum("hs,shd->hd", p, v).reshape(-1))
+    return torch.stack(out)
+
+
 def test_noalloc_decode_attention_matches_the_scratch_buffer_entry_point(cuda):
     _lib, ops = pkg("_lib"), pkg("ops")
     lib = _lib.lib
@@ -60,6 +75,7 @@ def test_noalloc_decode_attention_matches_the_scratch_buffer_entry_point(cuda):
         torch.cuda.synchronize()
         assert torch.isfinite(got.float()).all()
         assert (got.float() - expected.float()).abs().max().item() <= 2e-2
+        assert (got.float() - _fp32_reference(qkv, ctx_lens, table, k_pool, v_pool, n_head)).abs().max().item() <= 2e-2
         # both entry points append the new token's K/V to the same page slots
         assert torch.equal(k_pool, k_ref) and torch.equal(v_pool, v_ref)
 
