@@ -49,7 +49,14 @@ struct PagedPrefillArgs {
   const __nv_bfloat16* k_pool = nullptr;
   const __nv_bfloat16* v_pool = nullptr;
   __nv_bfloat16* out = nullptr;           // [n_rows, d]
+  int qkv_rows = 0;                       // rows backing qkv   } only the tcgen05 kernel needs these
+  int n_pages = 0;                        // pages in each pool } (extents of its TMA tensor maps)
 };
+// The engine's prefill attention (attention_tc.cu): tcgen05.mma for Q K^T and P V, accumulators
+// in TMEM, Q / K / V tiles by TMA.
+int prefill_attention_tc(const PagedPrefillArgs& a, cudaStream_t stream);
+// The same computation on the legacy tensor path (mma.sync + cp.async); kept as the A/B partner of
+// the kernel above (b200llm_op_prefill_attention_paged impl = 1).
 int prefill_attention_paged(const PagedPrefillArgs& a, cudaStream_t stream);
 
 struct DecodeAttnArgs {

@@ -340,7 +340,7 @@ struct StepPlan {
   int max_len = 0;     // prefill: longest prompt
   float* logits_all = nullptr;
   bool store_logits = true;  // materialise last-position logits (sampling rows / parity reads)
-  bool paged_prefill = false;  // prefill rows are prompt suffixes: attention reads K/V from the pages
+  bool paged_prefill = false;  // some prefill rows are prompt suffixes behind a cached prefix (prefix_dev is valid)
 };
 
 enum SkipBits { kSkipLn = 1, kSkipGemm = 2, kSkipAttn = 4, kSkipHead = 8, kSkipSelect = 16, kSkipGelu = 32 };
@@ -456,15 +456,14 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       if (p.attn_splits > 1 && !(a.cluster_combine && p.attn_splits <= 8)) {
         e->launches += 1, e->launches_in_capture += 1;  // separate combine kernel
       }
-    } else if (p.paged_prefill) {
-      // shared-prefix reuse: the suffix rows' K/V go to their pages first, then every query
-      // attends over the pages (cached prefix + the rows just written)
-      B200_PROPAGATE(count(e, kv_scatter(e->qkv, e->row_pos, e->row_slot, rows, e->H, e->page_table,
-                                         e->max_pages_per_seq, kp, vp, e->stream)));
+    } else {
+      // Prefill: every query attends over its sequence's cached prefix (shared-prefix reuse; read
+      // from the pages) followed by the rows of this call (read from qkv); the CTA on the diagonal
+      // writes its K/V tile into the pages, so there is no scatter pass.
       PagedPrefillArgs pa;
       pa.qkv = e->qkv;
       pa.cu_seqlens = e->cu_dev;
-      pa.prefix_len = e->prefix_dev;
+      pa.prefix_len = p.paged_prefill ? e->prefix_dev : nullptr;
       pa.slots = e->slots_dev;
       pa.batch = p.batch;
       pa.max_suffix_len = p.max_len;
@@ -474,16 +473,9 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       pa.k_pool = kp;
       pa.v_pool = vp;
       pa.out = e->attn;
-      B200_PROPAGATE(count(e, prefill_attention_paged(pa, e->stream)));
-    } else {
-      PrefillCache pc;
-      pc.slots = e->slots_dev;
-      pc.page_table = e->page_table;
-      pc.max_pages_per_seq = e->max_pages_per_seq;
-      pc.k_pool = kp;
-      pc.v_pool = vp;
-      B200_PROPAGATE(count(e, prefill_attention(e->qkv, e->cu_dev, p.batch, p.max_len, e->H,
-                                                e->attn, e->stream, &pc)));
+      pa.qkv_rows = e->max_rows;
+      pa.n_pages = static_cast<int>(e->n_pages);
+      B200_PROPAGATE(count(e, prefill_attention_tc(pa, e->stream)));
     }
     // attn c_proj + residual (:223, :282)
     if (p.decode && p.cl_o > 1) {
@@ -906,6 +898,10 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   e->pool_layer_stride = static_cast<size_t>(e->n_pages) * H * kPageTokens * kHeadDim;
   E_TRY(dev_alloc_t(e.get(), &e->k_pool, e->pool_layer_stride * L));
   E_TRY(dev_alloc_t(e.get(), &e->v_pool, e->pool_layer_stride * L));
+  // Pages start at zero: the prefill attention multiplies exact-zero softmax weights with whatever a
+  // partly filled page holds behind its last token, and 0 x (uninitialised NaN pattern) is NaN.
+  E_CUDA(cudaMemsetAsync(e->k_pool, 0, e->pool_layer_stride * L * sizeof(__nv_bfloat16), st));
+  E_CUDA(cudaMemsetAsync(e->v_pool, 0, e->pool_layer_stride * L * sizeof(__nv_bfloat16), st));
   E_TRY(dev_alloc_t(e.get(), &e->page_table, static_cast<size_t>(cfg->max_seqs) * e->max_pages_per_seq));
   E_CUDA(cudaMemsetAsync(e->page_table, 0,
                          static_cast<size_t>(cfg->max_seqs) * e->max_pages_per_seq * sizeof(int32_t), st));
@@ -1734,10 +1730,11 @@ int b200llm_op_lm_head_argmax(const void* act, const void* wte, int32_t tokens, 
 
 int32_t b200llm_lm_head_argmax_groups(int32_t vocab, int32_t tokens) { return gemm_argmax_groups(vocab, tokens); }
 
-int b200llm_op_prefill_attention_paged(const void* qkv, const int32_t* cu_seqlens, const int32_t* prefix_len,
-                                       const int32_t* slots, int32_t batch, int32_t max_suffix_len,
-                                       int32_t n_head, const int32_t* page_table, int32_t max_pages_per_seq,
-                                       const void* k_pool, const void* v_pool, void* out, void* stream) {
+int b200llm_op_prefill_attention_paged(const void* qkv, int32_t n_rows, const int32_t* cu_seqlens,
+                                       const int32_t* prefix_len, const int32_t* slots, int32_t batch,
+                                       int32_t max_suffix_len, int32_t n_head, const int32_t* page_table,
+                                       int32_t max_pages_per_seq, const void* k_pool, const void* v_pool,
+                                       int32_t n_pages, void* out, int32_t impl, void* stream) {
   B200_CHECK_ARG(qkv && cu_seqlens && prefix_len && slots && page_table && k_pool && v_pool && out,
                  "op_prefill_attention_paged: null argument");
   PagedPrefillArgs a;
@@ -1753,7 +1750,10 @@ int b200llm_op_prefill_attention_paged(const void* qkv, const int32_t* cu_seqlen
   a.k_pool = static_cast<const __nv_bfloat16*>(k_pool);
   a.v_pool = static_cast<const __nv_bfloat16*>(v_pool);
   a.out = static_cast<__nv_bfloat16*>(out);
-  return prefill_attention_paged(a, reinterpret_cast<cudaStream_t>(stream));
+  a.qkv_rows = n_rows;
+  a.n_pages = n_pages;
+  return impl == 1 ? prefill_attention_paged(a, reinterpret_cast<cudaStream_t>(stream))
+                   : prefill_attention_tc(a, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b200llm_op_kv_scatter(const void* qkv, const int32_t* row_pos, const int32_t* row_slot, int32_t n_tok,

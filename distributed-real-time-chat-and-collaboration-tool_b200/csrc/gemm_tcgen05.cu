@@ -22,6 +22,7 @@
 // epilogue, two accumulator stages so the epilogue of tile i overlaps the MMAs of tile i+1).
 #include "gemm_tcgen05.cuh"
 
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -1280,13 +1281,17 @@ int get_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMa
   return kOk;
 }
 
+// SM count of the CURRENT device (one process may drive several GPUs, one worker thread each).
 int num_sms() {
-  static int n = 0;
+  static std::atomic<int> cached[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return 148;
+  int n = cached[dev].load(std::memory_order_relaxed);
   if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     if (n <= 0) n = 148;
+    cached[dev].store(n, std::memory_order_relaxed);
   }
   return n;
 }
@@ -1556,6 +1561,10 @@ int launch_pair(const GemmArgs& g, cudaStream_t stream) {
 }  // namespace
 
 B200_DEFINE_STEP_TRACE_SETTER(step_trace_set_gemm)
+
+int gemm_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+  return get_tensor_map(ptr, rows, cols, box_rows, out);
+}
 
 void gemm_clear_tensor_map_cache() {
   std::lock_guard<std::mutex> lock(map_mutex());

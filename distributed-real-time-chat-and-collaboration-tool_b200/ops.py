@@ -100,13 +100,14 @@ def kv_scatter(qkv: torch.Tensor, row_pos: torch.Tensor, row_slot: torch.Tensor,
 
 def prefill_attention_paged(qkv: torch.Tensor, cu_seqlens: torch.Tensor, prefix_len: torch.Tensor,
                             slots: torch.Tensor, max_suffix_len: int, n_head: int, page_table: torch.Tensor,
-                            k_pool: torch.Tensor, v_pool: torch.Tensor) -> torch.Tensor:
-    """Causal attention of prompt suffixes over the paged cache (prefix + suffix keys in the pages)."""
+                            k_pool: torch.Tensor, v_pool: torch.Tensor, impl: int = 0) -> torch.Tensor:
+    """Causal attention of prompt suffixes over the paged cache (prefix + suffix keys in the pages).
+    impl 0: the engine's tcgen05 kernel; 1: the mma.sync version of the same computation."""
     out = torch.zeros(qkv.shape[0], n_head * 64, dtype=torch.bfloat16, device=qkv.device)
-    check(lib.b200llm_op_prefill_attention_paged(_ptr(qkv), _ptr(cu_seqlens), _ptr(prefix_len), _ptr(slots),
-                                                 cu_seqlens.numel() - 1, max_suffix_len, n_head,
+    check(lib.b200llm_op_prefill_attention_paged(_ptr(qkv), qkv.shape[0], _ptr(cu_seqlens), _ptr(prefix_len),
+                                                 _ptr(slots), cu_seqlens.numel() - 1, max_suffix_len, n_head,
                                                  _ptr(page_table), page_table.shape[1], _ptr(k_pool),
-                                                 _ptr(v_pool), _ptr(out), _stream()))
+                                                 _ptr(v_pool), k_pool.shape[0], _ptr(out), impl, _stream()))
     return out
 
 

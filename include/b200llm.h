@@ -263,13 +263,18 @@ int32_t b200llm_lm_head_argmax_groups(int32_t vocab, int32_t tokens);
  * sequence b has prefix_len_dev[b] tokens already cached in its pages and contributes rows
  * [cu_seqlens_dev[b], cu_seqlens_dev[b+1]) of qkv, whose positions are prefix_len + 0, 1, ...
  * The suffix K/V must already be in the pages (b200llm_op_kv_scatter). slots_dev[b] selects the
- * page-table row. modeling_gpt2.py:54-72 with the past taken from the cache (:194-196). */
-int b200llm_op_prefill_attention_paged(const void* qkv_dev, const int32_t* cu_seqlens_dev,
+ * page-table row. modeling_gpt2.py:54-72 with the past taken from the cache (:194-196).
+ * This is the engine's prefill attention for EVERY prompt (prefix_len 0 for a cold one).
+ * n_rows = rows of qkv, n_pages = pages in each pool (extents of the TMA tensor maps).
+ * impl: 0 = tcgen05 (S = Q K^T and O = P V by tcgen05.mma with TMEM accumulators, Q / K / V tiles
+ * by TMA; what the engine runs), 1 = the same computation on the legacy mma.sync path (A/B partner).
+ * Pages must hold finite values behind a sequence's last token (the engine zeroes its pools). */
+int b200llm_op_prefill_attention_paged(const void* qkv_dev, int32_t n_rows, const int32_t* cu_seqlens_dev,
                                        const int32_t* prefix_len_dev, const int32_t* slots_dev,
                                        int32_t batch, int32_t max_suffix_len, int32_t n_head,
                                        const int32_t* page_table_dev, int32_t max_pages_per_seq,
-                                       const void* k_pool_dev, const void* v_pool_dev, void* out_dev,
-                                       void* stream);
+                                       const void* k_pool_dev, const void* v_pool_dev, int32_t n_pages,
+                                       void* out_dev, int32_t impl, void* stream);
 /* K and V of packed rows -> KV pages: row t of qkv goes to position row_pos_dev[t] of slot
  * row_slot_dev[t] ($TF/cache_utils.py:119-120). */
 int b200llm_op_kv_scatter(const void* qkv_dev, const int32_t* row_pos_dev, const int32_t* row_slot_dev,

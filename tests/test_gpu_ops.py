@@ -299,12 +299,18 @@ def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, cluster):
 @pytest.mark.parametrize("prefix_suffix,n_head", [
     ([(0, 40), (64, 1), (16, 100), (496, 130)], 12),    # no prefix / one token / ragged tiles / long prefix
     ([(1008, 16), (32, 33)], 16),                       # Summarize-like: almost everything cached
-    ([(48, 64), (64, 64), (80, 65), (0, 200)], 20),     # prefix not a multiple of the 64-key tile
+    ([(48, 64), (64, 64), (80, 65), (0, 200)], 20),     # prefix not a multiple of the key tile
+    ([(0, 128)] * 4, 12),                               # BASELINE config 2 prompts (cold)
+    ([(0, 1024), (0, 127), (0, 129), (0, 257)], 16),    # config 3 prompt: 8 query tiles x up to 8 key tiles
+    ([(1, 1), (15, 2), (127, 1), (128, 1), (129, 130)], 12),
 ])
-def test_prefill_attention_over_a_cached_prefix(ops, cuda, prefix_suffix, n_head):
-    """Shared-prefix reuse: sequence b has `prefix` tokens in its pages already; its `suffix` rows
-    are scattered to the pages by kv_scatter and then attend over prefix + suffix keys read from
-    the pages. Reference: causal attention of the suffix queries over all keys."""
+@pytest.mark.parametrize("impl", [0, 1], ids=["tcgen05", "mma.sync"])
+def test_prefill_attention_over_a_cached_prefix(ops, cuda, prefix_suffix, n_head, impl):
+    """The engine's prefill attention. Sequence b has `prefix` tokens in its pages already (0 for a
+    cold prompt); its `suffix` rows are scattered to the pages by kv_scatter and then attend over
+    prefix + suffix keys read from the pages. Reference: fp32 causal attention of the suffix queries
+    over all keys. impl 0 is the tcgen05 / TMEM / TMA kernel the engine runs, impl 1 the same
+    computation with mma.sync."""
     d, page = n_head * 64, 16
     B = len(prefix_suffix)
     totals = [p + s for p, s in prefix_suffix]
@@ -335,9 +341,10 @@ def test_prefill_attention_over_a_cached_prefix(ops, cuda, prefix_suffix, n_head
     prefix = torch.tensor([p for p, _ in prefix_suffix], dtype=torch.int32, device=cuda)
     slots = torch.arange(B, dtype=torch.int32, device=cuda)
     k_before, v_before = k_pool.clone(), v_pool.clone()
-    ops.kv_scatter(qkv, row_pos, row_slot, page_table, k_pool, v_pool, n_head)
+    if impl == 1:   # the mma.sync partner reads every key from the pages; the tcgen05 kernel fills them itself
+        ops.kv_scatter(qkv, row_pos, row_slot, page_table, k_pool, v_pool, n_head)
     out = ops.prefill_attention_paged(qkv, cu_t, prefix, slots, max(s for _, s in prefix_suffix), n_head,
-                                      page_table, k_pool, v_pool)
+                                      page_table, k_pool, v_pool, impl=impl)
     torch.cuda.synchronize()
     for b, (P, S) in enumerate(prefix_suffix):
         blk = qkv[cu[b]:cu[b + 1]].view(S, 3, n_head, 64)

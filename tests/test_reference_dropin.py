@@ -52,7 +52,9 @@ def _exercise_all_four_handlers(mod, pb2, model):
     msgs = [pb2.Message(sender="alice", content="Are we still on for the design review at 3pm?"),
             pb2.Message(sender="bob", content="Yes, I booked room 4B. Bring the latency numbers.")]
     r = servicer.GetSmartReply(pb2.SmartReplyRequest(request_id="s1", recent_messages=msgs, user_id="bob"), None)
-    assert r.request_id == "s1" and len(r.suggestions) == 3 and all(isinstance(x, str) and x for x in r.suggestions)
+    # three parsed lines, or the reference's own padding ("I agree", "Interesting point", llm_server.py:251-260)
+    # when the random-weight model's text has fewer usable lines
+    assert r.request_id == "s1" and 2 <= len(r.suggestions) <= 3 and all(isinstance(x, str) and x for x in r.suggestions)
     r = servicer.SummarizeConversation(pb2.SummarizeRequest(request_id="m1", messages=msgs, max_length=120), None)
     assert r.request_id == "m1" and 0 < len(r.summary) <= 120 and 1 <= len(r.key_points) <= 3
     r = servicer.GetLLMAnswer(pb2.LLMRequest(request_id="a1", query="When is the review?", context=["alice: 3pm"]), None)
@@ -68,7 +70,7 @@ def _exercise_all_four_handlers(mod, pb2, model):
     ts = [threading.Thread(target=call, args=(i,)) for i in range(8)]
     [t.start() for t in ts]
     [t.join() for t in ts]
-    assert sorted(int(o.request_id) for o in out) == list(range(8)) and all(len(o.suggestions) == 3 for o in out)
+    assert sorted(int(o.request_id) for o in out) == list(range(8)) and all(2 <= len(o.suggestions) <= 3 for o in out)
     return servicer
 
 
