@@ -38,6 +38,9 @@ WORKLOADS = {
     "ask_large_b256": ("large", 256, 64, 256),        # configs[3] on one GPU
     "probe_short_ctx": ("small", 64, 16, 32),         # profiling probe: negligible KV traffic
     "probe_b1_long": ("small", 1, 496, 32),           # profiling probe: one SmartReply request (byte-level prompt)
+    "probe_b16": ("small", 16, 128, 32),              # profiling probes: fewer live rows (stream-like buckets)
+    "probe_b32": ("small", 32, 128, 32),
+    "probe_b48": ("small", 48, 128, 32),
     "probe_long_ctx": ("small", 64, 512, 64),         # profiling probe: contexts like the byte-level gRPC stream
 }
 

@@ -127,6 +127,9 @@ def main():
     ap.add_argument("--clients", type=int, default=64, help="concurrent callers (threads over all caller processes)")
     ap.add_argument("--client-procs", type=int, default=4, help="caller processes (0 = callers share this process)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="also time this many requests per RPC on the host CPU")
+    ap.add_argument("--process-per-gpu", type=int, default=-1,
+                    help="1 = one worker process per GPU behind the router, 0 = worker threads, -1 = server default")
+    ap.add_argument("--prefix-cache", type=int, default=1, help="shared-prefix KV reuse in the engines (1 = as served)")
     ap.add_argument("--switch-interval", type=float, default=0.0, help="sys.setswitchinterval for the server process (0 = leave)")
     ap.add_argument("--as-client", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--port", type=int, default=0, help=argparse.SUPPRESS)
@@ -146,7 +149,9 @@ def main():
     pb = importlib.import_module(f"{PKG}.llm_proto")
 
     model = CountingModel(server_mod.build_local_model("small", args.gpus, max_seqs=64, max_seq_len=1024,
-                                                       max_new_tokens=160))
+                                                       max_new_tokens=160, prefix_cache=bool(args.prefix_cache),
+                                                       process_per_gpu=None if args.process_per_gpu < 0
+                                                       else bool(args.process_per_gpu)))
     model.inner.default_max_new_tokens = 32        # SmartReply 32; Summarize overrides below; Ask passes 150
     servicer = svc.LLMServicer(model)
     server = grpc.server(futures.ThreadPoolExecutor(max_workers=max(args.clients, 8) + 8))
@@ -184,7 +189,11 @@ def main():
         wall = t_last - t_first
     server.stop(0)
     workers = model.inner.router.workers
-    worker_phases = [{**{k: round(v, 3) for k, v in w.phase_s.items()}, "iterations": w.iterations} for w in workers]
+    snaps = [w.snapshot() for w in workers]
+    worker_phases = [{**s["phase_s"], "iterations": s["iterations"], "completed": s["completed"],
+                      "prefix_hit_tokens": s["prefix_hit_tokens"]} for s in snaps]
+    cache = [s["prefix_cache"] or {"lookup_tokens": 0, "hit_tokens": 0} for s in snaps]
+    per_process = type(workers[0]).__name__ == "RemoteEngineWorker"
     model.inner.router.shutdown()
 
     out = {
@@ -196,6 +205,12 @@ def main():
         "latency_ms": {k: {"n": len(v), "p50": float(np.percentile(v, 50)), "p95": float(np.percentile(v, 95))}
                        for k, v in lat.items() if v},
         "worker_loop_s": worker_phases,
+        "process_model": (f"one serving process (gRPC, prompts, tokenizer, router) + {args.gpus} engine worker "
+                          f"{'process(es), one per GPU' if per_process else 'thread(s) in the same process'}"),
+        "prefix_cache": {"enabled": bool(args.prefix_cache),
+                         "lookup_tokens": sum(c["lookup_tokens"] for c in cache),
+                         "hit_tokens": sum(c["hit_tokens"] for c in cache),
+                         "hit_rate": sum(c["hit_tokens"] for c in cache) / max(1, sum(c["lookup_tokens"] for c in cache))},
         "tokenizer": "byte-level GPT-2 ids (no vocab files offline): prompts are ~4x longer than with BPE",
         "data": "synthetic conversations, random-init GPT-2 small",
     }

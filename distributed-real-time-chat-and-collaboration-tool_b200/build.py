@@ -18,7 +18,7 @@ HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 BUILD = HERE / "build"
 LIB = HERE / "libb200llm.so"
-SOURCES = ["gemm_tcgen05.cu", "ops.cu", "attention.cu", "attention_tc.cu", "engine.cu"]
+SOURCES = ["gemm_tcgen05.cu", "ops.cu", "attention.cu", "attention_tc.cu", "decode_fused.cu", "engine.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

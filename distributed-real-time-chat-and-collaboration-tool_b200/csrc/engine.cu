@@ -29,6 +29,7 @@
 #include "../../include/b200llm.h"
 #include "attention.cuh"
 #include "common.cuh"
+#include "decode_fused.cuh"
 #include "gemm_tcgen05.cuh"
 #include "ops.cuh"
 
@@ -266,6 +267,7 @@ struct b200llm_engine {
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
   int tune_splits[4] = {0, 0, 0, 0};  // tune build: split-K overrides for qkv, o, fc, proj
   int tune_attn_splits = 0;           // tune build: KV split override
+  int tune_fused_splits[2] = {0, 0};  // tune build: K splits of the fused path's out-proj / MLP-down
 };
 
 namespace b200llm {
@@ -340,10 +342,15 @@ struct StepPlan {
   int max_len = 0;     // prefill: longest prompt
   float* logits_all = nullptr;
   bool store_logits = true;  // materialise last-position logits (sampling rows / parity reads)
+  // decode, <= 64 rows: LayerNorm folded into the QKV / MLP-up GEMMs, out-proj / MLP-down add
+  // their K splits into x in L2 (decode_fused.cu): 5 kernels per layer instead of 8
+  bool fused = false;
+  int rs_o = 1, rs_p = 1;  // K splits of the two reduce-add GEMMs
   bool paged_prefill = false;  // some prefill rows are prompt suffixes behind a cached prefix (prefix_dev is valid)
 };
 
-enum SkipBits { kSkipLn = 1, kSkipGemm = 2, kSkipAttn = 4, kSkipHead = 8, kSkipSelect = 16, kSkipGelu = 32 };
+enum SkipBits { kSkipLn = 1, kSkipGemm = 2, kSkipAttn = 4, kSkipHead = 8, kSkipSelect = 16, kSkipGelu = 32,
+                kSkipLnGemm = 64, kSkipRedAdd = 128 };  // the two fused-path kernel classes
 
 int count(b200llm_engine* e, int rc) {
   if (rc == kOk) {
@@ -412,6 +419,79 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
     __nv_bfloat16* kp = e->k_pool + static_cast<size_t>(l) * e->pool_layer_stride;
     __nv_bfloat16* vp = e->v_pool + static_cast<size_t>(l) * e->pool_layer_stride;
 
+    if (p.decode && p.fused) {
+      const bool skip_gemm = (e->skip_mask & kSkipGemm) != 0;
+      // ln_1 + c_attn (modeling_gpt2.py:273, :185) -> bf16 qkv
+      LnGemmArgs lg;
+      lg.x = e->x;
+      lg.gamma = w.ln1_g;
+      lg.beta = w.ln1_b;
+      lg.eps = e->cfg.ln_eps;
+      lg.w = w.w_qkv;
+      lg.bias = w.b_qkv;
+      lg.out = e->qkv;
+      lg.rows = rows;
+      lg.d = d;
+      lg.features = 3 * d;
+      lg.ld_out = 3 * d;
+      lg.gelu = 0;
+      lg.pdl = pdl;
+      const bool skip_lg = skip_gemm || (e->skip_mask & kSkipLnGemm) != 0;
+      const bool skip_ra = skip_gemm || (e->skip_mask & kSkipRedAdd) != 0;
+      if (!skip_lg) B200_PROPAGATE(count(e, ln_gemm(lg, e->stream)));
+      // attention (:186-222) over the paged cache
+      DecodeAttnArgs a = {};
+      a.qkv = e->qkv;
+      a.active_slots = e->active_dev;
+      a.seq_len = e->seq_len;
+      a.finished = e->finished;
+      a.page_table = e->page_table;
+      a.max_pages_per_seq = e->max_pages_per_seq;
+      a.k_pool = kp;
+      a.v_pool = vp;
+      a.out = e->attn;
+      a.batch = rows;
+      a.n_head = e->H;
+      a.n_splits = p.attn_splits;
+      a.scratch = e->attn_scratch;
+      a.pdl = pdl;
+      a.cluster_combine = (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
+      if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
+      if (p.attn_splits > 1 && !(a.cluster_combine && p.attn_splits <= 8)) {
+        e->launches += 1, e->launches_in_capture += 1;  // separate combine kernel
+      }
+      // attn c_proj + residual (:223, :282): x += attn . W_o + b_o, K splits added in L2
+      GemmRedAddArgs ra;
+      ra.act = e->attn;
+      ra.w = w.w_o;
+      ra.bias = w.b_o;
+      ra.x = e->x;
+      ra.rows = rows;
+      ra.features = d;
+      ra.k = d;
+      ra.split = p.rs_o;
+      ra.act_rows_alloc = e->max_rows;
+      ra.pdl = pdl;
+      if (!skip_ra) B200_PROPAGATE(count(e, gemm_redadd(ra, e->stream)));
+      // ln_2 + c_fc + gelu_new (:304, :239-240) -> bf16 ffn
+      lg.gamma = w.ln2_g;
+      lg.beta = w.ln2_b;
+      lg.w = w.w_fc;
+      lg.bias = w.b_fc;
+      lg.out = e->ffn;
+      lg.features = 4 * d;
+      lg.ld_out = 4 * d;
+      lg.gelu = 1;
+      if (!skip_lg) B200_PROPAGATE(count(e, ln_gemm(lg, e->stream)));
+      // mlp c_proj + residual (:241, :307)
+      ra.act = e->ffn;
+      ra.w = w.w_proj;
+      ra.bias = w.b_proj;
+      ra.k = 4 * d;
+      ra.split = p.rs_p;
+      if (!skip_ra) B200_PROPAGATE(count(e, gemm_redadd(ra, e->stream)));
+      continue;
+    }
     // ln_1 (modeling_gpt2.py:273), folding the previous layer's MLP partials into x first
     B200_PROPAGATE(ln(e, pending_partials, pending_n, rows, pending_bias, w.ln1_g, w.ln1_b,
                       nullptr, rows, pdl));
@@ -606,30 +686,38 @@ int mark_pinned_used(b200llm_engine* e) {
 }
 
 // ---- shared-prefix cache (cfg.prefix_cache) ---------------------------------------------------
-// Drop the least recently used cached page that nothing else references and that no other
-// cached page hangs off (leaves first, so a chain is never cut in the middle).
-bool evict_one_cached_page(b200llm_engine* e) {
-  const PrefixKey* best = nullptr;
-  uint64_t best_use = ~0ull;
-  for (const auto& kv : e->prefix_map) {
-    const PrefixEntry& en = kv.second;
-    if (en.children == 0 && e->page_ref[en.page] == 1 && en.last_use < best_use) {
-      best = &kv.first;
-      best_use = en.last_use;
+// Make room: drop least-recently-used cached pages that nothing else references and that no other
+// cached page hangs off (leaves first, so a chain is never cut in the middle). One scan of the
+// cache serves a whole batch of evictions -- at least `want` pages and a few percent of the pool on
+// top -- so a pool that is permanently full of cached prompts does not pay a scan per page.
+int evict_cached_pages(b200llm_engine* e, int want) {
+  int freed = 0;
+  const int goal = std::max(want, static_cast<int>(e->n_pages / 16));
+  while (freed < want) {
+    std::vector<std::pair<uint64_t, int32_t>> leaves;  // (last_use, page)
+    for (const auto& kv : e->prefix_map) {
+      const PrefixEntry& en = kv.second;
+      if (en.children == 0 && e->page_ref[en.page] == 1) leaves.emplace_back(en.last_use, en.page);
     }
+    if (leaves.empty()) break;
+    std::sort(leaves.begin(), leaves.end());
+    for (const auto& lf : leaves) {
+      if (freed >= goal) break;
+      const int32_t page = lf.second;
+      const PrefixKey key = e->page_key[page];
+      if (key.parent >= 0 && e->page_cached[key.parent]) {
+        auto it = e->prefix_map.find(e->page_key[key.parent]);
+        if (it != e->prefix_map.end()) it->second.children -= 1;
+      }
+      e->prefix_map.erase(key);
+      e->page_cached[page] = 0;
+      e->prefix_cached_pages -= 1;
+      if (--e->page_ref[page] == 0) e->free_pages.push_back(page);
+      ++freed;
+    }
+    // parents of the evicted leaves may have become leaves themselves: next round
   }
-  if (best == nullptr) return false;
-  const PrefixKey key = *best;
-  const int32_t page = e->prefix_map[key].page;
-  if (key.parent >= 0 && e->page_cached[key.parent]) {
-    auto it = e->prefix_map.find(e->page_key[key.parent]);
-    if (it != e->prefix_map.end()) it->second.children -= 1;
-  }
-  e->prefix_map.erase(key);
-  e->page_cached[page] = 0;
-  e->prefix_cached_pages -= 1;
-  if (--e->page_ref[page] == 0) e->free_pages.push_back(page);
-  return true;
+  return freed;
 }
 
 int alloc_slot(b200llm_engine* e, int capacity_tokens, const int32_t* ids, int n_ids, int32_t* out_slot,
@@ -667,8 +755,9 @@ int alloc_slot(b200llm_engine* e, int capacity_tokens, const int32_t* ids, int n
     e->prefix_lookup_tokens += n_ids;
   }
   const int fresh = need - shared;
-  while (static_cast<int64_t>(e->free_pages.size()) < fresh) {
-    if (!e->cfg.prefix_cache || !evict_one_cached_page(e)) {
+  if (static_cast<int64_t>(e->free_pages.size()) < fresh) {
+    if (e->cfg.prefix_cache) evict_cached_pages(e, fresh - static_cast<int>(e->free_pages.size()));
+    if (static_cast<int64_t>(e->free_pages.size()) < fresh) {
       for (int32_t p : pages) e->page_ref[p] -= 1;  // cached pages keep the cache's own reference
       pages.clear();
       return fail(kErrCapacity, "seq_alloc: KV pool exhausted");
@@ -751,6 +840,7 @@ namespace b200llm {
 void step_trace_set_gemm(unsigned long long*, unsigned int*, unsigned int);
 void step_trace_set_ops(unsigned long long*, unsigned int*, unsigned int);
 void step_trace_set_attention(unsigned long long*, unsigned int*, unsigned int);
+void step_trace_set_fused(unsigned long long*, unsigned int*, unsigned int);
 }  // namespace b200llm
 #endif
 
@@ -805,6 +895,9 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   if (const char* pair = std::getenv("B200LLM_PAIR")) e->pair_mode = std::atoi(pair);
   if (const char* env = std::getenv("B200LLM_SPLITS")) {  // "qkv,o,fc,proj" (0 keeps the pick)
     std::sscanf(env, "%d,%d,%d,%d", &e->tune_splits[0], &e->tune_splits[1], &e->tune_splits[2], &e->tune_splits[3]);
+  }
+  if (const char* env = std::getenv("B200LLM_FUSED_SPLITS")) {  // "o,p"
+    std::sscanf(env, "%d,%d", &e->tune_fused_splits[0], &e->tune_fused_splits[1]);
   }
   if (const char* env = std::getenv("B200LLM_ATTN_SPLITS")) e->tune_attn_splits = std::max(1, std::min(16, std::atoi(env)));
 #endif
@@ -1285,7 +1378,20 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   const int sms = e->sm_count;
   // auto: pick_split's rule, never more than 12 planes
   const int cap = e->cfg.decode_split_k == 0 ? 12 : std::min(e->cfg.decode_split_k, 32);
-  if (bucket <= 256 && cap > 1 && e->cfg.decode_reduce == 2) {
+  // automatic: the fused layer where it was measured faster (weights of a CTA resident: d <= 768);
+  // decode_reduce = 3 forces it wherever the kernels support the shape
+  if (bucket <= 64 && ln_gemm_supported(bucket, e->d, 3 * e->d) && e->d % 128 == 0 &&
+      (e->cfg.decode_reduce == 3 || (e->cfg.decode_reduce == 0 && ln_gemm_weights_resident(e->d)))) {
+    p.fused = true;
+    p.rs_o = gemm_redadd_pick_split(e->d, e->d, bucket, sms);
+    p.rs_p = gemm_redadd_pick_split(e->d, 4 * e->d, bucket, sms);
+    if (e->tune_fused_splits[0] > 0) p.rs_o = e->tune_fused_splits[0];
+    if (e->tune_fused_splits[1] > 0) p.rs_p = e->tune_fused_splits[1];
+    if (p.rs_o <= 0 || p.rs_p <= 0) p.fused = false;
+  }
+  if (p.fused) {
+    // no split-K planes anywhere in the step
+  } else if (bucket <= 256 && cap > 1 && e->cfg.decode_reduce == 2) {
     p.cl_qkv = pick_cluster(3 * e->d, e->d, sms);
     p.cl_o = pick_cluster(e->d, e->d, sms);
     p.cl_fc = pick_cluster(4 * e->d, e->d, sms);
@@ -1578,6 +1684,7 @@ int b200llm_debug_step_trace(int op, unsigned long long* out, int capacity) {
     b200llm::step_trace_set_gemm(buf, idx, cap);
     b200llm::step_trace_set_ops(buf, idx, cap);
     b200llm::step_trace_set_attention(buf, idx, cap);
+    b200llm::step_trace_set_fused(buf, idx, cap);
     return cudaDeviceSynchronize() == cudaSuccess ? 0 : 2;
   }
   unsigned int n = 0;
@@ -1763,6 +1870,46 @@ int b200llm_op_kv_scatter(const void* qkv, const int32_t* row_pos, const int32_t
   return kv_scatter(static_cast<const __nv_bfloat16*>(qkv), row_pos, row_slot, n_tok, n_head, page_table,
                     max_pages_per_seq, static_cast<__nv_bfloat16*>(k_pool), static_cast<__nv_bfloat16*>(v_pool),
                     reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_ln_gemm(const float* x, const float* gamma, const float* beta, float eps, const void* w,
+                       const float* bias, void* out, int32_t rows, int32_t features, int32_t d, int32_t ld_out,
+                       int32_t gelu, void* stream) {
+  LnGemmArgs a;
+  a.x = x;
+  a.gamma = gamma;
+  a.beta = beta;
+  a.eps = eps;
+  a.w = static_cast<const __nv_bfloat16*>(w);
+  a.bias = bias;
+  a.out = static_cast<__nv_bfloat16*>(out);
+  a.rows = rows;
+  a.d = d;
+  a.features = features;
+  a.ld_out = ld_out;
+  a.gelu = gelu;
+  return ln_gemm(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_gemm_redadd(const void* act, const void* w, const float* bias, float* x, int32_t rows,
+                           int32_t features, int32_t k, int32_t split, void* stream) {
+  GemmRedAddArgs a;
+  a.act = static_cast<const __nv_bfloat16*>(act);
+  a.w = static_cast<const __nv_bfloat16*>(w);
+  a.bias = bias;
+  a.x = x;
+  a.rows = rows;
+  a.features = features;
+  a.k = k;
+  int sms = 148;
+  if (split <= 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  a.split = split > 0 ? split : gemm_redadd_pick_split(features, k, rows, sms);
+  a.act_rows_alloc = rows <= 16 ? 16 : rows <= 32 ? 32 : 64;  // the caller's buffer holds the whole token tile
+  return gemm_redadd(a, reinterpret_cast<cudaStream_t>(stream));
 }
 
 size_t b200llm_decode_attention_scratch_floats(int32_t batch, int32_t n_head, int32_t n_splits) {

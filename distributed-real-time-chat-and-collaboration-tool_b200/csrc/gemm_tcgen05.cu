@@ -1566,6 +1566,10 @@ int gemm_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorM
   return get_tensor_map(ptr, rows, cols, box_rows, out);
 }
 
+int gemm_tensor_map_f32(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+  return get_tensor_map(ptr, rows, cols, box_rows, out, 4);
+}
+
 void gemm_clear_tensor_map_cache() {
   std::lock_guard<std::mutex> lock(map_mutex());
   map_cache().clear();

@@ -65,6 +65,8 @@ int gemm_argmax_groups(int features, int tokens);
 // Cached SWIZZLE_128B tensor map of a row-major bf16 [rows, cols] matrix with boxes of
 // [box_rows, 64 columns] (the operand layout every UMMA descriptor in this library assumes).
 int gemm_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out);
+// The same for an fp32 matrix: boxes of [box_rows, 32 columns] (a box row is again 128 bytes).
+int gemm_tensor_map_f32(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out);
 
 // Drop cached tensor maps (engine teardown / tests).
 void gemm_clear_tensor_map_cache();

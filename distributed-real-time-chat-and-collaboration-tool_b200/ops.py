@@ -144,3 +144,23 @@ def convert_transpose(src: torch.Tensor) -> torch.Tensor:
     dst = torch.empty(cols, rows, dtype=torch.bfloat16, device=src.device)
     check(lib.b200llm_op_convert_transpose(_ptr(src), _ptr(dst), rows, cols, _stream()))
     return dst
+
+
+def ln_gemm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None,
+            gelu: bool = False, eps: float = 1e-5) -> torch.Tensor:
+    """out = (gelu_new)(LayerNorm(x) @ w.T + bias), LayerNorm folded into the GEMM (decode, <= 64 rows)."""
+    rows, d = x.shape
+    features = w.shape[0]
+    out = torch.zeros(rows, features, dtype=torch.bfloat16, device=x.device)
+    check(lib.b200llm_op_ln_gemm(_ptr(x), _ptr(gamma), _ptr(beta), eps, _ptr(w), _ptr(bias), _ptr(out), rows,
+                                 features, d, features, int(gelu), _stream()))
+    return out
+
+
+def gemm_redadd(act: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, x: torch.Tensor, rows: int,
+                split: int = 0) -> torch.Tensor:
+    """x[:rows] += act[:rows] @ w.T + bias, K splits added into x in L2 (decode, <= 64 rows). `act` must
+    hold the whole 16 / 32 / 64-row token tile."""
+    check(lib.b200llm_op_gemm_redadd(_ptr(act), _ptr(w), _ptr(bias), _ptr(x), rows, w.shape[0], w.shape[1],
+                                     split, _stream()))
+    return x

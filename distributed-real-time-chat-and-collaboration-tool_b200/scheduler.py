@@ -82,7 +82,7 @@ class EngineWorker(threading.Thread):
     def submit(self, ids: Sequence[int], sampling: SamplingParams) -> Future:
         fut: Future = Future()
         req = _Request(list(ids), sampling, fut)
-        fut.request = req  # lets the caller cancel (Router.generate on timeout)
+        fut.cancel_request = lambda: setattr(req, "cancelled", True)  # Router.generate on timeout
         with self._lock:
             self._inflight_tokens += len(req.ids) + sampling.max_new_tokens
         self.inbox.put(req)
@@ -92,9 +92,17 @@ class EngineWorker(threading.Thread):
     def cancel(fut: Future) -> None:
         """The caller no longer wants the result: a waiting request is dropped at the next
         admission, an active one is stopped on the device and its slot freed at the next retire."""
-        req = getattr(fut, "request", None)
-        if req is not None:
-            req.cancelled = True
+        stop = getattr(fut, "cancel_request", None)
+        if stop is not None:
+            stop()
+
+    def snapshot(self) -> dict:
+        """Counters for the stream benchmark's report (also served across the process boundary by
+        remote_worker.RemoteEngineWorker)."""
+        cache = self.engine.prefix_cache_stats() if hasattr(self.engine, "prefix_cache_stats") else {}
+        return {"phase_s": {k: round(v, 3) for k, v in self.phase_s.items()}, "iterations": self.iterations,
+                "completed": self.completed, "cancelled": self.cancelled, "generated_tokens": self.generated_tokens,
+                "prefix_hit_tokens": self.prefix_hit_tokens, "prefix_cache": cache}
 
     @property
     def healthy(self) -> bool:
@@ -301,7 +309,7 @@ class Router:
         if not workers:
             raise ValueError("Router needs at least one worker")
         self.workers = list(workers)
-        for w in self.workers:
+        for w in self.workers:  # thread workers start running; process workers finish coming up
             if not w.is_alive():
                 w.start()
 

@@ -46,8 +46,14 @@ class LLMServiceStub:
 
 def build_local_model(model: str = "small", gpus: int = 1, *, max_seqs: int = 64, max_seq_len: int = 1024,
                       max_new_tokens: int = 256, weights: str | None = None, vocab_json: str | None = None,
-                      merges_txt: str | None = None, seed: int = 0):
-    """Engines (one per GPU) + workers + router + tokenizer -> LocalGenerativeModel."""
+                      merges_txt: str | None = None, seed: int = 0, prefix_cache: bool = True,
+                      process_per_gpu: bool | None = None):
+    """Engines (one per GPU) + workers + router + tokenizer -> LocalGenerativeModel.
+
+    process_per_gpu: every GPU's engine and scheduler loop in a process of its own behind the router
+    (remote_worker.py) instead of a thread of this process. Default: threads for one GPU, processes
+    for several (with threads the workers and the gRPC handlers share one interpreter lock; measured
+    in profiles/r2_stream_*)."""
     from .engine import MODEL_SHAPES, Engine
     from .local_model import LocalGenerativeModel
     from .scheduler import EngineWorker, Router
@@ -55,12 +61,20 @@ def build_local_model(model: str = "small", gpus: int = 1, *, max_seqs: int = 64
     from .weights import blob_from_safetensors, synthetic_blob
 
     shape = MODEL_SHAPES[model]
-    blob = blob_from_safetensors(shape, weights) if weights else synthetic_blob(shape, seed=seed)
+    engine_kwargs = dict(max_seqs=max_seqs, max_seq_len=min(max_seq_len, shape.n_positions), max_batch_tokens=8192,
+                         max_new_tokens=max_new_tokens, prefix_cache=prefix_cache)
+    if process_per_gpu is None:
+        process_per_gpu = gpus > 1
     workers = []
-    for dev in range(gpus):
-        eng = Engine(shape, blob, device=dev, max_seqs=max_seqs, max_seq_len=min(max_seq_len, shape.n_positions),
-                     max_batch_tokens=8192, max_new_tokens=max_new_tokens, prefix_cache=True)
-        workers.append(EngineWorker(eng, name=f"b200llm-gpu{dev}"))
+    if process_per_gpu:
+        from .remote_worker import RemoteEngineWorker
+
+        workers = [RemoteEngineWorker(dev, model, engine_kwargs, weights=weights, seed=seed) for dev in range(gpus)]
+    else:
+        blob = blob_from_safetensors(shape, weights) if weights else synthetic_blob(shape, seed=seed)
+        for dev in range(gpus):
+            eng = Engine(shape, blob, device=dev, **engine_kwargs)
+            workers.append(EngineWorker(eng, name=f"b200llm-gpu{dev}"))
     router = Router(workers)
     return LocalGenerativeModel(router, load_tokenizer(vocab_json, merges_txt),
                                 max_prompt_tokens=min(max_seq_len, shape.n_positions) - max_new_tokens - 1)

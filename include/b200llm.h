@@ -78,10 +78,17 @@ typedef struct b200llm_config {
   int32_t decode_split_k;   /* 0 = auto; 1 = off; >1 = split-K factor cap for decode GEMMs */
   int32_t keep_logits;      /* 1 = decode steps also store the fp32 logits (greedy rows do not
                                need them: the LM-head GEMM fuses the argmax)                 */
-  int32_t decode_reduce;    /* how decode GEMMs combine their K splits: 0/1 = fp32 partial planes in L2
-                               reduced by the consumer kernel (default; measured faster);
+  int32_t decode_reduce;    /* how decode GEMMs combine their K splits:
+                               0 = automatic: the fused path (3) for up to 64 rows when d_model <= 768
+                                   (where it was measured faster), else planes (1);
+                               1 = fp32 partial planes in L2 reduced in a fixed order by the consumer
+                                   kernel: 8 kernels per layer, bit-reproducible;
                                2 = inside the GEMM, over a thread-block cluster through distributed
-                               shared memory (fewer kernels, but DSMEM moves ~20 B/clk per SM)    */
+                                   shared memory (DSMEM moves ~20 B/clk per SM: measured slower);
+                               3 = fused (<= 64 rows): LayerNorm inside the QKV / MLP-up GEMM, out-proj /
+                                   MLP-down add their splits into the residual stream in L2 (TMA
+                                   reduce-add): 5 kernels per layer; the fp32 additions of one element
+                                   arrive in no fixed order (last-bit differences run to run)      */
   int32_t prefix_cache;     /* 1 = shared-prefix KV reuse: the full 16-token pages of every prompt
                                stay in a ref-counted, LRU-evicted cache keyed by their token chain;
                                b200llm_seq_alloc_with_prefix maps a new prompt's longest cached page
@@ -228,6 +235,19 @@ int64_t b200llm_kernel_launches(const b200llm_engine* engine);
 int b200llm_op_gemm(const void* act_dev, const void* w_dev, const float* bias_dev, void* out_dev,
                     int32_t tokens, int32_t features, int32_t k, int32_t ld_out, int32_t epilogue,
                     int32_t split_k, int32_t orientation, void* stream);
+
+/* out_bf16[row, f] = epilogue( LayerNorm(x_f32[row, :]) . w[f, :] + bias[f] ), epilogue = identity or
+ * gelu_new: LayerNorm folded into the consuming GEMM's operand path (the decode step's ln_1 + c_attn
+ * and ln_2 + c_fc + act; modeling_gpt2.py:273,185 / :304,239-240). rows <= 64, d % 64 == 0. */
+int b200llm_op_ln_gemm(const float* x_dev, const float* gamma_dev, const float* beta_dev, float eps,
+                       const void* w_dev, const float* bias_dev, void* out_bf16_dev, int32_t rows,
+                       int32_t features, int32_t d, int32_t ld_out, int32_t gelu, void* stream);
+/* x_f32[row, f] += act[row, :] . w[f, :] + bias[f], split-K over `split` CTAs per 128 features whose
+ * partial tiles are added into x in L2 by TMA reduce-add (the decode step's attention out-proj and
+ * MLP down-proj with their residual adds, modeling_gpt2.py:223,282 / :241,307). split 0 = automatic.
+ * act must be backed by 16 / 32 / 64 rows (the token tile that holds `rows`). */
+int b200llm_op_gemm_redadd(const void* act_dev, const void* w_dev, const float* bias_dev, float* x_dev,
+                           int32_t rows, int32_t features, int32_t k, int32_t split, void* stream);
 
 /* out_bf16 = LayerNorm(x_f32) ; optional fused "x += bias + sum partials" first.
  * modeling_gpt2.py:252-254 (nn.LayerNorm, eps inside sqrt, biased variance). */

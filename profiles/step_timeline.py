@@ -18,7 +18,8 @@ E = importlib.import_module(f"{PKG}.engine")
 W = importlib.import_module(f"{PKG}.weights")
 L = importlib.import_module(f"{PKG}._lib")
 TAGS = {1: "layernorm", 2: "gelu_reduce", 3: "select", 4: "embed", 5: "attention", 100: "gemm bias", 101: "gemm gelu",
-        102: "gemm resid", 103: "gemm f32", 104: "gemm partial", 105: "gemm lm-head+argmax"}
+        102: "gemm resid", 103: "gemm f32", 104: "gemm partial", 105: "gemm lm-head+argmax",
+        300: "ln+gemm (qkv)", 301: "ln+gemm+gelu (mlp up)", 310: "gemm reduce-add"}
 workload = sys.argv[1] if len(sys.argv) > 1 else "smart_reply_b64"
 model, B, T, N = WORKLOADS[workload]
 shape = E.MODEL_SHAPES[model]
@@ -58,8 +59,12 @@ for i, (b, e, tag) in enumerate(step):
     a[2] += (nxt - b) / 1e3        # entry -> next kernel's entry (pipeline pitch)
     if 8 <= i < 26 or i >= len(step) - 4:
         print(f"{i:3d} {name:22s} entry {(b - base) / 1e3:8.2f} us  exit {(e - base) / 1e3:8.2f} us  dur {(e - b) / 1e3:6.2f}")
-        if name.startswith("gemm"):
+        if name.startswith("gemm") and "reduce-add" not in name:
             print("      " + "  ".join(f"{MARK_NAMES[j]} {(m - base) / 1e3:.2f}" for j, m in enumerate(marks[i]) if m > 0))
+        if name.startswith("ln+gemm"):
+            names = {3: "dep ok", 4: "rows in registers", 5: "B operand written", 8: "mma sees B", 9: "mma issued",
+                     6: "epi sees acc", 7: "stores done"}
+            print("      " + "  ".join(f"{names[j]} {(marks[i][j] - base) / 1e3:.2f}" for j in (3, 4, 5, 8, 9, 6, 7) if marks[i][j] > 0))
 print("per kernel class in one step: count, sum CTA0 duration us, sum entry-to-next-entry us")
 for k, a in sorted(agg.items(), key=lambda kv: -kv[1][2]):
     print(f"  {k:22s} {a[0]:4d} {a[1]:9.1f} {a[2]:9.1f}")

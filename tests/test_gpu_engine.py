@@ -59,8 +59,8 @@ def test_tiny_model_all_position_logits(cuda):
     eng.close()
 
 
-@pytest.mark.parametrize("graphs,pdl,split,reduce", [(False, False, 1, 0), (True, False, 0, 0), (True, True, 0, 0),
-                                                     (True, True, 0, 2)])
+@pytest.mark.parametrize("graphs,pdl,split,reduce", [(False, False, 1, 1), (True, False, 0, 1), (True, True, 0, 1),
+                                                     (True, True, 0, 2), (False, False, 0, 3), (True, True, 0, 0)])
 def test_small_greedy_generation_margin_aware(cuda, small_weights, graphs, pdl, split, reduce):
     B, T, N = 8, 64, 32
     ids = O.synthetic_prompts(B, T)

@@ -395,3 +395,61 @@ def test_lm_head_with_fused_argmax(ops, cuda, tokens, vocab, k):
         assert (got != eos).all()
         if store:
             assert (logits - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("rows,d,features,gelu", [
+    (64, 768, 2304, False),    # GPT-2 small ln_1 + c_attn at the headline batch
+    (64, 768, 3072, True),     # ln_2 + c_fc + gelu_new
+    (16, 1024, 3072, False),   # medium: the weight ring recycles (16 k-blocks, 12 stages)
+    (32, 1280, 5120, True),    # large
+    (1, 768, 2304, False), (13, 128, 384, True), (50, 256, 1024, True),
+])
+def test_layernorm_folded_into_the_gemm(ops, cuda, rows, d, features, gelu):
+    """ln_gemm_kernel: out = (gelu_new)(LayerNorm(x) W^T + b) with the LayerNorm computed inside the
+    GEMM kernel (fp32 statistics) and handed to the tensor core through shared memory. Reference:
+    fp32 layer_norm -> bf16 (the operand precision) -> fp32 matmul."""
+    g = torch.Generator(device="cpu").manual_seed(rows + d)
+    x = (torch.randn(rows, d, generator=g) * 3.0 + 1.5).to(cuda)     # non-zero mean, std 3
+    gamma = (1.0 + 0.1 * torch.randn(d, generator=g)).to(cuda)
+    beta = (0.1 * torch.randn(d, generator=g)).to(cuda)
+    w = (torch.randn(features, d, generator=g) * 0.05).to(torch.bfloat16).to(cuda)
+    bias = (torch.randn(features, generator=g) * 0.1).to(cuda)
+    out = ops.ln_gemm(x, gamma, beta, w, bias, gelu=gelu)
+    torch.cuda.synchronize()
+    h = torch.nn.functional.layer_norm(x, (d,), gamma, beta, 1e-5).to(torch.bfloat16).float()
+    ref = h @ w.float().t() + bias
+    if gelu:
+        ref = gelu_new(ref)
+    err = (out.float() - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    # bf16 output rounding + an occasional 1-ulp difference of a normalised operand element
+    assert err <= 4e-3 * scale + 2 ** -8 * scale, (err, scale)
+
+
+@pytest.mark.parametrize("rows,features,k,split", [
+    (64, 768, 768, 0), (64, 768, 3072, 0),      # GPT-2 small out-proj / MLP-down, automatic split
+    (64, 768, 3072, 6), (64, 768, 768, 2),
+    (16, 1024, 4096, 0), (32, 1280, 5120, 0),   # medium / large
+    (3, 768, 768, 12), (40, 256, 1024, 4), (64, 128, 512, 8),
+])
+def test_split_k_gemm_reduce_added_into_the_residual_stream(ops, cuda, rows, features, k, split):
+    """gemm_redadd_kernel: x += act W^T + b with the K splits added into x in L2 by TMA reduce-add.
+    Rows of x beyond the live batch must stay untouched."""
+    g = torch.Generator(device="cpu").manual_seed(features + k)
+    tile = 16 if rows <= 16 else 32 if rows <= 32 else 64
+    act = (torch.randn(tile, k, generator=g) * 0.5).to(torch.bfloat16).to(cuda)
+    w = (torch.randn(features, k, generator=g) * 0.05).to(torch.bfloat16).to(cuda)
+    bias = (torch.randn(features, generator=g) * 0.1).to(cuda)
+    x0 = torch.randn(tile, features, generator=g).to(cuda)
+    x = x0.clone()
+    ops.gemm_redadd(act, w, bias, x, rows, split)
+    torch.cuda.synchronize()
+    ref = x0[:rows] + act[:rows].float() @ w.float().t() + bias
+    err = (x[:rows] - ref).abs().max().item()
+    assert err <= 2e-3 * ref.abs().max().item(), err
+    assert torch.equal(x[rows:], x0[rows:]), "rows beyond the batch were modified"
+    # twice more: the additions accumulate
+    ops.gemm_redadd(act, w, None, x, rows, split)
+    torch.cuda.synchronize()
+    ref2 = ref + act[:rows].float() @ w.float().t()
+    assert (x[:rows] - ref2).abs().max().item() <= 3e-3 * ref2.abs().max().item()

@@ -185,3 +185,47 @@ def test_a_failing_replica_is_bypassed_and_reprobed():
     assert len(r.generate([99], sp, timeout=5).tokens) == 4
     assert wb.healthy and wb.completed == 1
     r.shutdown()
+
+
+def test_process_per_gpu_workers_behind_the_router():
+    """remote_worker.RemoteEngineWorker: the EngineWorker loop runs in a child process (one per
+    GPU), the Router talks to it over a pipe. Same results as in-process workers, requests are
+    sharded, cancel and a dying process are handled."""
+    import time
+    from concurrent.futures import TimeoutError as FutureTimeout
+
+    rw = pkg("remote_worker")
+    kw = dict(max_seqs=4, max_seq_len=4096, max_new_tokens=600, step_sleep=0.001)
+    workers = [rw.RemoteEngineWorker(d, "small", kw, engine_factory="fakes:FakeEngine", decode_burst=4) for d in (0, 1)]
+    r = sched.Router(workers)
+    assert all(w.is_alive() for w in workers)
+    prompts = [[i, 2 * i + 1] for i in range(16)]
+    sp = SamplingParams(max_new_tokens=6)
+    futs = [r.submit(p, sp) for p in prompts]
+    got = [f.result(timeout=20).tokens for f in futs]
+    one = _router(FakeEngine(max_seqs=4))
+    assert got == [one.generate(p, sp, timeout=10).tokens for p in prompts]
+    one.shutdown()
+    snaps = [w.snapshot() for w in workers]
+    assert all(s["completed"] > 0 for s in snaps) and sum(s["completed"] for s in snaps) == 16
+    assert all(w.inflight_tokens == 0 for w in workers)
+    # a caller that gives up: the cancel crosses the pipe and the child frees the slot
+    with pytest.raises(FutureTimeout):
+        r.generate([1, 2, 3], SamplingParams(max_new_tokens=600), timeout=0.1)
+    deadline = time.time() + 5
+    while sum(w.snapshot()["cancelled"] for w in workers) == 0 and time.time() < deadline:
+        time.sleep(0.02)
+    assert sum(w.snapshot()["cancelled"] for w in workers) == 1
+    with pytest.raises(ValueError):  # a bad request is reported as such and does not mark the replica unhealthy
+        r.generate([1] * 5000, sp, timeout=5)
+    assert all(w.healthy for w in workers)
+    # a worker process that dies fails its requests and leaves the rotation
+    workers[0].proc.terminate()
+    workers[0].proc.join(5)
+    time.sleep(0.2)
+    assert not workers[0].healthy
+    assert [len(r.generate(p, sp, timeout=10).tokens) for p in prompts[:6]] == [6] * 6
+    assert workers[1].snapshot()["completed"] >= 6
+    r.shutdown()
+    for w in workers:
+        w.join(5)
