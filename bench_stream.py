@@ -119,6 +119,39 @@ def client_main(args):
     print(json.dumps({"lat": lat, "t_first": t_first, "t_last": t_last}))
 
 
+def growing_channels(pb, server_mod, port: int, channels: int, first: int, last: int) -> dict:
+    """Summaries of growing channels (the call pattern of reference server/raft_node.py:2032-2084: the
+    Raft node sends the channel's recent messages, in order, on every summarise request). Each of
+    `channels` callers owns one channel, appends one message at a time and asks for a summary after
+    each, so consecutive prompts of a channel share everything but their last message."""
+    import grpc
+
+    rng = np.random.default_rng(7)
+    lat: list[float] = []
+    lock = threading.Lock()
+
+    def one_channel(c: int):
+        r = np.random.default_rng(1000 + c)
+        msgs = [pb.Message(sender=USERS[int(r.integers(len(USERS)))], content=f"[ch{c}] " + SENTENCES[int(r.integers(len(SENTENCES)))])
+                for _ in range(last)]
+        with grpc.insecure_channel(f"127.0.0.1:{port}") as ch:
+            stub = server_mod.LLMServiceStub(ch)
+            for n in range(first, last + 1):
+                req = pb.SummarizeRequest(request_id=f"{c}-{n}", messages=msgs[:n], max_length=200)
+                t0 = time.perf_counter()
+                stub.SummarizeConversation(req, timeout=60)
+                with lock:
+                    lat.append((time.perf_counter() - t0) * 1e3)
+
+    del rng
+    t0 = time.perf_counter()
+    with futures.ThreadPoolExecutor(max_workers=channels) as pool:
+        list(pool.map(one_channel, range(channels)))
+    wall = time.perf_counter() - t0
+    return {"channels": channels, "messages_per_channel": [first, last], "requests": len(lat), "wall_s": wall,
+            "p50_ms": float(np.percentile(lat, 50)), "p95_ms": float(np.percentile(lat, 95))}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -127,6 +160,9 @@ def main():
     ap.add_argument("--clients", type=int, default=64, help="concurrent callers (threads over all caller processes)")
     ap.add_argument("--client-procs", type=int, default=4, help="caller processes (0 = callers share this process)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="also time this many requests per RPC on the host CPU")
+    ap.add_argument("--scenario", default="mixed", choices=["mixed", "growing_channel"],
+                    help="mixed: BASELINE configs[4]; growing_channel: consecutive summaries of growing channels")
+    ap.add_argument("--channels", type=int, default=8)
     ap.add_argument("--process-per-gpu", type=int, default=-1,
                     help="1 = one worker process per GPU behind the router, 0 = worker threads, -1 = server default")
     ap.add_argument("--prefix-cache", type=int, default=1, help="shared-prefix KV reuse in the engines (1 = as served)")
@@ -160,6 +196,24 @@ def main():
     server.start()
 
     reqs = make_requests(pb, args.requests)
+    if args.scenario == "growing_channel":
+        with grpc.insecure_channel(f"127.0.0.1:{port}") as ch:
+            stub = server_mod.LLMServiceStub(ch)
+            for rpc, req in reqs[:8]:
+                getattr(stub, rpc)(req, timeout=60)
+        base = [w.snapshot()["prefix_cache"] or {"lookup_tokens": 0, "hit_tokens": 0} for w in model.inner.router.workers]
+        res = growing_channels(pb, server_mod, port, args.channels, 3, 12)
+        server.stop(0)
+        cache = [w.snapshot()["prefix_cache"] or {"lookup_tokens": 0, "hit_tokens": 0} for w in model.inner.router.workers]
+        model.inner.router.shutdown()
+        look = sum(c["lookup_tokens"] for c in cache) - sum(c["lookup_tokens"] for c in base)
+        hit = sum(c["hit_tokens"] for c in cache) - sum(c["hit_tokens"] for c in base)
+        print(json.dumps({"metric": "SummarizeConversation latency for growing channels (shared-prefix KV reuse)",
+                          "n_gpus": args.gpus, "prefix_cache": {"enabled": bool(args.prefix_cache), "lookup_tokens": look,
+                                                                 "hit_tokens": hit, "hit_rate": hit / max(1, look)},
+                          **res, "new_tokens": 32,
+                          "tokenizer": "byte-level GPT-2 ids: prompts of 350-900 tokens", "data": "synthetic conversations, random-init GPT-2 small"}))
+        return
     rng = np.random.default_rng(99)
     arrivals = np.cumsum(rng.exponential(1.0 / args.rate, size=len(reqs))) if args.rate > 0 else np.zeros(len(reqs))
     with grpc.insecure_channel(f"127.0.0.1:{port}") as ch:

@@ -239,10 +239,15 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
 
       mbar_wait(&sm.s_bar, static_cast<uint32_t>(t) & 1u);
       tc_fence_after();
+      // 32-key chunks of the tile that at least one row of this warp can see (lim grows with the
+      // row, so lane 31 has the warp's largest): on a diagonal tile warp w sees w + 1 of the 4 chunks,
+      // the others are all-masked and cost neither TMEM reads nor exponentials
+      const int warp_lim = need_mask ? __shfl_sync(0xffffffffu, lim, 31) : kTK;
       // ---- softmax of this thread's row over the tile's 128 keys (two passes over TMEM) ----
       float mx = -INFINITY;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
+        if (c * 32 >= warp_lim) break;  // warp-uniform
         uint32_t r[32];
         tmem_ld_32x32(tmem_s + c * 32, r);
         tmem_ld_wait();
@@ -261,10 +266,19 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
       float row_sum = 0.f;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
+        uint32_t pk[16];
+        const uint32_t blk0 = p_row + static_cast<uint32_t>((c >> 1) * kTileBytes);
+        if (c * 32 >= warp_lim) {  // warp-uniform: nothing visible in this chunk, P = 0
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const uint32_t chunk = static_cast<uint32_t>((c & 1) * 4 + g) ^ static_cast<uint32_t>(tid & 7);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(blk0 + (chunk << 4)), "r"(0u) : "memory");
+          }
+          continue;
+        }
         uint32_t r[32];
         tmem_ld_32x32(tmem_s + c * 32, r);
         tmem_ld_wait();
-        uint32_t pk[16];
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
           float s0 = __uint_as_float(r[j]), s1 = __uint_as_float(r[j + 1]);

@@ -332,6 +332,7 @@ gemm_redadd_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
         tma_load_2d(ring + i * kStage, &map_w, full_bar, (kb0 + i) * kKB, m_blk * kM, kEvictFirst);
       }
       pdl_wait();
+      B200_FTRACE(3);
       for (int i = 0; i < a.kb_per_split; ++i) {
         tma_load_2d(ring + i * kStage + kABytes, &map_act, full_bar, (kb0 + i) * kKB, 0, kEvictLast);
       }
@@ -339,6 +340,7 @@ gemm_redadd_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
   } else if (warp == 1) {
     constexpr uint32_t idesc = umma_idesc_bf16(kM, NB);
     mbar_wait(full_bar, 0);
+    if (lane == 0) B200_FTRACE(4);
     tc_fence_after();
     if (elect_one()) {
       for (int i = 0; i < a.kb_per_split; ++i) {
@@ -361,6 +363,7 @@ gemm_redadd_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
     const float bias = (split == 0 && a.bias != nullptr && feature < a.features) ? __ldg(a.bias + feature) : 0.f;
     pdl_wait();  // x must not be touched before the upstream grid (its last reader) has finished
     mbar_wait(tmem_full, 0);  // every MMA has retired: the operand ring is free to be overwritten
+    if (threadIdx.x == 128) B200_FTRACE(6);
     tc_fence_after();
     uint8_t* box = ring + q * (NB * 128);  // this warp's 32 features: rows = tokens, 128 B per row
     constexpr int kChunk = NB >= 32 ? 32 : 16;
@@ -392,6 +395,7 @@ gemm_redadd_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
     tc_fence_before();
     fence_proxy_async();
     __syncwarp();
+    if (threadIdx.x == 128) B200_FTRACE(5);
     if (lane == 0) {  // each warp hands its own box of 32 features to the TMA unit as soon as it is staged
       const int f0 = m_blk * kM + q * 32;
       if (f0 < a.features) {
@@ -403,6 +407,7 @@ gemm_redadd_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // complete before the CTA exits
+      if (threadIdx.x == 128) B200_FTRACE(7);
     }
   }
   __syncthreads();

@@ -267,6 +267,8 @@ struct b200llm_engine {
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
   int tune_splits[4] = {0, 0, 0, 0};  // tune build: split-K overrides for qkv, o, fc, proj
   int tune_attn_splits = 0;           // tune build: KV split override
+  int prefill_attn_mode = -1;         // -1 auto, 0 tcgen05 always, 1 mma.sync always (tune build: B200LLM_PREFILL_ATTN)
+  int tune_fused_qkv = -1;            // tune build: 0 / 1 force ln_1 + c_attn as LayerNorm + planes / as the fused kernel
   int tune_fused_splits[2] = {0, 0};  // tune build: K splits of the fused path's out-proj / MLP-down
 };
 
@@ -345,7 +347,10 @@ struct StepPlan {
   // decode, <= 64 rows: LayerNorm folded into the QKV / MLP-up GEMMs, out-proj / MLP-down add
   // their K splits into x in L2 (decode_fused.cu): 5 kernels per layer instead of 8
   bool fused = false;
+  bool fused_qkv = true;   // false: ln_1 and c_attn stay LayerNorm + split-K planes (light CTAs: the
+                           // attention kernel of the same layer can start beside them and prefetch its KV)
   int rs_o = 1, rs_p = 1;  // K splits of the two reduce-add GEMMs
+  int max_keys = 0;            // prefill: most keys (cached prefix + own rows) any sequence of the call has
   bool paged_prefill = false;  // some prefill rows are prompt suffixes behind a cached prefix (prefix_dev is valid)
 };
 
@@ -438,10 +443,25 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       lg.pdl = pdl;
       const bool skip_lg = skip_gemm || (e->skip_mask & kSkipLnGemm) != 0;
       const bool skip_ra = skip_gemm || (e->skip_mask & kSkipRedAdd) != 0;
-      if (!skip_lg) B200_PROPAGATE(count(e, ln_gemm(lg, e->stream)));
+      const bool qkv_planes = !p.fused_qkv && p.split_qkv > 1;
+      if (p.fused_qkv) {
+        if (!skip_lg) B200_PROPAGATE(count(e, ln_gemm(lg, e->stream)));
+      } else {
+        B200_PROPAGATE(ln(e, nullptr, 0, rows, nullptr, w.ln1_g, w.ln1_b, nullptr, rows, pdl));
+        if (qkv_planes) {
+          B200_PROPAGATE(gemm(e, e->h, w.w_qkv, nullptr, e->partials, rows, 3 * d, d, 3 * d, kEpiPartialF32,
+                              p.split_qkv, pdl));
+        } else {
+          B200_PROPAGATE(gemm(e, e->h, w.w_qkv, w.b_qkv, e->qkv, rows, 3 * d, d, 3 * d, kEpiBiasBf16, 1, pdl));
+        }
+      }
       // attention (:186-222) over the paged cache
       DecodeAttnArgs a = {};
-      a.qkv = e->qkv;
+      a.qkv = qkv_planes ? nullptr : e->qkv;
+      a.qkv_partials = qkv_planes ? e->partials : nullptr;
+      a.n_qkv_partials = qkv_planes ? p.split_qkv : 0;
+      a.partial_rows = rows;
+      a.qkv_bias = w.b_qkv;
       a.active_slots = e->active_dev;
       a.seq_len = e->seq_len;
       a.finished = e->finished;
@@ -540,6 +560,24 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       // Prefill: every query attends over its sequence's cached prefix (shared-prefix reuse; read
       // from the pages) followed by the rows of this call (read from qkv); the CTA on the diagonal
       // writes its K/V tile into the pages, so there is no scatter pass.
+      // Sequences of at most one 128-key tile (prompts of <= 128 tokens: every CTA would be set-up,
+      // one tile, tear-down) stay on the mma.sync kernel with 64-row CTAs, measured faster there
+      // (64 x 128-token prompts: 25.9 vs 33.3 us per layer); everything longer runs on tcgen05
+      // (16 x 1024 tokens: 147 vs 200 us per layer).
+      const bool tc = e->prefill_attn_mode == 0 || (e->prefill_attn_mode < 0 && p.max_keys > 128);
+      if (!tc && !p.paged_prefill) {
+        PrefillCache pc;
+        pc.slots = e->slots_dev;
+        pc.page_table = e->page_table;
+        pc.max_pages_per_seq = e->max_pages_per_seq;
+        pc.k_pool = kp;
+        pc.v_pool = vp;
+        B200_PROPAGATE(count(e, prefill_attention(e->qkv, e->cu_dev, p.batch, p.max_len, e->H, e->attn, e->stream, &pc)));
+      } else {
+      if (!tc) {  // short prompts behind a cached prefix: rows to the pages first, then every key from the pages
+        B200_PROPAGATE(count(e, kv_scatter(e->qkv, e->row_pos, e->row_slot, rows, e->H, e->page_table,
+                                           e->max_pages_per_seq, kp, vp, e->stream)));
+      }
       PagedPrefillArgs pa;
       pa.qkv = e->qkv;
       pa.cu_seqlens = e->cu_dev;
@@ -555,7 +593,12 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       pa.out = e->attn;
       pa.qkv_rows = e->max_rows;
       pa.n_pages = static_cast<int>(e->n_pages);
-      B200_PROPAGATE(count(e, prefill_attention_tc(pa, e->stream)));
+      if (tc) {
+        B200_PROPAGATE(count(e, prefill_attention_tc(pa, e->stream)));
+      } else {
+        B200_PROPAGATE(count(e, prefill_attention_paged(pa, e->stream)));
+      }
+      }
     }
     // attn c_proj + residual (:223, :282)
     if (p.decode && p.cl_o > 1) {
@@ -896,6 +939,8 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   if (const char* env = std::getenv("B200LLM_SPLITS")) {  // "qkv,o,fc,proj" (0 keeps the pick)
     std::sscanf(env, "%d,%d,%d,%d", &e->tune_splits[0], &e->tune_splits[1], &e->tune_splits[2], &e->tune_splits[3]);
   }
+  if (const char* env = std::getenv("B200LLM_PREFILL_ATTN")) e->prefill_attn_mode = std::atoi(env);
+  if (const char* env = std::getenv("B200LLM_FUSED_QKV")) e->tune_fused_qkv = std::atoi(env);
   if (const char* env = std::getenv("B200LLM_FUSED_SPLITS")) {  // "o,p"
     std::sscanf(env, "%d,%d", &e->tune_fused_splits[0], &e->tune_fused_splits[1]);
   }
@@ -1181,7 +1226,7 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   // prefix cache -- only the tokens behind them. `cu` always describes the full prompts.
   std::vector<int32_t> prefix(batch, 0), cu_rows(batch + 1, 0);
   bool any_prefix = false;
-  int max_len = 0;
+  int max_len = 0, max_keys = 0;
   for (int b = 0; b < batch; ++b) {
     const int len = cu[b + 1] - cu[b];
     B200_CHECK_ARG(len > 0, "prefill: empty prompt");
@@ -1200,6 +1245,7 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
     }
     cu_rows[b + 1] = cu_rows[b] + len - prefix[b];
     max_len = std::max(max_len, len - prefix[b]);
+    max_keys = std::max(max_keys, len);
   }
   const int n_tok = cu_rows[batch];
   if (n_tok > e->cfg.max_batch_tokens) {
@@ -1299,6 +1345,7 @@ int b200llm_prefill(b200llm_engine* e, const int32_t* ids, int32_t ids_on_device
   p.decode = false;
   p.batch = batch;
   p.max_len = max_len;
+  p.max_keys = max_keys;
   p.logits_all = logits_all_dev;
   p.store_logits = true;
   p.paged_prefill = any_prefix;
@@ -1413,6 +1460,21 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     while (splits < 16 && ctas * splits < 4 * sms && max_ctx / (splits * 2) >= 64) splits *= 2;
     p.attn_splits = splits;
     if (e->tune_attn_splits > 0) p.attn_splits = e->tune_attn_splits;
+  }
+  if (p.fused) {
+    // ln_1 + c_attn as one kernel holds whole SMs (its CTAs keep their 196 KB weight tile resident), so
+    // the attention CTAs of the layer can only start early -- and prefetch their KV rows under the
+    // projection -- on the SMs it leaves free. When they all fit there the fused kernel wins (16 rows:
+    // 265 vs 276 us per step); with 64 rows x 12 heads they do not, and LayerNorm + split-K planes
+    // (light CTAs) is the faster producer for the attention kernel (340 vs 347 us).
+    {
+      const int qkv_ctas = ((3 * e->d + 127) / 128) * ((bucket + 15) / 16);
+      const int early_slots = (sms - qkv_ctas) * 6;  // six attention CTAs share an SM
+      p.fused_qkv = bucket * e->H * p.attn_splits <= early_slots;
+    }
+    if (e->tune_fused_qkv >= 0) p.fused_qkv = e->tune_fused_qkv != 0;
+    if (!p.fused_qkv && cap > 1) p.split_qkv = pick_split(3 * e->d, e->d, sms, cap);
+    if (e->tune_splits[0] > 0) p.split_qkv = e->tune_splits[0];
   }
 
   if (!e->cfg.use_cuda_graphs) {

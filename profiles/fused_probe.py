@@ -34,7 +34,7 @@ steps = min(N - 1, 63)
 
 
 def run(env: dict, reduce: int) -> float:
-    for k in ("B200LLM_SKIP", "B200LLM_FUSED_SPLITS", "B200LLM_SPLITS"):
+    for k in ("B200LLM_SKIP", "B200LLM_FUSED_SPLITS", "B200LLM_SPLITS", "B200LLM_FUSED_QKV"):
         os.environ.pop(k, None)
     os.environ.update(env)
     eng = E.Engine(shape, blob, max_seqs=B, max_seq_len=T + N, max_batch_tokens=min(B * T, 16384), max_new_tokens=N,
@@ -57,9 +57,13 @@ def run(env: dict, reduce: int) -> float:
     return best
 
 
-cases = [({}, 1), ({}, 3), ({"B200LLM_SKIP": "64"}, 3), ({"B200LLM_SKIP": "128"}, 3), ({"B200LLM_SKIP": "192"}, 3),
-         ({"B200LLM_SKIP": "4"}, 3), ({"B200LLM_SKIP": "196"}, 3)]
+cases = [({}, 1), ({}, 3)]
 for sp in sys.argv[2:]:
-    cases.append(({"B200LLM_FUSED_SPLITS": sp}, 3))
+    if "=" in sp:
+        cases.append((dict(kv.split("=") for kv in sp.split(";")), 3))
+    elif sp == "ablate":
+        cases += [({"B200LLM_SKIP": m}, 3) for m in ("64", "128", "192", "4", "196")]
+    else:
+        cases.append(({"B200LLM_FUSED_SPLITS": sp}, 3))
 for env, reduce in cases:
     print(f"reduce={reduce} {env}: {run(env, reduce):8.1f} us/step", flush=True)

@@ -61,6 +61,9 @@ for i, (b, e, tag) in enumerate(step):
         print(f"{i:3d} {name:22s} entry {(b - base) / 1e3:8.2f} us  exit {(e - base) / 1e3:8.2f} us  dur {(e - b) / 1e3:6.2f}")
         if name.startswith("gemm") and "reduce-add" not in name:
             print("      " + "  ".join(f"{MARK_NAMES[j]} {(m - base) / 1e3:.2f}" for j, m in enumerate(marks[i]) if m > 0))
+        if "reduce-add" in name:
+            names = {3: "dep ok", 4: "operands landed", 6: "epi sees acc", 5: "tile staged", 7: "reduce-add complete"}
+            print("      " + "  ".join(f"{names[j]} {(marks[i][j] - base) / 1e3:.2f}" for j in (3, 4, 6, 5, 7) if marks[i][j] > 0))
         if name.startswith("ln+gemm"):
             names = {3: "dep ok", 4: "rows in registers", 5: "B operand written", 8: "mma sees B", 9: "mma issued",
                      6: "epi sees acc", 7: "stores done"}
