@@ -546,12 +546,27 @@ __global__ void __launch_bounds__(1024) select_kernel(SelectArgs a) {
     m.v = -INFINITY;
     m.i = 0x7fffffff;
     if (a.amax_val != nullptr) {
-      // reduce the per-group candidates the LM-head epilogue produced (EOS handled apart)
-      for (int i = threadIdx.x; i < a.n_groups; i += blockDim.x) {
-        MaxIdx c;
-        c.v = a.amax_val[static_cast<size_t>(i) * a.ld_amax + row];
-        c.i = a.amax_idx[static_cast<size_t>(i) * a.ld_amax + row];
-        m = better(m, c);
+      // reduce the per-group candidates the LM-head epilogue produced (EOS handled apart). The
+      // thread's candidates are fetched with independent loads first: a load -> compare loop pays
+      // one L2 round trip per candidate (7 of them for GPT-2's 1572 groups on 256 threads).
+      constexpr int kBatch = 8;
+      for (int i0 = threadIdx.x; i0 < a.n_groups; i0 += blockDim.x * kBatch) {
+        float cv[kBatch];
+        int ci[kBatch];
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) {
+          const int i = i0 + j * static_cast<int>(blockDim.x);
+          const bool ok = i < a.n_groups;
+          cv[j] = ok ? a.amax_val[static_cast<size_t>(i) * a.ld_amax + row] : -INFINITY;
+          ci[j] = ok ? a.amax_idx[static_cast<size_t>(i) * a.ld_amax + row] : 0x7fffffff;
+        }
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) {
+          MaxIdx c;
+          c.v = cv[j];
+          c.i = ci[j];
+          m = better(m, c);
+        }
       }
       m = block_argmax(m, red);
       if (!ban_eos) {
