@@ -113,9 +113,24 @@ def client_main(args):
     rng = np.random.default_rng(99)
     arrivals = np.cumsum(rng.exponential(1.0 / args.rate, size=len(reqs))) if args.rate > 0 else np.zeros(len(reqs))
     indices = list(range(args.client_index, len(reqs), args.client_procs))
-    with grpc.insecure_channel(f"127.0.0.1:{args.port}") as ch:
-        lat, t_first, t_last = run_calls(lambda: server_mod.LLMServiceStub(ch), reqs, indices, arrivals,
-                                         max(1, args.clients // args.client_procs), args.t_zero)
+    # several TCP connections per caller process: with more than one serving process the kernel
+    # balances CONNECTIONS over the listeners (SO_REUSEPORT), not requests
+    chans = [grpc.insecure_channel(f"127.0.0.1:{args.port}", options=(("grpc.use_local_subchannel_pool", 1),))
+             for _ in range(max(1, args.connections))]
+    stubs = [server_mod.LLMServiceStub(ch) for ch in chans]
+
+    class RoundRobin:
+        def __init__(self):
+            self.n = 0
+
+        def __getattr__(self, rpc):
+            self.n += 1
+            return getattr(stubs[self.n % len(stubs)], rpc)
+
+    lat, t_first, t_last = run_calls(RoundRobin, reqs, indices, arrivals,
+                                     max(1, args.clients // args.client_procs), args.t_zero)
+    for ch in chans:
+        ch.close()
     print(json.dumps({"lat": lat, "t_first": t_first, "t_last": t_last}))
 
 
@@ -160,6 +175,9 @@ def main():
     ap.add_argument("--clients", type=int, default=64, help="concurrent callers (threads over all caller processes)")
     ap.add_argument("--client-procs", type=int, default=4, help="caller processes (0 = callers share this process)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="also time this many requests per RPC on the host CPU")
+    ap.add_argument("--serving-procs", type=int, default=1,
+                    help="serving processes sharing the port (server.serve_many), each with gpus / serving-procs GPUs")
+    ap.add_argument("--connections", type=int, default=1, help="TCP connections per caller process")
     ap.add_argument("--scenario", default="mixed", choices=["mixed", "growing_channel"],
                     help="mixed: BASELINE configs[4]; growing_channel: consecutive summaries of growing channels")
     ap.add_argument("--channels", type=int, default=8)
@@ -178,6 +196,9 @@ def main():
 
     import grpc
 
+    if args.serving_procs > 1:
+        many_main(args)
+        return
     if args.switch_interval > 0:
         sys.setswitchinterval(args.switch_interval)
     server_mod = importlib.import_module(f"{PKG}.server")
@@ -271,6 +292,87 @@ def main():
     if args.cpu_sample > 0:
         out["cpu_latency_ms"] = cpu_sample(pb, svc, reqs, args.cpu_sample)
     print(json.dumps(out))
+
+
+def many_main(args):
+    """Several serving processes on one port (server.serve_many): the callers are the same caller
+    processes as in the single-server run, each with `--connections` TCP connections."""
+    import signal
+    import socket
+    import tempfile
+
+    import grpc
+
+    server_mod = importlib.import_module(f"{PKG}.server")
+    pb = importlib.import_module(f"{PKG}.llm_proto")
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    stats_dir = tempfile.mkdtemp(prefix="b200llm_stream_")
+    extra = ["--workers", str(max(args.clients, 8) + 8), "--max-seqs", "64", "--max-new-tokens", "160",
+             "--default-new-tokens", "32", "--prefix-cache", str(args.prefix_cache)]
+    servers = server_mod.serve_many("small", args.gpus, args.serving_procs, port, extra, stats_dir)
+    try:
+        deadline = time.time() + 600
+        ready = [os.path.join(stats_dir, f"serving_{i}.json.ready") for i in range(args.serving_procs)]
+        while not all(os.path.exists(r) for r in ready):
+            if time.time() > deadline or any(p.poll() is not None for p in servers):
+                raise RuntimeError("a serving process did not come up")
+            time.sleep(0.5)
+        reqs = make_requests(pb, args.requests)
+        # warm-up over many connections so that every listener captures its graphs
+        for _ in range(4 * args.serving_procs):
+            with grpc.insecure_channel(f"127.0.0.1:{port}", options=(("grpc.use_local_subchannel_pool", 1),)) as ch:
+                stub = server_mod.LLMServiceStub(ch)
+                for rpc, req in reqs[:6]:
+                    getattr(stub, rpc)(req, timeout=120)
+        t_zero = time.time() + 10.0
+        procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--as-client", "--port", str(port),
+                                   "--requests", str(args.requests), "--rate", str(args.rate),
+                                   "--clients", str(args.clients), "--client-procs", str(args.client_procs),
+                                   "--connections", str(args.connections),
+                                   "--client-index", str(i), "--t-zero", repr(t_zero)],
+                                  stdout=subprocess.PIPE, text=True) for i in range(args.client_procs)]
+        lat = {"GetSmartReply": [], "SummarizeConversation": [], "GetLLMAnswer": []}
+        t_first, t_last = float("inf"), 0.0
+        for pr in procs:
+            out, _ = pr.communicate(timeout=900)
+            if pr.returncode != 0:
+                raise RuntimeError(f"caller process failed with code {pr.returncode}")
+            d = json.loads(out.strip().splitlines()[-1])
+            for k, v in d["lat"].items():
+                lat[k].extend(v)
+            t_first, t_last = min(t_first, d["t_first"]), max(t_last, d["t_last"])
+    finally:
+        for p in servers:
+            p.send_signal(signal.SIGTERM)
+        for p in servers:
+            try:
+                p.wait(timeout=60)
+            except subprocess.TimeoutExpired:
+                p.kill()
+    wall = t_last - t_first
+    stats = []
+    for i in range(args.serving_procs):
+        path = os.path.join(stats_dir, f"serving_{i}.json")
+        if os.path.exists(path):
+            stats.append(json.load(open(path)))
+    gen = sum(s_["generated_tokens"] for s_ in stats)
+    warm = 4 * args.serving_procs * 6
+    print(json.dumps({
+        "metric": "mixed SmartReply/Summarize/Ask stream through gRPC LLMService (BASELINE configs[4])",
+        "n_gpus": args.gpus, "requests": len(reqs), "clients": args.clients, "client_processes": args.client_procs,
+        "connections_per_client_process": args.connections,
+        "process_model": f"{args.serving_procs} serving processes on one port (SO_REUSEPORT), each with "
+                         f"{args.gpus // args.serving_procs} GPU worker process(es) behind its router",
+        "wall_s": wall, "requests_per_s": len(reqs) / wall,
+        "generated_tokens_per_s_incl_warmup_tokens": gen / wall,
+        "requests_per_serving_process": [s_["requests"] for s_ in stats], "warmup_requests": warm,
+        "latency_ms": {k: {"n": len(v), "p50": float(np.percentile(v, 50)), "p95": float(np.percentile(v, 95))}
+                       for k, v in lat.items() if v},
+        "completed_per_gpu": [w["completed"] for s_ in stats for w in s_["workers"]],
+        "tokenizer": "byte-level GPT-2 ids (no vocab files offline): prompts are ~4x longer than with BPE",
+        "data": "synthetic conversations, random-init GPT-2 small"}))
 
 
 def cpu_sample(pb, svc, reqs, k: int) -> dict:

@@ -11,6 +11,7 @@ rather than hanging, which the callers turn into their canned replies.
 from __future__ import annotations
 
 import itertools
+import threading
 from dataclasses import dataclass, field
 
 from .engine import SamplingParams
@@ -59,6 +60,10 @@ class LocalGenerativeModel:
         self.timeout_s = timeout_s  # below the Raft node's tightest LLM deadline (10 s, raft_node.py:2084)
         self.max_prompt_tokens = max_prompt_tokens
         self._seed = itertools.count(1)  # next() is atomic under the GIL: 128 handler threads share it
+        self._meter = threading.Lock()
+        self.requests = 0
+        self.prompt_tokens = 0
+        self.generated_tokens = 0
 
     def _sampling(self, generation_config: dict | None) -> SamplingParams:
         cfg = generation_config or {}
@@ -76,6 +81,10 @@ class LocalGenerativeModel:
             ids = ids[-self.max_prompt_tokens:]  # keep the instructions at the end of the template
         result: GenerationResult = self.router.generate(ids, self._sampling(generation_config), timeout=self.timeout_s)
         text = self.tokenizer.decode(result.tokens)
+        with self._meter:
+            self.requests += 1
+            self.prompt_tokens += result.prompt_tokens
+            self.generated_tokens += len(result.tokens)
         return GenerateContentResponse(
             candidates=[Candidate(finish_reason=result.finish_reason, content=Content(parts=[Part(text=text)]))],
             usage={"prompt_tokens": result.prompt_tokens, "generated_tokens": len(result.tokens),
