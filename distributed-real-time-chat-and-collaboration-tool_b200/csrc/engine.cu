@@ -1455,9 +1455,24 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   if (e->tune_splits[3] > 0) p.split_p = e->tune_splits[3];
   // split-KV when (rows x heads) alone cannot fill the machine and contexts are long
   {
+    // One CTA per (row, head, split), six of them per SM, each walking its share of the context in
+    // 128-row passes. Cost model: waves of CTAs x (passes per CTA + a fixed half pass of set-up);
+    // fewer splits win ties. Doubling alone picked 4 splits for 16 rows x 16 heads at context 1100:
+    // 1024 CTAs on 888 slots = two waves; 3 splits (768 CTAs, one wave) is the better cut.
     const int ctas = bucket * e->H;
+    const int slots = 6 * sms;
     int splits = 1;
-    while (splits < 16 && ctas * splits < 4 * sms && max_ctx / (splits * 2) >= 64) splits *= 2;
+    float best = 1e30f;
+    for (int s = 1; s <= 16; ++s) {
+      const int per = (max_ctx + s - 1) / s;
+      if (s > 1 && per < 64) break;
+      const int waves = (ctas * s + slots - 1) / slots;
+      const float cost = static_cast<float>(waves) * (static_cast<float>((per + 127) / 128) + 0.5f);
+      if (cost < best - 1e-3f) {
+        best = cost;
+        splits = s;
+      }
+    }
     p.attn_splits = splits;
     if (e->tune_attn_splits > 0) p.attn_splits = e->tune_attn_splits;
   }
