@@ -103,7 +103,7 @@ def _load() -> C.CDLL:
         "b200llm_lm_head_argmax_groups": (i32, [i32, i32]),
         "b200llm_op_prefill_attention_paged": (C.c_int, [vp, i32, vp, vp, vp, i32, i32, i32, vp, i32, vp, vp, i32,
                                                          vp, i32, vp]),
-        "b200llm_op_ln_gemm": (C.c_int, [vp, vp, vp, f32, vp, vp, vp, i32, i32, i32, i32, i32, vp]),
+        "b200llm_op_ln_gemm": (C.c_int, [vp, vp, vp, f32, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
         "b200llm_op_gemm_redadd": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, i32, vp]),
         "b200llm_op_kv_scatter": (C.c_int, [vp, vp, vp, i32, i32, vp, i32, vp, vp, vp]),
         "b200llm_kv_pages_free": (C.c_int, [vp, P(i64), P(i64)]),

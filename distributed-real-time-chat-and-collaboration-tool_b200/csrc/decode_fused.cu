@@ -65,6 +65,11 @@ struct LnGemmKernelArgs {
   int ld_out;
   int stages;           // weight ring depth
   float eps;
+  // K split over gridDim.z: this CTA multiplies k-blocks [z * kb_per_split, (z + 1) * kb_per_split) and
+  // writes an fp32 partial plane (no bias, no activation) that the consumer reduces in a fixed order
+  int kb_per_split;     // = d / 64 without a split
+  float* partial_out;   // [gridDim.z][plane_rows, ld_out] or null
+  int plane_rows;
 };
 
 // 4 role warps + 16 LayerNorm warps (one token row each; the first 4 also own a TMEM lane quarter
@@ -76,7 +81,8 @@ template <bool GELU>
 __global__ void __launch_bounds__(kLnThreads, 1)
 ln_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const LnGemmKernelArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  const int n_kb = a.d / kKB;
+  const int n_kb = a.kb_per_split;        // k-blocks of this CTA
+  const int kb0 = blockIdx.z * n_kb;      // its first k-block
   uint8_t* ring = smem;                                   // stages x 16 KB weight tiles
   uint8_t* bop = smem + a.stages * kABytes;               // n_kb x [16 tokens x 64] bf16 (2 KB each)
   float* gb = reinterpret_cast<float*>(bop + n_kb * kNT * 128);  // gamma[d] | beta[d]
@@ -125,7 +131,7 @@ ln_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const LnGemmKernelArgs
           if (kb >= a.stages) mbar_wait(&empty_bar[s], static_cast<uint32_t>(kb / a.stages - 1) & 1u);
           mbar_arrive_expect_tx(&full_bar[s], kABytes);
         }
-        tma_load_2d(ring + s * kABytes, &map_w, &full_bar[single ? 0 : s], kb * kKB, m_blk * kM, kEvictFirst);
+        tma_load_2d(ring + s * kABytes, &map_w, &full_bar[single ? 0 : s], (kb0 + kb) * kKB, m_blk * kM, kEvictFirst);
       }
     }
   } else if (warp == 1) {
@@ -231,10 +237,13 @@ ln_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const LnGemmKernelArgs
           hi = pack_bf16x2((v[j].z - mean) * rstd * gm.z + bb.z, (v[j].w - mean) * rstd * gm.w + bb.w);
         }
         const int col = i << 2;                         // K index of the first of the 4 elements
-        const uint32_t kb = static_cast<uint32_t>(col >> 6);
-        const uint32_t chunk = static_cast<uint32_t>((col & 63) >> 3) ^ static_cast<uint32_t>(g & 7);
-        const uint32_t addr = row_base + kb * (kNT * 128) + (chunk << 4) + static_cast<uint32_t>((col & 4) << 1);
-        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(lo), "r"(hi) : "memory");
+        const int kb = (col >> 6) - kb0;                // k-block within this CTA's K range
+        if (kb >= 0 && kb < n_kb) {
+          const uint32_t chunk = static_cast<uint32_t>((col & 63) >> 3) ^ static_cast<uint32_t>(g & 7);
+          const uint32_t addr = row_base + static_cast<uint32_t>(kb) * (kNT * 128) + (chunk << 4) +
+                                static_cast<uint32_t>((col & 4) << 1);
+          asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(lo), "r"(hi) : "memory");
+        }
       }
     }
     fence_proxy_async();  // generic-proxy writes -> visible to the tensor core's reads
@@ -258,13 +267,22 @@ ln_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const LnGemmKernelArgs
                  : "memory");
     tmem_ld_wait();
     const int n_valid = f_ok ? (a.rows - tok0 - c0) : 0;  // token columns of this warp that exist
-    __nv_bfloat16* o = a.out + static_cast<size_t>(tok0 + c0) * a.ld_out + feature;
+    if (a.partial_out != nullptr) {
+      float* o = a.partial_out + (static_cast<size_t>(blockIdx.z) * a.plane_rows + tok0 + c0) * a.ld_out + feature;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float y = __uint_as_float(r[j]) + bias;
-      if (GELU) y = gelu_new(y);
-      if (j < n_valid) *o = __float2bfloat16(y);  // 32 lanes -> 64 contiguous bytes of one token row
-      o += a.ld_out;
+      for (int j = 0; j < 4; ++j) {
+        if (j < n_valid) *o = __uint_as_float(r[j]);  // 32 lanes -> 128 contiguous bytes of one token row
+        o += a.ld_out;
+      }
+    } else {
+      __nv_bfloat16* o = a.out + static_cast<size_t>(tok0 + c0) * a.ld_out + feature;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float y = __uint_as_float(r[j]) + bias;
+        if (GELU) y = gelu_new(y);
+        if (j < n_valid) *o = __float2bfloat16(y);  // 32 lanes -> 64 contiguous bytes of one token row
+        o += a.ld_out;
+      }
     }
     if (te == 0) B200_FTRACE(7);
     tc_fence_before();
@@ -463,9 +481,13 @@ bool ln_gemm_weights_resident(int d) {
 }
 
 int ln_gemm(const LnGemmArgs& g, cudaStream_t stream) {
-  B200_CHECK_ARG(g.x && g.gamma && g.beta && g.w && g.out, "ln_gemm: null argument");
+  const int split = g.split > 1 ? g.split : 1;
+  B200_CHECK_ARG(g.x && g.gamma && g.beta && g.w && (split > 1 ? g.partial_out != nullptr : g.out != nullptr),
+                 "ln_gemm: null argument");
   B200_CHECK_ARG(ln_gemm_supported(g.rows, g.d, g.features), "ln_gemm: shape not supported (rows <= 64, d % 64 == 0)");
-  const int n_kb = g.d / kKB;
+  B200_CHECK_ARG((g.d / kKB) % split == 0, "ln_gemm: split must divide d / 64");
+  B200_CHECK_ARG(split == 1 || !g.gelu, "ln_gemm: the gelu epilogue needs the whole K range in one CTA");
+  const int n_kb = g.d / kKB / split;
   const int bop_bytes = n_kb * kNT * 128 + 2 * g.d * 4;  // B operand + staged gamma / beta
   int stages = (kSmemLimit - bop_bytes - 512) / kABytes;
   if (stages > n_kb) stages = n_kb;
@@ -483,8 +505,11 @@ int ln_gemm(const LnGemmArgs& g, cudaStream_t stream) {
   a.ld_out = g.ld_out;
   a.stages = stages;
   a.eps = g.eps;
+  a.kb_per_split = n_kb;
+  a.partial_out = split > 1 ? g.partial_out : nullptr;
+  a.plane_rows = g.plane_rows > 0 ? g.plane_rows : g.rows;
   const int smem_bytes = stages * kABytes + bop_bytes + (2 * stages + 2) * 8 + 16;
-  const dim3 grid((g.features + kM - 1) / kM, (g.rows + kNT - 1) / kNT, 1);
+  const dim3 grid((g.features + kM - 1) / kM, (g.rows + kNT - 1) / kNT, split);
   if (g.gelu) {
     B200_PROPAGATE(set_smem(ln_gemm_kernel<true>, smem_bytes));
     return launch_pdl(ln_gemm_kernel<true>, grid, kLnThreads, smem_bytes, stream, g.pdl, map_w, a);

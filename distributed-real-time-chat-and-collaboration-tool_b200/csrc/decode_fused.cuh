@@ -24,6 +24,12 @@ struct LnGemmArgs {
   int ld_out = 0;
   int gelu = 0;                    // 1: gelu_new after the bias
   int pdl = 0;
+  // split > 1: K split over `split` CTAs per tile; each writes an fp32 partial plane
+  // partial_out[split][plane_rows, ld_out] (no bias, no activation) for the consumer to reduce in a
+  // fixed order (decode attention does, for the QKV projection). Light CTAs: d / split of the weights.
+  int split = 1;
+  float* partial_out = nullptr;
+  int plane_rows = 0;
 };
 bool ln_gemm_supported(int rows, int d, int features);
 bool ln_gemm_weights_resident(int d);  // the shape class for which the engine picks the fused path by itself

@@ -269,6 +269,7 @@ struct b200llm_engine {
   int tune_attn_splits = 0;           // tune build: KV split override
   int prefill_attn_mode = -1;         // -1 auto, 0 tcgen05 always, 1 mma.sync always (tune build: B200LLM_PREFILL_ATTN)
   int tune_fused_qkv = -1;            // tune build: 0 / 1 force ln_1 + c_attn as LayerNorm + planes / as the fused kernel
+  int tune_lnqkv_split = 0;           // tune build: K split of the light ln_1 + c_attn kernel (0 = LayerNorm + planes GEMM)
   int tune_fused_splits[2] = {0, 0};  // tune build: K splits of the fused path's out-proj / MLP-down
 };
 
@@ -349,6 +350,7 @@ struct StepPlan {
   bool fused = false;
   bool fused_qkv = true;   // false: ln_1 and c_attn stay LayerNorm + split-K planes (light CTAs: the
                            // attention kernel of the same layer can start beside them and prefetch its KV)
+  int lnqkv_split = 0;     // > 1 (with fused_qkv false): ln_1 + c_attn as ONE K-split kernel writing planes
   int rs_o = 1, rs_p = 1;  // K splits of the two reduce-add GEMMs
   int max_keys = 0;            // prefill: most keys (cached prefix + own rows) any sequence of the call has
   bool paged_prefill = false;  // some prefill rows are prompt suffixes behind a cached prefix (prefix_dev is valid)
@@ -443,12 +445,24 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       lg.pdl = pdl;
       const bool skip_lg = skip_gemm || (e->skip_mask & kSkipLnGemm) != 0;
       const bool skip_ra = skip_gemm || (e->skip_mask & kSkipRedAdd) != 0;
-      const bool qkv_planes = !p.fused_qkv && p.split_qkv > 1;
+      const bool qkv_planes = !p.fused_qkv && (p.lnqkv_split > 1 || p.split_qkv > 1);
+      const int qkv_plane_count = p.lnqkv_split > 1 ? p.lnqkv_split : p.split_qkv;
+      const bool lnqkv_planes = !p.fused_qkv && p.lnqkv_split > 1;
       if (p.fused_qkv) {
         if (!skip_lg) B200_PROPAGATE(count(e, ln_gemm(lg, e->stream)));
+      } else if (lnqkv_planes) {
+        // ln_1 inside a K-split c_attn with light CTAs (half of the weight tile each): the attention
+        // CTAs of the layer start beside them; it reduces the partial planes as on the ordered path
+        LnGemmArgs ls = lg;
+        ls.bias = nullptr;
+        ls.out = nullptr;
+        ls.split = p.lnqkv_split;
+        ls.partial_out = e->partials;
+        ls.plane_rows = rows;
+        if (!skip_lg) B200_PROPAGATE(count(e, ln_gemm(ls, e->stream)));
       } else {
         B200_PROPAGATE(ln(e, nullptr, 0, rows, nullptr, w.ln1_g, w.ln1_b, nullptr, rows, pdl));
-        if (qkv_planes) {
+        if (p.split_qkv > 1) {
           B200_PROPAGATE(gemm(e, e->h, w.w_qkv, nullptr, e->partials, rows, 3 * d, d, 3 * d, kEpiPartialF32,
                               p.split_qkv, pdl));
         } else {
@@ -459,7 +473,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       DecodeAttnArgs a = {};
       a.qkv = qkv_planes ? nullptr : e->qkv;
       a.qkv_partials = qkv_planes ? e->partials : nullptr;
-      a.n_qkv_partials = qkv_planes ? p.split_qkv : 0;
+      a.n_qkv_partials = qkv_planes ? qkv_plane_count : 0;
       a.partial_rows = rows;
       a.qkv_bias = w.b_qkv;
       a.active_slots = e->active_dev;
@@ -940,6 +954,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
     std::sscanf(env, "%d,%d,%d,%d", &e->tune_splits[0], &e->tune_splits[1], &e->tune_splits[2], &e->tune_splits[3]);
   }
   if (const char* env = std::getenv("B200LLM_PREFILL_ATTN")) e->prefill_attn_mode = std::atoi(env);
+  if (const char* env = std::getenv("B200LLM_LNQKV_SPLIT")) e->tune_lnqkv_split = std::atoi(env);
   if (const char* env = std::getenv("B200LLM_FUSED_QKV")) e->tune_fused_qkv = std::atoi(env);
   if (const char* env = std::getenv("B200LLM_FUSED_SPLITS")) {  // "o,p"
     std::sscanf(env, "%d,%d", &e->tune_fused_splits[0], &e->tune_fused_splits[1]);
@@ -1488,6 +1503,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
       p.fused_qkv = bucket * e->H * p.attn_splits <= early_slots;
     }
     if (e->tune_fused_qkv >= 0) p.fused_qkv = e->tune_fused_qkv != 0;
+    p.lnqkv_split = e->tune_lnqkv_split;
     if (!p.fused_qkv && cap > 1) p.split_qkv = pick_split(3 * e->d, e->d, sms, cap);
     if (e->tune_splits[0] > 0) p.split_qkv = e->tune_splits[0];
   }
@@ -1951,7 +1967,7 @@ int b200llm_op_kv_scatter(const void* qkv, const int32_t* row_pos, const int32_t
 
 int b200llm_op_ln_gemm(const float* x, const float* gamma, const float* beta, float eps, const void* w,
                        const float* bias, void* out, int32_t rows, int32_t features, int32_t d, int32_t ld_out,
-                       int32_t gelu, void* stream) {
+                       int32_t gelu, int32_t split, float* partial_out, void* stream) {
   LnGemmArgs a;
   a.x = x;
   a.gamma = gamma;
@@ -1965,6 +1981,9 @@ int b200llm_op_ln_gemm(const float* x, const float* gamma, const float* beta, fl
   a.features = features;
   a.ld_out = ld_out;
   a.gelu = gelu;
+  a.split = split;
+  a.partial_out = partial_out;
+  a.plane_rows = rows;
   return ln_gemm(a, reinterpret_cast<cudaStream_t>(stream));
 }
 

@@ -147,13 +147,19 @@ def convert_transpose(src: torch.Tensor) -> torch.Tensor:
 
 
 def ln_gemm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None,
-            gelu: bool = False, eps: float = 1e-5) -> torch.Tensor:
-    """out = (gelu_new)(LayerNorm(x) @ w.T + bias), LayerNorm folded into the GEMM (decode, <= 64 rows)."""
+            gelu: bool = False, eps: float = 1e-5, split: int = 1) -> torch.Tensor:
+    """out = (gelu_new)(LayerNorm(x) @ w.T + bias), LayerNorm folded into the GEMM (decode, <= 64 rows).
+    split > 1: returns the fp32 partial planes [split, rows, features] (no bias) instead."""
     rows, d = x.shape
     features = w.shape[0]
+    if split > 1:
+        planes = torch.zeros(split, rows, features, dtype=torch.float32, device=x.device)
+        check(lib.b200llm_op_ln_gemm(_ptr(x), _ptr(gamma), _ptr(beta), eps, _ptr(w), None, None, rows, features, d,
+                                     features, 0, split, _ptr(planes), _stream()))
+        return planes
     out = torch.zeros(rows, features, dtype=torch.bfloat16, device=x.device)
     check(lib.b200llm_op_ln_gemm(_ptr(x), _ptr(gamma), _ptr(beta), eps, _ptr(w), _ptr(bias), _ptr(out), rows,
-                                 features, d, features, int(gelu), _stream()))
+                                 features, d, features, int(gelu), 1, None, _stream()))
     return out
 
 

@@ -238,10 +238,14 @@ int b200llm_op_gemm(const void* act_dev, const void* w_dev, const float* bias_de
 
 /* out_bf16[row, f] = epilogue( LayerNorm(x_f32[row, :]) . w[f, :] + bias[f] ), epilogue = identity or
  * gelu_new: LayerNorm folded into the consuming GEMM's operand path (the decode step's ln_1 + c_attn
- * and ln_2 + c_fc + act; modeling_gpt2.py:273,185 / :304,239-240). rows <= 64, d % 64 == 0. */
+ * and ln_2 + c_fc + act; modeling_gpt2.py:273,185 / :304,239-240). rows <= 64, d % 64 == 0.
+ * split > 1: K split over `split` CTAs per tile, each writing an fp32 partial plane
+ * partial_out_dev[split][rows, ld_out] (no bias, no activation; out_bf16_dev unused) that the consumer
+ * reduces in a fixed order -- the form decode attention takes the QKV projection in. */
 int b200llm_op_ln_gemm(const float* x_dev, const float* gamma_dev, const float* beta_dev, float eps,
                        const void* w_dev, const float* bias_dev, void* out_bf16_dev, int32_t rows,
-                       int32_t features, int32_t d, int32_t ld_out, int32_t gelu, void* stream);
+                       int32_t features, int32_t d, int32_t ld_out, int32_t gelu, int32_t split,
+                       float* partial_out_dev, void* stream);
 /* x_f32[row, f] += act[row, :] . w[f, :] + bias[f], split-K over `split` CTAs per 128 features whose
  * partial tiles are added into x in L2 by TMA reduce-add (the decode step's attention out-proj and
  * MLP down-proj with their residual adds, modeling_gpt2.py:223,282 / :241,307). split 0 = automatic.

@@ -84,7 +84,7 @@ out = {"workload": workload, "step_us": full, "method": "B200LLM_SKIP difference
 acc = 0.0
 for name, bit in CLASSES:
     us = max(full - step_us(bit), 0.0)
-    if bit in (64, 128) and us < 0.5:
+    if bit in (64, 128) and us < 0.03 * full:
         continue  # not the fused path: these classes do not exist in this step
     if bit != 2:
         acc += us  # (bit 2 = all layer GEMMs: on the fused path that is the sum of the two classes below it)

@@ -34,7 +34,7 @@ steps = min(N - 1, 63)
 
 
 def run(env: dict, reduce: int) -> float:
-    for k in ("B200LLM_SKIP", "B200LLM_FUSED_SPLITS", "B200LLM_SPLITS", "B200LLM_FUSED_QKV"):
+    for k in ("B200LLM_SKIP", "B200LLM_FUSED_SPLITS", "B200LLM_SPLITS", "B200LLM_FUSED_QKV", "B200LLM_LNQKV_SPLIT"):
         os.environ.pop(k, None)
     os.environ.update(env)
     eng = E.Engine(shape, blob, max_seqs=B, max_seq_len=T + N, max_batch_tokens=min(B * T, 16384), max_new_tokens=N,

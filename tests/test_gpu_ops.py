@@ -424,6 +424,15 @@ def test_layernorm_folded_into_the_gemm(ops, cuda, rows, d, features, gelu):
     scale = ref.abs().max().item()
     # bf16 output rounding + an occasional 1-ulp difference of a normalised operand element
     assert err <= 4e-3 * scale + 2 ** -8 * scale, (err, scale)
+    # the K-split form (light CTAs, fp32 partial planes for the consumer to reduce): same sum, no bias
+    if not gelu:
+        n_kb = d // 64
+        for split in [s for s in (2, 4) if n_kb % s == 0]:
+            planes = ops.ln_gemm(x, gamma, beta, w, None, split=split)
+            torch.cuda.synchronize()
+            got = planes.sum(0) + bias
+            err = (got - (h @ w.float().t() + bias)).abs().max().item()
+            assert err <= 4e-3 * scale, (split, err, scale)
 
 
 @pytest.mark.parametrize("rows,features,k,split", [
