@@ -26,6 +26,7 @@
 // into their accumulators. One CTA needs 112 KB of shared memory and 256 TMEM columns: two CTAs
 // share an SM, and one's softmax overlaps the other's MMAs.
 #include <mutex>
+#include <type_traits>
 
 #include "attention.cuh"
 #include "common.cuh"
@@ -54,6 +55,22 @@ struct TcSmem {
   uint64_t s_bar;      // S = Q K^T complete
   uint64_t p_bar;      // 128 row threads: P written, S and O_t of the previous tile consumed
   uint64_t o_bar;      // O_t = P V complete (K/V buffer and P reusable)
+  uint32_t tmem_slot;
+};
+
+// Sequences of at most one key tile and no cached prefix (prompts of <= 128 tokens): one K/V buffer,
+// P overwrites Q and K once S is complete, and O_t reuses the TMEM columns of S once every row has
+// read it. 48 KB + 128 TMEM columns + no 64-float accumulator per thread: four CTAs per SM instead of
+// two, which is what a CTA that is all set-up, one tile and tear-down needs.
+struct TcSmemSingle {
+  uint8_t q[kTileBytes];   // then P, first half
+  uint8_t k[kTileBytes];   // then P, second half
+  uint8_t v[kTileBytes];
+  uint64_t q_bar;
+  uint64_t kv_bar[2];
+  uint64_t s_bar;
+  uint64_t p_bar;
+  uint64_t o_bar;
   uint32_t tmem_slot;
 };
 
@@ -91,11 +108,24 @@ __device__ __forceinline__ float ex2_approx(float x) {
 constexpr int kRowThreads = 128;
 constexpr int kTcThreads = kRowThreads + 32;
 
-__global__ void __launch_bounds__(kTcThreads, 2)
+template <bool kSingle>
+__global__ void __launch_bounds__(kTcThreads, kSingle ? 4 : 2)
 prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ CUtensorMap map_k,
                        const __grid_constant__ CUtensorMap map_v, const TcArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  TcSmem& sm = *reinterpret_cast<TcSmem*>(smem_raw);
+  using Smem = typename std::conditional<kSingle, TcSmemSingle, TcSmem>::type;
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+  uint8_t* const q_s = sm.q;
+  uint8_t* const p_s = kSingle ? sm.q : reinterpret_cast<TcSmem*>(smem_raw)->p;
+  auto k_s = [&](int buf) -> uint8_t* {
+    if constexpr (kSingle) return reinterpret_cast<TcSmemSingle*>(smem_raw)->k;
+    else return reinterpret_cast<TcSmem*>(smem_raw)->k[buf];
+  };
+  auto v_s = [&](int buf) -> uint8_t* {
+    if constexpr (kSingle) return reinterpret_cast<TcSmemSingle*>(smem_raw)->v;
+    else return reinterpret_cast<TcSmem*>(smem_raw)->v[buf];
+  };
+  constexpr uint32_t kCols = kSingle ? 128u : kTmemCols;
 
   const int b = blockIdx.z, h = blockIdx.y, qt = blockIdx.x;
   const int row0 = a.cu_seqlens[b];
@@ -111,20 +141,45 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if ((smem_u32(smem_raw) & 1023u) != 0) __trap();  // SWIZZLE_128B tiles need 1024 B alignment
 
-  if (tid == 0) {
-    tma_prefetch_desc(&map_qkv);
-    tma_prefetch_desc(&map_k);
-    tma_prefetch_desc(&map_v);
-    mbar_init(&sm.q_bar, 1);
-    mbar_init(&sm.kv_bar[0], 1);
-    mbar_init(&sm.kv_bar[1], 1);
-    mbar_init(&sm.s_bar, 1);
-    mbar_init(&sm.p_bar, kRowThreads);
-    mbar_init(&sm.o_bar, 1);
-    fence_barrier_init();
+  // Warp 4 initialises the barriers and puts the first loads (Q, key tile 0) in flight at once; the
+  // TMEM allocation (warp 1) and the CTA-wide barrier run under their latency.
+  constexpr uint32_t idesc_s = umma_idesc_bf16(kTQ, kTK);                    // both operands K-major
+  constexpr uint32_t idesc_o = umma_idesc_bf16(kTQ, kHeadDim) | (1u << 16);  // B (= V) is MN-major
+  auto load_kv = [&](int t, int buf) {  // whole warp 4
+    if (t < n_pre) {
+      const int n_keys = min(kTK, prefix - t * kTK);
+      const int pages = (n_keys + kPageTokens - 1) / kPageTokens;
+      if (lane == 0) mbar_arrive_expect_tx(&sm.kv_bar[buf], static_cast<uint32_t>(pages) * 2u * kPageBytes);
+      __syncwarp();
+      if (lane < pages) {
+        const int row = (pt[t * kPagesPerTile + lane] * a.n_head + h) * kPageTokens;
+        tma_load_2d(k_s(buf) + lane * kPageBytes, &map_k, &sm.kv_bar[buf], 0, row, kEvictNormal);
+        tma_load_2d(v_s(buf) + lane * kPageBytes, &map_v, &sm.kv_bar[buf], 0, row, kEvictNormal);
+      }
+    } else if (lane == 0) {
+      const int r = row0 + (t - n_pre) * kTK;
+      mbar_arrive_expect_tx(&sm.kv_bar[buf], 2u * kTileBytes);
+      tma_load_2d(k_s(buf), &map_qkv, &sm.kv_bar[buf], d + h * kHeadDim, r, kEvictNormal);
+      tma_load_2d(v_s(buf), &map_qkv, &sm.kv_bar[buf], 2 * d + h * kHeadDim, r, kEvictNormal);
+    }
+  };
+  if (warp == 4) {
+    if (lane == 0) {
+      mbar_init(&sm.q_bar, 1);
+      mbar_init(&sm.kv_bar[0], 1);
+      mbar_init(&sm.kv_bar[1], 1);
+      mbar_init(&sm.s_bar, 1);
+      mbar_init(&sm.p_bar, kRowThreads);
+      mbar_init(&sm.o_bar, 1);
+      fence_barrier_init();
+      mbar_arrive_expect_tx(&sm.q_bar, kTileBytes);
+      tma_load_2d(q_s, &map_qkv, &sm.q_bar, h * kHeadDim, row0 + qt * kTQ, kEvictFirst);
+    }
+    __syncwarp();
+    load_kv(0, 0);
   }
   if (warp == 1) {
-    tmem_alloc(&sm.tmem_slot, kTmemCols);
+    tmem_alloc(&sm.tmem_slot, kCols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -134,31 +189,11 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
 
   if (warp == 4) {
     // ================= data movement + MMA issue =================
-    constexpr uint32_t idesc_s = umma_idesc_bf16(kTQ, kTK);                    // both operands K-major
-    constexpr uint32_t idesc_o = umma_idesc_bf16(kTQ, kHeadDim) | (1u << 16);  // B (= V) is MN-major
-    auto load_kv = [&](int t, int buf) {  // whole warp
-      if (t < n_pre) {
-        const int n_keys = min(kTK, prefix - t * kTK);
-        const int pages = (n_keys + kPageTokens - 1) / kPageTokens;
-        if (lane == 0) mbar_arrive_expect_tx(&sm.kv_bar[buf], static_cast<uint32_t>(pages) * 2u * kPageBytes);
-        __syncwarp();
-        if (lane < pages) {
-          const int row = (pt[t * kPagesPerTile + lane] * a.n_head + h) * kPageTokens;
-          tma_load_2d(sm.k[buf] + lane * kPageBytes, &map_k, &sm.kv_bar[buf], 0, row, kEvictNormal);
-          tma_load_2d(sm.v[buf] + lane * kPageBytes, &map_v, &sm.kv_bar[buf], 0, row, kEvictNormal);
-        }
-      } else if (lane == 0) {
-        const int r = row0 + (t - n_pre) * kTK;
-        mbar_arrive_expect_tx(&sm.kv_bar[buf], 2u * kTileBytes);
-        tma_load_2d(sm.k[buf], &map_qkv, &sm.kv_bar[buf], d + h * kHeadDim, r, kEvictNormal);
-        tma_load_2d(sm.v[buf], &map_qkv, &sm.kv_bar[buf], 2 * d + h * kHeadDim, r, kEvictNormal);
-      }
-    };
     auto issue_s = [&](int t) {  // lane 0
       mbar_wait(&sm.kv_bar[t & 1], static_cast<uint32_t>(t >> 1) & 1u);
       tc_fence_after();
-      const uint64_t dq = umma_desc_k_sw128(smem_u32(sm.q));
-      const uint64_t dk = umma_desc_k_sw128(smem_u32(sm.k[t & 1]));
+      const uint64_t dq = umma_desc_k_sw128(smem_u32(q_s));
+      const uint64_t dk = umma_desc_k_sw128(smem_u32(k_s(t & 1)));
 #pragma unroll
       for (int k = 0; k < kHeadDim / 16; ++k) {  // 16 dims = 32 B inside the 128 B swizzle row
         umma_bf16_ss(tmem_base, dq + static_cast<uint64_t>(k * 2), dk + static_cast<uint64_t>(k * 2), idesc_s,
@@ -166,11 +201,6 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
       }
       umma_commit(&sm.s_bar);
     };
-    if (lane == 0) {
-      mbar_arrive_expect_tx(&sm.q_bar, kTileBytes);
-      tma_load_2d(sm.q, &map_qkv, &sm.q_bar, h * kHeadDim, row0 + qt * kTQ, kEvictFirst);
-    }
-    load_kv(0, 0);
     if (lane == 0) {
       mbar_wait(&sm.q_bar, 0);
       issue_s(0);
@@ -184,13 +214,13 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
       if (lane == 0) {
         mbar_wait(&sm.p_bar, static_cast<uint32_t>(t) & 1u);  // P(t) in shared memory, S(t) consumed
         tc_fence_after();
-        const uint64_t dv = umma_desc_mn_sw128(smem_u32(sm.v[t & 1]));
+        const uint64_t dv = umma_desc_mn_sw128(smem_u32(v_s(t & 1)));
 #pragma unroll
         for (int s = 0; s < kTK / 16; ++s) {
           // A: 16 keys = 32 B inside the 128 B row of column block s / 4; B: 16 key rows = 2048 B further
           const uint64_t dp =
-              umma_desc_k_sw128(smem_u32(sm.p) + static_cast<uint32_t>((s >> 2) * kTileBytes + (s & 3) * 32));
-          umma_bf16_ss(tmem_base + kTK, dp, dv + static_cast<uint64_t>((s * 16 * 128) >> 4), idesc_o, s > 0 ? 1u : 0u);
+              umma_desc_k_sw128(smem_u32(p_s) + static_cast<uint32_t>((s >> 2) * kTileBytes + (s & 3) * 32));
+          umma_bf16_ss(tmem_base + (kSingle ? 0u : static_cast<uint32_t>(kTK)), dp, dv + static_cast<uint64_t>((s * 16 * 128) >> 4), idesc_o, s > 0 ? 1u : 0u);
         }
         umma_commit(&sm.o_bar);
         if (t + 1 < n_tiles) issue_s(t + 1);  // computed while the row threads fold O_t(t)
@@ -200,13 +230,13 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
   } else {
     // ================= 128 row threads =================
     const uint32_t tmem_s = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
-    const uint32_t tmem_o = tmem_s + kTK;
-    float o_acc[kHeadDim];
+    const uint32_t tmem_o = tmem_s + (kSingle ? 0u : static_cast<uint32_t>(kTK));  // single tile: O_t over the consumed S
+    float o_acc[kSingle ? 1 : kHeadDim];  // single tile: O_t goes from TMEM straight to the output
 #pragma unroll
-    for (int j = 0; j < kHeadDim; ++j) o_acc[j] = 0.f;
+    for (int j = 0; j < (kSingle ? 1 : kHeadDim); ++j) o_acc[j] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;  // m_run in units of raw scores
     const int q_local = qt * kTQ + tid;    // this thread's row within the sequence's rows
-    const uint32_t p_row = smem_u32(sm.p) + static_cast<uint32_t>((tid >> 3) * 1024 + (tid & 7) * 128);
+    const uint32_t p_row = smem_u32(p_s) + static_cast<uint32_t>((tid >> 3) * 1024 + (tid & 7) * 128);
 
     for (int t = 0; t < n_tiles; ++t) {
       const int buf = t & 1;
@@ -218,27 +248,24 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
       const int lim = pre ? min(kTK, prefix - tile_lo) : min(min(q_local, len_q - 1) - tile_lo + 1, kTK);
       const bool need_mask = pre ? (tile_lo + kTK > prefix) : (t == n_tiles - 1 || tile_lo + kTK > len_q);
 
-      if (!pre && t - n_pre == qt && pt != nullptr) {
-        // diagonal tile: this CTA fills the KV pages with its 128 rows of K and V. Row tid of the
-        // swizzled tile: chunk c lives at chunk position c ^ (tid & 7).
-        mbar_wait(&sm.kv_bar[buf], static_cast<uint32_t>(t >> 1) & 1u);
-        if (q_local < len_q) {
+      mbar_wait(&sm.s_bar, static_cast<uint32_t>(t) & 1u);
+      tc_fence_after();
+      if constexpr (kSingle) {
+        // P is about to overwrite Q and K: this row's K goes to its page first
+        if (pt != nullptr && q_local < len_q) {
+          mbar_wait(&sm.kv_bar[buf], 0);
           const int pos = prefix + q_local;
           const size_t dst = ((static_cast<size_t>(pt[pos / kPageTokens]) * a.n_head + h) * kPageTokens +
                               pos % kPageTokens) * kHeadDim;
-          const uint8_t* krow = sm.k[buf] + (tid >> 3) * 1024 + (tid & 7) * 128;
-          const uint8_t* vrow = sm.v[buf] + (tid >> 3) * 1024 + (tid & 7) * 128;
+          const uint8_t* krow = k_s(buf) + (tid >> 3) * 1024 + (tid & 7) * 128;
 #pragma unroll
           for (int c = 0; c < 8; ++c) {
-            const int sc = (c ^ (tid & 7)) * 16;
-            *reinterpret_cast<uint4*>(a.k_pool + dst + c * 8) = *reinterpret_cast<const uint4*>(krow + sc);
-            *reinterpret_cast<uint4*>(a.v_pool + dst + c * 8) = *reinterpret_cast<const uint4*>(vrow + sc);
+            *reinterpret_cast<uint4*>(a.k_pool + dst + c * 8) =
+                *reinterpret_cast<const uint4*>(krow + ((c ^ (tid & 7)) * 16));
           }
         }
+        // (row r of P's second half lands exactly on row r of K, which only thread r reads: no barrier)
       }
-
-      mbar_wait(&sm.s_bar, static_cast<uint32_t>(t) & 1u);
-      tc_fence_after();
       // 32-key chunks of the tile that at least one row of this warp can see (lim grows with the
       // row, so lane 31 has the warp's largest): on a diagonal tile warp w sees w + 1 of the 4 chunks,
       // the others are all-masked and cost neither TMEM reads nor exponentials
@@ -307,43 +334,95 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid
         // buffer had before; their weights are exactly 0, but 0 x NaN is NaN, so clear them.
         // (TMA never touches these rows, and the page rows it did load are complete: s_bar fired.)
         const int loaded = ((prefix - tile_lo + kPageTokens - 1) / kPageTokens) * kPageTokens;
-        uint4* vz = reinterpret_cast<uint4*>(sm.v[buf] + loaded * 128);
+        uint4* vz = reinterpret_cast<uint4*>(v_s(buf) + loaded * 128);
         for (int i = tid; i < (kTK - loaded) * 8; i += kRowThreads) vz[i] = make_uint4(0u, 0u, 0u, 0u);
       }
       fence_proxy_async();  // P (and cleared V rows) must be visible to the tensor core's proxy
       tc_fence_before();
       mbar_arrive(&sm.p_bar);
 
+      if (!pre && t - n_pre == qt && pt != nullptr) {
+        // diagonal tile: this CTA fills the KV pages with its 128 rows of K and V while P V runs (the
+        // tile landed before S was computed). Row tid of the swizzled tile: chunk c lives at chunk
+        // position c ^ (tid & 7). (Single-tile instance: K went out before P overwrote it, see above.)
+        mbar_wait(&sm.kv_bar[buf], static_cast<uint32_t>(t >> 1) & 1u);  // complete long ago: orders the reads below
+        if (q_local < len_q) {
+          const int pos = prefix + q_local;
+          const size_t dst = ((static_cast<size_t>(pt[pos / kPageTokens]) * a.n_head + h) * kPageTokens +
+                              pos % kPageTokens) * kHeadDim;
+          const uint8_t* krow = k_s(buf) + (tid >> 3) * 1024 + (tid & 7) * 128;
+          const uint8_t* vrow = v_s(buf) + (tid >> 3) * 1024 + (tid & 7) * 128;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const int sc = (c ^ (tid & 7)) * 16;
+            if (!kSingle) *reinterpret_cast<uint4*>(a.k_pool + dst + c * 8) = *reinterpret_cast<const uint4*>(krow + sc);
+            *reinterpret_cast<uint4*>(a.v_pool + dst + c * 8) = *reinterpret_cast<const uint4*>(vrow + sc);
+          }
+        }
+      }
+
       mbar_wait(&sm.o_bar, static_cast<uint32_t>(t) & 1u);
       tc_fence_after();
+      if constexpr (kSingle) {
+        // the only tile: normalise O_t and store it, 16 columns at a time (few registers)
+        const float inv = 1.0f / l_run;
+        __nv_bfloat16* orow = a.out + static_cast<size_t>(row0 + q_local) * d + h * kHeadDim;
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_o + c * 32, r);
-        tmem_ld_wait();
+        for (int c = 0; c < 4; ++c) {
+          uint32_t r[16];
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+              "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+              : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+              : "r"(tmem_o + c * 16)
+              : "memory");
+          tmem_ld_wait();
+          if (q_local < len_q) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) o_acc[c * 32 + j] = fmaf(o_acc[c * 32 + j], alpha, __uint_as_float(r[j]));
+            for (int g = 0; g < 2; ++g) {
+              uint4 v;
+              v.x = pack_bf16x2(__uint_as_float(r[8 * g]) * inv, __uint_as_float(r[8 * g + 1]) * inv);
+              v.y = pack_bf16x2(__uint_as_float(r[8 * g + 2]) * inv, __uint_as_float(r[8 * g + 3]) * inv);
+              v.z = pack_bf16x2(__uint_as_float(r[8 * g + 4]) * inv, __uint_as_float(r[8 * g + 5]) * inv);
+              v.w = pack_bf16x2(__uint_as_float(r[8 * g + 6]) * inv, __uint_as_float(r[8 * g + 7]) * inv);
+              *reinterpret_cast<uint4*>(orow + 16 * c + 8 * g) = v;
+            }
+          }
+        }
+        (void)alpha;
+      } else {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_o + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) o_acc[c * 32 + j] = fmaf(o_acc[c * 32 + j], alpha, __uint_as_float(r[j]));
+        }
       }
       tc_fence_before();
     }
 
-    if (q_local < len_q) {
-      const float inv = 1.0f / l_run;
-      __nv_bfloat16* orow = a.out + static_cast<size_t>(row0 + q_local) * d + h * kHeadDim;
+    if constexpr (!kSingle) {
+      if (q_local < len_q) {
+        const float inv = 1.0f / l_run;
+        __nv_bfloat16* orow = a.out + static_cast<size_t>(row0 + q_local) * d + h * kHeadDim;
 #pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        uint4 v;
-        v.x = pack_bf16x2(o_acc[8 * g] * inv, o_acc[8 * g + 1] * inv);
-        v.y = pack_bf16x2(o_acc[8 * g + 2] * inv, o_acc[8 * g + 3] * inv);
-        v.z = pack_bf16x2(o_acc[8 * g + 4] * inv, o_acc[8 * g + 5] * inv);
-        v.w = pack_bf16x2(o_acc[8 * g + 6] * inv, o_acc[8 * g + 7] * inv);
-        *reinterpret_cast<uint4*>(orow + 8 * g) = v;
+        for (int g = 0; g < 8; ++g) {
+          uint4 v;
+          v.x = pack_bf16x2(o_acc[8 * g] * inv, o_acc[8 * g + 1] * inv);
+          v.y = pack_bf16x2(o_acc[8 * g + 2] * inv, o_acc[8 * g + 3] * inv);
+          v.z = pack_bf16x2(o_acc[8 * g + 4] * inv, o_acc[8 * g + 5] * inv);
+          v.w = pack_bf16x2(o_acc[8 * g + 6] * inv, o_acc[8 * g + 7] * inv);
+          *reinterpret_cast<uint4*>(orow + 8 * g) = v;
+        }
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == 1) tmem_dealloc(tmem_base, kCols);
 }
 
 }  // namespace
@@ -377,11 +456,18 @@ int prefill_attention_tc(const PagedPrefillArgs& a, cudaStream_t stream) {
   k.k_pool = const_cast<__nv_bfloat16*>(a.k_pool);
   k.v_pool = const_cast<__nv_bfloat16*>(a.v_pool);
   k.out = a.out;
-  // per device, and cheap: set on every launch rather than remembering which devices have it
-  B200_CUDA_OK(cudaFuncSetAttribute(prefill_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    static_cast<int>(sizeof(TcSmem))));
   dim3 grid((a.max_suffix_len + kTQ - 1) / kTQ, a.n_head, a.batch);
-  prefill_attn_tc_kernel<<<grid, kTcThreads, sizeof(TcSmem), stream>>>(map_qkv, map_k, map_v, k);
+  // (the opt-in shared-memory size is per device, and cheap: set on every launch)
+  if (a.prefix_len == nullptr && a.max_suffix_len <= kTK) {
+    // every sequence is one key tile: the light instance (four CTAs per SM)
+    B200_CUDA_OK(cudaFuncSetAttribute(prefill_attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(sizeof(TcSmemSingle))));
+    prefill_attn_tc_kernel<true><<<grid, kTcThreads, sizeof(TcSmemSingle), stream>>>(map_qkv, map_k, map_v, k);
+  } else {
+    B200_CUDA_OK(cudaFuncSetAttribute(prefill_attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(sizeof(TcSmem))));
+    prefill_attn_tc_kernel<false><<<grid, kTcThreads, sizeof(TcSmem), stream>>>(map_qkv, map_k, map_v, k);
+  }
   B200_CUDA_OK(cudaGetLastError());
   return kOk;
 }

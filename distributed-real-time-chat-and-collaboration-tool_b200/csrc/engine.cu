@@ -574,11 +574,12 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       // Prefill: every query attends over its sequence's cached prefix (shared-prefix reuse; read
       // from the pages) followed by the rows of this call (read from qkv); the CTA on the diagonal
       // writes its K/V tile into the pages, so there is no scatter pass.
-      // Sequences of at most one 128-key tile (prompts of <= 128 tokens: every CTA would be set-up,
-      // one tile, tear-down) stay on the mma.sync kernel with 64-row CTAs, measured faster there
-      // (64 x 128-token prompts: 25.9 vs 33.3 us per layer); everything longer runs on tcgen05
-      // (16 x 1024 tokens: 147 vs 200 us per layer).
-      const bool tc = e->prefill_attn_mode == 0 || (e->prefill_attn_mode < 0 && p.max_keys > 128);
+      // tcgen05 for every prompt longer than 64 tokens (a light single-tile instance for <= 128 keys,
+      // the pipelined one beyond; 64 x 128 tokens: 2.18 vs 2.20 ms per prefill against the mma.sync
+      // kernel, 16 x 1024: 12.3 vs 13.7 ms). Prompts of at most 64 tokens would fill less than half
+      // of a 128-row tcgen05 tile and stay on the 64-row mma.sync kernel (32 x 64 tokens, GPT-2 large:
+      // 6.02 vs 6.08 ms).
+      const bool tc = e->prefill_attn_mode == 0 || (e->prefill_attn_mode < 0 && p.max_keys > 64);
       if (!tc && !p.paged_prefill) {
         PrefillCache pc;
         pc.slots = e->slots_dev;
