@@ -56,7 +56,9 @@ def _exercise_all_four_handlers(mod, pb2, model):
     # when the random-weight model's text has fewer usable lines
     assert r.request_id == "s1" and 2 <= len(r.suggestions) <= 3 and all(isinstance(x, str) and x for x in r.suggestions)
     r = servicer.SummarizeConversation(pb2.SummarizeRequest(request_id="m1", messages=msgs, max_length=120), None)
-    assert r.request_id == "m1" and 0 < len(r.summary) <= 120 and 1 <= len(r.key_points) <= 3
+    # (a random-weight model's text rarely contains "Summary:": the reference then returns what its
+    # parser found, possibly an empty summary, plus its default key points, llm_server.py:316-348)
+    assert r.request_id == "m1" and len(r.summary) <= 120 and 1 <= len(r.key_points) <= 3
     r = servicer.GetLLMAnswer(pb2.LLMRequest(request_id="a1", query="When is the review?", context=["alice: 3pm"]), None)
     assert r.request_id == "a1" and isinstance(r.answer, str) and r.answer
     assert r.confidence in (0.0, pytest.approx(0.95))
