@@ -14,10 +14,13 @@
 //   deterministically by a combine pass or, for small grids, inside a thread-block cluster.
 #include "attention.cuh"
 
+#include <cuda.h>
+
 #include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
+#include "gemm_tcgen05.cuh"
 #include "ops.cuh"
 
 #ifdef B200_ATTN_TRACE
@@ -781,6 +784,363 @@ __global__ void __launch_bounds__(64) decode_combine_kernel(DecodeAttnArgs a) {
   a.out[static_cast<size_t>(b) * d + h * kHeadDim + dim] = __float2bfloat16(o / l);
 }
 
+// ---------------------------------------------------------------------------------------
+// Decode, streaming form: many (row, head) units per SM and / or long contexts
+// ---------------------------------------------------------------------------------------
+// decode_attn_kernel above is built for the single-wave step (64 rows x 12 heads at context ~150: every
+// CTA resident at once, KV rows fetched under the QKV projection). With more units than CTA slots, or
+// several 128-row passes per CTA, its load -> wait -> compute chain repeats serially per CTA and the
+// 16 cp.async per thread and pass cost more instructions than the math. This kernel is the
+// bandwidth-oriented form for those shapes:
+//   * persistent warps (3 per CTA, 3 CTAs per SM); a WARP owns a contiguous range of
+//     (row, split, head) units and walks each unit's tokens in tiles of 32 (two KV pages) -- the very
+//     per-warp MMA / online-softmax body of the kernel above, so no cross-warp merge and no CTA barrier;
+//   * every tile arrives by TMA: one 16 x 64 box per page straight out of the paged pools, SWIZZLE_128B
+//     (= the chunk ^ (row & 7) layout ldmatrix wants), completion on an mbarrier; a warp keeps
+//     kStreamStages tiles in flight in its own ring and issues across unit boundaries, so the loads of
+//     the next unit run under the math of this one. The first tiles are issued before the grid
+//     dependency resolves (same ordering argument as above);
+//   * split-KV partials go to the same scratch as above and are merged by decode_combine_kernel.
+constexpr int kStreamWarps = 3;
+constexpr int kStreamStages = 3;
+constexpr int kStreamTile = 32;                         // tokens per tile (two pages)
+constexpr int kStreamTileBytes = 2 * kStreamTile * 128; // K rows + V rows
+constexpr int kStreamMiscBytes = 512;                   // per warp: q parts / result staging
+constexpr int kStreamSmemBytes =
+    kStreamWarps * (kStreamStages * kStreamTileBytes + kStreamMiscBytes) + kStreamWarps * kStreamStages * 8 + 1024;
+constexpr int kStreamCtasPerSm = 3;
+
+struct StreamUnit {   // warp-uniform description of one (row, split, head) unit
+  int b, h, split;
+  int slot;           // < 0: padding row, nothing to do
+  int pos;            // position of the new token
+  int t_begin;        // first token of the split's range
+  int n_tok;          // tokens the unit attends (cached + the new one if it owns it)
+  int n_cached;
+  int own_new;
+  int n_tiles;
+};
+
+__device__ __forceinline__ StreamUnit stream_unit(const DecodeAttnArgs& a, int u) {
+  StreamUnit s;
+  s.h = u % a.n_head;
+  const int bs = u / a.n_head;
+  s.split = bs % a.n_splits;
+  s.b = bs / a.n_splits;
+  s.slot = a.active_slots ? a.active_slots[s.b] : s.b;
+  s.pos = 0, s.t_begin = 0, s.n_tok = 0, s.n_cached = 0, s.own_new = 0, s.n_tiles = 0;
+  if (s.slot < 0) return s;
+  s.pos = a.seq_len[s.slot];
+  const int ctx = s.pos + 1;
+  int chunk = (ctx + a.n_splits - 1) / a.n_splits;
+  chunk = ((chunk + kPageTokens - 1) / kPageTokens) * kPageTokens;
+  s.t_begin = s.split * chunk;
+  const int t_end = min(ctx, s.t_begin + chunk);
+  s.n_tok = max(0, t_end - s.t_begin);
+  s.n_cached = max(0, min(t_end, s.pos) - s.t_begin);
+  s.own_new = (s.pos >= s.t_begin && s.pos < t_end) ? 1 : 0;
+  s.n_tiles = (s.n_tok + kStreamTile - 1) / kStreamTile;
+  return s;
+}
+
+__global__ void __launch_bounds__(kStreamWarps * 32, kStreamCtasPerSm)
+decode_attn_stream_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
+                          const DecodeAttnArgs a) {
+  extern __shared__ uint8_t stream_smem_raw[];
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(stream_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* ring = base + warp * (kStreamStages * kStreamTileBytes);  // [stage]: K rows 0..31, then V rows 0..31
+  uint8_t* misc = base + kStreamWarps * (kStreamStages * kStreamTileBytes) + warp * kStreamMiscBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(base + kStreamWarps * (kStreamStages * kStreamTileBytes + kStreamMiscBytes)) +
+                   warp * kStreamStages;
+  __nv_bfloat16* sq = reinterpret_cast<__nv_bfloat16*>(misc);  // [2][64] q high / low parts
+  float* so = reinterpret_cast<float*>(misc + 256);            // [64] result staging
+  const int d = a.n_head * kHeadDim;
+
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < kStreamStages; ++s) mbar_init(&full[s], 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+
+  // this warp's units: a contiguous range, ordered (row, split, head) so neighbours share the page list
+  const long long total = static_cast<long long>(a.batch) * a.n_splits * a.n_head;
+  const long long gw = static_cast<long long>(blockIdx.x) * kStreamWarps + warp;
+  const long long n_gw = static_cast<long long>(gridDim.x) * kStreamWarps;
+  const int u_begin = static_cast<int>(gw * total / n_gw);
+  const int u_end = static_cast<int>((gw + 1) * total / n_gw);
+
+  // ---- producer cursor: which tile is loaded next ----
+  int pu = u_begin;
+  StreamUnit P = {};
+  int p_tile = 0;
+  uint32_t p_count = 0;        // tiles issued so far
+  int p_pg = 0;                // lane l: page id of page (first page of the range + 32 * refill + l)
+  int p_pg_slot = -1, p_pg_first = -1;
+  auto p_seek = [&]() {        // move to the next unit that has tiles
+    while (pu < u_end) {
+      P = stream_unit(a, pu);
+      if (P.n_tiles > 0) break;
+      ++pu;
+    }
+    p_tile = 0;
+  };
+  auto p_issue = [&]() {       // load tile p_tile of unit P into the next ring slot, advance
+    const int first_page = P.t_begin / kPageTokens + 2 * (p_tile & ~15);
+    if (p_pg_slot != P.slot || p_pg_first != first_page) {
+      const int pi = first_page + lane;
+      p_pg = pi < a.max_pages_per_seq ? a.page_table[static_cast<size_t>(P.slot) * a.max_pages_per_seq + pi] : 0;
+      p_pg_slot = P.slot;
+      p_pg_first = first_page;
+    }
+    const int pg0 = __shfl_sync(0xffffffffu, p_pg, (2 * p_tile) & 31);
+    const int pg1 = __shfl_sync(0xffffffffu, p_pg, (2 * p_tile + 1) & 31);
+    const int rows = min(P.n_tok - p_tile * kStreamTile, kStreamTile);
+    const int n_pg = (rows + kPageTokens - 1) / kPageTokens;  // 1 or 2
+    const uint32_t stage = p_count % kStreamStages;
+    uint8_t* dst = ring + stage * kStreamTileBytes;
+    fence_proxy_async();  // this warp's reads / writes of the slot are ordered before the TMA writes
+    if (lane == 0) mbar_arrive_expect_tx(&full[stage], static_cast<uint32_t>(n_pg) * 2u * kPageTokens * 128u);
+    __syncwarp();
+    if (lane < 2 * n_pg) {
+      const int which = lane & 1;   // 0: K, 1: V
+      const int pgi = lane >> 1;
+      const int page = pgi ? pg1 : pg0;
+      tma_load_2d(dst + which * (kStreamTile * 128) + pgi * (kPageTokens * 128), which ? &map_v : &map_k,
+                  &full[stage], 0, (page * a.n_head + P.h) * kPageTokens, kEvictNormal);
+    }
+    ++p_count;
+    if (++p_tile == P.n_tiles) {
+      ++pu;
+      p_seek();
+    }
+  };
+  p_seek();
+#pragma unroll 1
+  for (int i = 0; i < kStreamStages - 1 && pu < u_end; ++i) p_issue();
+
+  pdl_wait();
+  pdl_launch_dependents();
+
+  // ---- consumer: unit by unit, tile by tile ----
+  uint32_t c_count = 0;  // tiles consumed so far
+#pragma unroll 1
+  for (int u = u_begin; u < u_end; ++u) {
+    const StreamUnit C = stream_unit(a, u);
+    if (C.slot < 0) continue;
+    const int bh = C.b * a.n_head + C.h;
+
+    // This token's q (every split) and k, v (the split that owns the new position): lane l holds
+    // dims 2l, 2l + 1. Split-K planes are summed in plane order (deterministic), bias added here.
+    float2 qv = make_float2(0.f, 0.f), kv = qv, vv = qv;
+    {
+      const size_t col = static_cast<size_t>(C.h) * kHeadDim + 2 * lane;
+      if (a.qkv_partials != nullptr) {
+        const size_t plane = static_cast<size_t>(a.partial_rows) * 3 * d;
+        const float* src = a.qkv_partials + static_cast<size_t>(C.b) * 3 * d + col;
+        qv = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + col));
+        if (C.own_new) {
+          kv = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + d + col));
+          vv = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + 2 * d + col));
+        }
+        for (int s0 = 0; s0 < a.n_qkv_partials; s0 += 4) {
+          float2 x[3][4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {  // all planes of the group requested before anything is summed
+            const bool on = s0 + j < a.n_qkv_partials;
+            const float* p = src + static_cast<size_t>(s0 + j) * plane;
+            x[0][j] = on ? __ldcg(reinterpret_cast<const float2*>(p)) : make_float2(0.f, 0.f);
+            x[1][j] = (on && C.own_new) ? __ldcg(reinterpret_cast<const float2*>(p + d)) : make_float2(0.f, 0.f);
+            x[2][j] = (on && C.own_new) ? __ldcg(reinterpret_cast<const float2*>(p + 2 * d)) : make_float2(0.f, 0.f);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            qv.x += x[0][j].x, qv.y += x[0][j].y;
+            kv.x += x[1][j].x, kv.y += x[1][j].y;
+            vv.x += x[2][j].x, vv.y += x[2][j].y;
+          }
+        }
+      } else {
+        const __nv_bfloat16* src = a.qkv + static_cast<size_t>(C.b) * 3 * d + col;
+        qv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src));
+        if (C.own_new) {
+          kv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src + d));
+          vv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src + 2 * d));
+        }
+      }
+    }
+    const uint32_t k_new = pack_bf16x2(kv.x, kv.y);  // rounded to the cache dtype
+    const uint32_t v_new = pack_bf16x2(vv.x, vv.y);
+    {
+      const float x0 = qv.x * kScaleLog2, x1 = qv.y * kScaleLog2;
+      const __nv_bfloat16 h0 = __float2bfloat16(x0), h1 = __float2bfloat16(x1);
+      __nv_bfloat162 hi, lo;
+      hi.x = h0, hi.y = h1;
+      lo.x = __float2bfloat16(x0 - __bfloat162float(h0));
+      lo.y = __float2bfloat16(x1 - __bfloat162float(h1));
+      __syncwarp();  // the previous unit's readers of this staging area are done
+      reinterpret_cast<__nv_bfloat162*>(sq)[lane] = hi;
+      reinterpret_cast<__nv_bfloat162*>(sq + kHeadDim)[lane] = lo;
+      __syncwarp();
+    }
+    // q as the A operand of all four 16-dim steps: lanes 0..3 carry row 0 (high) and row 8 (low)
+    uint32_t qa[4][4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const int j2 = 2 * (lane & 3);
+      const bool on = lane < 4;
+      qa[s][0] = on ? *reinterpret_cast<const uint32_t*>(&sq[16 * s + j2]) : 0u;
+      qa[s][1] = on ? *reinterpret_cast<const uint32_t*>(&sq[kHeadDim + 16 * s + j2]) : 0u;
+      qa[s][2] = on ? *reinterpret_cast<const uint32_t*>(&sq[16 * s + 8 + j2]) : 0u;
+      qa[s][3] = on ? *reinterpret_cast<const uint32_t*>(&sq[kHeadDim + 16 * s + 8 + j2]) : 0u;
+    }
+    // append this token to its page (kept out of the tile loop: nothing below reads it from global)
+    const bool fin = a.finished != nullptr && a.finished[C.slot] != 0;
+    if (C.own_new && !fin) {
+      const int page = a.page_table[static_cast<size_t>(C.slot) * a.max_pages_per_seq + C.pos / kPageTokens];
+      const size_t dst = ((static_cast<size_t>(page) * a.n_head + C.h) * kPageTokens + C.pos % kPageTokens) * kHeadDim + 2 * lane;
+      *reinterpret_cast<uint32_t*>(a.k_pool + dst) = k_new;
+      *reinterpret_cast<uint32_t*>(a.v_pool + dst) = v_new;
+    }
+
+    float m_run = -INFINITY;  // warp-uniform running max (log2 domain)
+    float l_part = 0.f;       // this lane's share of the running sum (lanes 0..3 matter)
+    float oacc[4][4];
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) oacc[mt][e] = 0.f;
+    }
+#pragma unroll 1
+    for (int t = 0; t < C.n_tiles; ++t) {
+      // keep the ring full: the slot this load goes to was consumed in the previous iteration
+      __syncwarp();
+      if (pu < u_end) p_issue();
+      const uint32_t stage = c_count % kStreamStages;
+      mbar_wait(&full[stage], (c_count / kStreamStages) & 1u);
+      ++c_count;
+      uint4 (*sk)[8] = reinterpret_cast<uint4 (*)[8]>(ring + stage * kStreamTileBytes);
+      uint4 (*sv)[8] = reinterpret_cast<uint4 (*)[8]>(ring + stage * kStreamTileBytes + kStreamTile * 128);
+      const int rows = min(C.n_tok - t * kStreamTile, kStreamTile);
+      {
+        bool touched = false;
+        if (C.own_new && t == C.n_cached / kStreamTile) {  // the new token's row (the page holds no data there yet)
+          const int row = C.n_cached - t * kStreamTile;
+          const int c = (lane >> 2) ^ (row & 7);
+          reinterpret_cast<uint32_t*>(&sk[row][c])[lane & 3] = k_new;
+          reinterpret_cast<uint32_t*>(&sv[row][c])[lane & 3] = v_new;
+          touched = true;
+        }
+        const int rows_pad = ((rows + kPageTokens - 1) / kPageTokens) * kPageTokens;
+        if (rows < rows_pad) {  // V rows of the last page that hold no token: 0 * stale must not be NaN
+          for (int i = rows * 8 + lane; i < rows_pad * 8; i += 32) sv[i >> 3][i & 7] = make_uint4(0u, 0u, 0u, 0u);
+          touched = true;
+        }
+        if (touched) __syncwarp();
+      }
+      float sacc[4][4];
+#pragma unroll
+      for (int tt = 0; tt < 4; ++tt) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) sacc[tt][e] = 0.f;
+      }
+#pragma unroll
+      for (int sp = 0; sp < 2; ++sp) {  // 32 dims per ldmatrix.x4
+#pragma unroll
+        for (int tt = 0; tt < 4; ++tt) {  // 8 tokens per score tile
+          if (8 * tt < rows) {            // warp-uniform; pages that were not loaded are never read
+            uint32_t kb[4];
+            const int row = 8 * tt + (lane & 7);
+            const int c = 4 * sp + (lane >> 3);
+            ldmatrix_x4(kb, &sk[row][c ^ (row & 7)]);
+            mma_bf16_16816(sacc[tt], qa[2 * sp], kb[0], kb[1]);
+            mma_bf16_16816(sacc[tt], qa[2 * sp + 1], kb[2], kb[3]);
+          }
+        }
+      }
+      float s[4][2];
+      bool ok[4][2];
+      float m_loc = -INFINITY;
+#pragma unroll
+      for (int tt = 0; tt < 4; ++tt) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          ok[tt][e] = lane < 4 && (8 * tt + 2 * (lane & 3) + e) < rows;
+          s[tt][e] = sacc[tt][e] + sacc[tt][e + 2];
+          m_loc = ok[tt][e] ? fmaxf(m_loc, s[tt][e]) : m_loc;
+        }
+      }
+      m_loc = fmaxf(m_loc, __shfl_xor_sync(0xffffffffu, m_loc, 1));
+      m_loc = fmaxf(m_loc, __shfl_xor_sync(0xffffffffu, m_loc, 2));
+      m_loc = __shfl_sync(0xffffffffu, m_loc, 0);  // lanes 0..3 own the real scores
+      const float m_new = fmaxf(m_run, m_loc);     // finite: row 0 of a tile is a real token
+      if (m_run != -INFINITY) {                    // warp-uniform
+        const float f = exp2f(m_run - m_new);
+        l_part *= f;
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) oacc[mt][e] *= f;
+        }
+      }
+      m_run = m_new;
+      float p[4][2];
+#pragma unroll
+      for (int tt = 0; tt < 4; ++tt) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          p[tt][e] = ok[tt][e] ? exp2f(s[tt][e] - m_new) : 0.f;
+          l_part += p[tt][e];
+        }
+      }
+#pragma unroll
+      for (int uu = 0; uu < 2; ++uu) {  // 16 tokens (one page) per output tile
+        if (16 * uu < rows) {           // warp-uniform
+          const uint32_t b0 = pack_bf16x2(p[2 * uu][0], p[2 * uu][1]);
+          const uint32_t b1 = pack_bf16x2(p[2 * uu + 1][0], p[2 * uu + 1][1]);
+#pragma unroll
+          for (int mt = 0; mt < 4; ++mt) {  // 16 dims per tile
+            uint32_t va[4];
+            const int row = 16 * uu + ((lane >> 4) << 3) + (lane & 7);
+            const int c = 2 * mt + ((lane >> 3) & 1);
+            ldmatrix_x4_trans(va, &sv[row][c ^ (row & 7)]);
+            mma_bf16_16816(oacc[mt], va, b0, b1);
+          }
+        }
+      }
+    }
+
+    // the unit's result: column 0 of the output tiles lives in lanes 0, 4, ..., 28
+    float l_unit = l_part + __shfl_xor_sync(0xffffffffu, l_part, 1);
+    l_unit += __shfl_xor_sync(0xffffffffu, l_unit, 2);
+    l_unit = __shfl_sync(0xffffffffu, l_unit, 0);
+    __syncwarp();
+    if ((lane & 3) == 0) {
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt) {
+        so[16 * mt + (lane >> 2)] = oacc[mt][0];
+        so[16 * mt + 8 + (lane >> 2)] = oacc[mt][2];
+      }
+    }
+    __syncwarp();
+    const float2 o2 = *reinterpret_cast<const float2*>(&so[2 * lane]);
+    if (a.n_splits == 1) {
+      const float inv = 1.f / l_unit;  // a unit of the only split always holds the new token
+      *reinterpret_cast<uint32_t*>(a.out + static_cast<size_t>(C.b) * d + C.h * kHeadDim + 2 * lane) =
+          pack_bf16x2(o2.x * inv, o2.y * inv);
+    } else {
+      float* sc = a.scratch + (static_cast<size_t>(bh) * a.n_splits + C.split) * kScratchStride;
+      *reinterpret_cast<float2*>(&sc[2 * lane]) = o2;  // an empty split leaves (0, -inf, 0)
+      if (lane == 0) {
+        sc[kHeadDim] = m_run;
+        sc[kHeadDim + 1] = l_unit;
+      }
+    }
+  }
+}
+
 int launch_with_pdl(void (*kernel)(DecodeAttnArgs), dim3 grid, dim3 block, cudaStream_t stream,
                     int pdl, const DecodeAttnArgs& a) {
   cudaLaunchConfig_t cfg = {};
@@ -922,12 +1282,43 @@ extern "C" int b200llm_debug_attn_cta_trace(unsigned long long* out, int n_ctas)
 namespace b200llm {
 #endif
 
+int decode_attention_stream(const DecodeAttnArgs& a, cudaStream_t stream) {
+  B200_CHECK_ARG(a.n_pages > 0, "decode_attention: the streaming kernel needs n_pages (extent of its tensor maps)");
+  const long long pool_rows = static_cast<long long>(a.n_pages) * a.n_head * kPageTokens;
+  B200_CHECK_ARG(pool_rows < (1ll << 31), "decode_attention: KV pool too large for one tensor map");
+  CUtensorMap map_k, map_v;
+  B200_PROPAGATE(gemm_tensor_map(a.k_pool, static_cast<int>(pool_rows), kHeadDim, kPageTokens, &map_k));
+  B200_PROPAGATE(gemm_tensor_map(a.v_pool, static_cast<int>(pool_rows), kHeadDim, kPageTokens, &map_v));
+  B200_CUDA_OK(cudaFuncSetAttribute(decode_attn_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    kStreamSmemBytes));
+  const long long units = static_cast<long long>(a.batch) * a.n_head * a.n_splits;
+  const long long want = (units + kStreamWarps - 1) / kStreamWarps;
+  const long long cap = static_cast<long long>(device_sm_count()) * kStreamCtasPerSm;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(want < cap ? want : cap));
+  cfg.blockDim = dim3(kStreamWarps * 32);
+  cfg.dynamicSmemBytes = kStreamSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = a.pdl ? 1 : 0;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, decode_attn_stream_kernel, map_k, map_v, a));
+  if (a.n_splits > 1) {
+    B200_PROPAGATE(
+        launch_with_pdl(decode_combine_kernel, dim3(a.batch * a.n_head), dim3(64), stream, a.pdl, a));
+  }
+  return kOk;
+}
+
 int decode_attention(const DecodeAttnArgs& a, cudaStream_t stream) {
   B200_CHECK_ARG(a.batch > 0 && a.n_head > 0 && a.n_splits >= 1, "decode_attention: bad shape");
   B200_CHECK_ARG(a.n_splits == 1 || a.scratch != nullptr,
                  "decode_attention: split-KV needs a scratch buffer");
   dim3 grid(a.batch * a.n_head, a.n_splits);
   DecodeAttnArgs args = a;
+  if (args.stream_kernel != 0) return decode_attention_stream(args, stream);
   if (args.n_splits < 2 || args.n_splits > 8) args.cluster_combine = 0;
   if (args.cluster_combine != 0) {
     cudaLaunchConfig_t cfg = {};

@@ -83,6 +83,11 @@ struct DecodeAttnArgs {
   // their partial results through distributed shared memory inside the kernel (no scratch, no
   // combine launch). The engine sets it; the operator entry points keep the scratch path.
   int cluster_combine;
+  // Streaming form (persistent warps, one unit per warp at a time, K/V tiles by TMA): the engine picks
+  // it when the (row, head, split) units outnumber the resident CTAs of the kernel above or contexts
+  // run to several 128-row passes. Needs n_pages (extent of the tensor maps over the pools).
+  int stream_kernel;
+  int n_pages;
 };
 // One decode step of attention: appends this token's K/V to its pages, then attends over
 // positions 0..seq_len (inclusive).

@@ -267,6 +267,7 @@ struct b200llm_engine {
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
   int tune_splits[4] = {0, 0, 0, 0};  // tune build: split-K overrides for qkv, o, fc, proj
   int tune_attn_splits = 0;           // tune build: KV split override
+  int tune_attn_stream = -1;          // tune build: -1 auto, 0 never, 1 always the streaming decode attention (B200LLM_ATTN_STREAM)
   int prefill_attn_mode = -1;         // -1 auto, 0 tcgen05 always, 1 mma.sync always (tune build: B200LLM_PREFILL_ATTN)
   int tune_fused_qkv = -1;            // tune build: 0 / 1 force ln_1 + c_attn as LayerNorm + planes / as the fused kernel
   int tune_lnqkv_split = 0;           // tune build: K split of the light ln_1 + c_attn kernel (0 = LayerNorm + planes GEMM)
@@ -339,6 +340,7 @@ struct StepPlan {
   // cluster (DSMEM) split-K factors; when > 1 they take precedence over the plane splits
   int cl_qkv = 1, cl_o = 1, cl_fc = 1, cl_p = 1;
   int attn_splits = 1;
+  bool attn_stream = false;  // decode attention on the streaming kernel (many units per SM / long contexts)
   int live_rows = 1 << 30;  // decode: sequences in the call (the bucket's other rows are padding)
   int pdl = 0;
   int batch = 0;       // sequences (prefill) / bucket rows (decode)
@@ -489,7 +491,9 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       a.n_splits = p.attn_splits;
       a.scratch = e->attn_scratch;
       a.pdl = pdl;
-      a.cluster_combine = (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
+      a.cluster_combine = (!p.attn_stream && p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
+      a.stream_kernel = p.attn_stream ? 1 : 0;
+      a.n_pages = static_cast<int>(e->n_pages);
       if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
       if (p.attn_splits > 1 && !(a.cluster_combine && p.attn_splits <= 8)) {
         e->launches += 1, e->launches_in_capture += 1;  // separate combine kernel
@@ -565,7 +569,9 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       // small grids (a handful of rows): 2..8 splits are merged inside the kernel, no combine launch.
       // With a thousand CTAs the co-scheduling of whole clusters costs more than the launch it saves
       // (GPT-2 medium, 16 rows x 16 heads x 4 splits: 1148 vs 1014 us per step).
-      a.cluster_combine = (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
+      a.cluster_combine = (!p.attn_stream && p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
+      a.stream_kernel = p.attn_stream ? 1 : 0;
+      a.n_pages = static_cast<int>(e->n_pages);
       if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
       if (p.attn_splits > 1 && !(a.cluster_combine && p.attn_splits <= 8)) {
         e->launches += 1, e->launches_in_capture += 1;  // separate combine kernel
@@ -961,6 +967,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
     std::sscanf(env, "%d,%d", &e->tune_fused_splits[0], &e->tune_fused_splits[1]);
   }
   if (const char* env = std::getenv("B200LLM_ATTN_SPLITS")) e->tune_attn_splits = std::max(1, std::min(16, std::atoi(env)));
+  if (const char* env = std::getenv("B200LLM_ATTN_STREAM")) e->tune_attn_stream = std::atoi(env);
 #endif
   e->d = cfg->d_model;
   e->H = cfg->n_head;
@@ -1490,6 +1497,25 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
       }
     }
     p.attn_splits = splits;
+    // More units than resident CTAs, or several passes per CTA: the streaming kernel (persistent warps,
+    // nine per SM, each walking whole units in 32-token tiles). Its cut: rounds of units per warp x
+    // (tiles per unit + two tiles' worth of per-unit set-up).
+    p.attn_stream = ctas > slots || max_ctx > 2 * 128;
+    if (e->tune_attn_stream >= 0) p.attn_stream = e->tune_attn_stream != 0;
+    if (p.attn_stream) {
+      const int warps = 9 * sms;
+      best = 1e30f;
+      for (int s = 1; s <= 16; ++s) {
+        const int per = (max_ctx + s - 1) / s;
+        if (s > 1 && per < 64) break;
+        const int rounds = (ctas * s + warps - 1) / warps;
+        const float cost = static_cast<float>(rounds) * (static_cast<float>((per + 31) / 32) + 2.f);
+        if (cost < best - 1e-3f) {
+          best = cost;
+          p.attn_splits = s;
+        }
+      }
+    }
     if (e->tune_attn_splits > 0) p.attn_splits = e->tune_attn_splits;
   }
   if (p.fused) {
@@ -1517,7 +1543,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     // (~4 us). The remainder runs on the single-step graph.
     auto get_graph = [&](int steps, b200llm_engine::GraphEntry** out) -> int {
       // (the in-kernel split combine depends on the live row count, so it is part of the key)
-      const int attn_cluster = (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
+      const int attn_cluster = p.attn_stream ? 2 : (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
       b200llm_engine::GraphKey key{bucket, p.attn_splits, need_logits ? 1 : 0, steps, attn_cluster};
       auto it = e->graphs.find(key);
       if (it == e->graphs.end()) {
@@ -1878,6 +1904,30 @@ int b200llm_op_decode_attention(const void* qkv, const int32_t* seq_len, const i
   a.cluster_combine = n_splits < 0 ? 1 : 0;
   a.scratch = scratch;
   a.pdl = 0;
+  return decode_attention(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200llm_op_decode_attention_stream(const void* qkv, const int32_t* seq_len, const int32_t* page_table,
+                                       int32_t max_pages_per_seq, void* k_pool, void* v_pool, int32_t n_pages,
+                                       void* out, int32_t batch, int32_t n_head, int32_t n_splits,
+                                       float* scratch, void* stream) {
+  B200_CHECK_ARG(qkv && seq_len && page_table && k_pool && v_pool && out,
+                 "op_decode_attention_stream: null argument");
+  B200_CHECK_ARG(n_splits >= 1 && n_pages > 0, "op_decode_attention_stream: n_splits and n_pages must be positive");
+  DecodeAttnArgs a = {};
+  a.qkv = static_cast<const __nv_bfloat16*>(qkv);
+  a.seq_len = seq_len;
+  a.page_table = page_table;
+  a.max_pages_per_seq = max_pages_per_seq;
+  a.k_pool = static_cast<__nv_bfloat16*>(k_pool);
+  a.v_pool = static_cast<__nv_bfloat16*>(v_pool);
+  a.out = static_cast<__nv_bfloat16*>(out);
+  a.batch = batch;
+  a.n_head = n_head;
+  a.n_splits = n_splits;
+  a.scratch = scratch;
+  a.stream_kernel = 1;
+  a.n_pages = n_pages;
   return decode_attention(a, reinterpret_cast<cudaStream_t>(stream));
 }
 

@@ -1562,6 +1562,8 @@ int launch_pair(const GemmArgs& g, cudaStream_t stream) {
 
 B200_DEFINE_STEP_TRACE_SETTER(step_trace_set_gemm)
 
+int device_sm_count() { return num_sms(); }
+
 int gemm_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
   return get_tensor_map(ptr, rows, cols, box_rows, out);
 }

@@ -68,6 +68,9 @@ int gemm_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorM
 // The same for an fp32 matrix: boxes of [box_rows, 32 columns] (a box row is again 128 bytes).
 int gemm_tensor_map_f32(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out);
 
+// SM count of the current device (cached per device).
+int device_sm_count();
+
 // Drop cached tensor maps (engine teardown / tests).
 void gemm_clear_tensor_map_cache();
 
