@@ -120,7 +120,7 @@ def _load() -> C.CDLL:
         "b200llm_op_embed": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]),
         "b200llm_op_prefill_attention": (C.c_int, [vp, vp, i32, i32, i32, vp, vp]),
         "b200llm_op_decode_attention": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp]),
-        "b200llm_op_decode_attention_stream": (C.c_int, [vp, vp, vp, i32, vp, vp, i32, vp, i32, i32, i32, vp, vp]),
+        "b200llm_op_decode_attention_stream": (C.c_int, [vp, vp, vp, i32, vp, vp, i32, vp, i32, i32, i32, vp, vp, vp]),
         "b200llm_decode_attention_scratch_floats": (C.c_size_t, [i32, i32, i32]),
         "b200llm_op_decode_attention_noalloc": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp]),
         "b200llm_op_argmax": (C.c_int, [vp, i32, i32, i32, vp, vp]),

@@ -44,7 +44,33 @@ __device__ unsigned long long g_attn_cta_trace[4096][4];
       g_attn_cta_trace[blockIdx.x][3] = _sm;                                               \
     }                                                                                      \
   } while (0)
+#define B200_STRACE_DECL                                                                     \
+  unsigned long long st_acc[6] = {0, 0, 0, 0, 0, 0}, st_t = clock64(), st_t0 = st_t, st_g0; \
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(st_g0));
+#define B200_STRACE(i)                      \
+  do {                                      \
+    const unsigned long long _n = clock64(); \
+    st_acc[i] += _n - st_t;                 \
+    st_t = _n;                              \
+  } while (0)
+#define B200_STRACE_END                                                             \
+  do {                                                                              \
+    if (blockIdx.x == gridDim.x / 2 && threadIdx.x == 0) {                          \
+      for (int _i = 0; _i < 6; ++_i) g_attn_trace[8 + _i] = st_acc[_i];             \
+      g_attn_trace[14] = clock64() - st_t0;                                         \
+      unsigned long long _g;                                                        \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_g));                        \
+      g_attn_trace[15] = _g - st_g0;                                                \
+    }                                                                               \
+  } while (0)
 #else
+#define B200_STRACE_DECL
+#define B200_STRACE(i) \
+  do {                 \
+  } while (0)
+#define B200_STRACE_END \
+  do {                  \
+  } while (0)
 #define B200_ATRACE(slot) \
   do {                    \
   } while (0)
@@ -801,62 +827,91 @@ __global__ void __launch_bounds__(64) decode_combine_kernel(DecodeAttnArgs a) {
 //     the next unit run under the math of this one. The first tiles are issued before the grid
 //     dependency resolves (same ordering argument as above);
 //   * split-KV partials go to the same scratch as above and are merged by decode_combine_kernel.
-constexpr int kStreamWarps = 3;
-constexpr int kStreamStages = 3;
-constexpr int kStreamTile = 32;                         // tokens per tile (two pages)
-constexpr int kStreamTileBytes = 2 * kStreamTile * 128; // K rows + V rows
-constexpr int kStreamMiscBytes = 512;                   // per warp: q parts / result staging
-constexpr int kStreamSmemBytes =
-    kStreamWarps * (kStreamStages * kStreamTileBytes + kStreamMiscBytes) + kStreamWarps * kStreamStages * 8 + 1024;
-constexpr int kStreamCtasPerSm = 3;
-
-struct StreamUnit {   // warp-uniform description of one (row, split, head) unit
-  int b, h, split;
-  int slot;           // < 0: padding row, nothing to do
-  int pos;            // position of the new token
-  int t_begin;        // first token of the split's range
-  int n_tok;          // tokens the unit attends (cached + the new one if it owns it)
-  int n_cached;
-  int own_new;
-  int n_tiles;
+template <int kWarps, int kStages, int kTile>
+struct StreamCfg {
+  static constexpr int kTileBytes = 2 * kTile * 128;  // K rows + V rows
+  static constexpr int kMiscBytes = 640;              // per warp: q parts, result staging, append pages
+  static constexpr int kSmemBytes = kWarps * (kStages * kTileBytes + kMiscBytes) + kWarps * kStages * 8 + 1024;
 };
 
-__device__ __forceinline__ StreamUnit stream_unit(const DecodeAttnArgs& a, int u) {
-  StreamUnit s;
-  s.h = u % a.n_head;
+// Warp-uniform cursor over (row, split, head) units. Moving to the next unit costs a few integer
+// operations; only a new ROW loads anything (its slot, position, finished flag) and divides.
+struct StreamCursor {
+  int u, b, split, h;
+  int slot;      // < 0: padding row
+  int pos;       // position of the row's new token
+  int chunk;     // tokens per split of this row (page-aligned)
+  int fin;       // row is finished: no append
+  // derived for (row, split):
+  int t_begin, n_tok, n_cached, own_new, n_tiles;
+};
+
+__device__ __forceinline__ void stream_load_row(const DecodeAttnArgs& a, StreamCursor& c) {
+  c.slot = a.active_slots ? a.active_slots[c.b] : c.b;
+  c.pos = 0, c.chunk = kPageTokens, c.fin = 0;
+  if (c.slot < 0) return;
+  c.pos = a.seq_len[c.slot];
+  c.fin = a.finished != nullptr ? a.finished[c.slot] : 0;
+  const int chunk = (c.pos + a.n_splits) / a.n_splits;  // ceil((pos + 1) / n_splits)
+  c.chunk = ((chunk + kPageTokens - 1) / kPageTokens) * kPageTokens;
+}
+__device__ __forceinline__ void stream_derive(StreamCursor& c) {
+  c.t_begin = c.split * c.chunk;
+  const int ctx = c.pos + 1;
+  const int t_end = min(ctx, c.t_begin + c.chunk);
+  c.n_tok = c.slot < 0 ? 0 : max(0, t_end - c.t_begin);
+  c.n_cached = max(0, min(t_end, c.pos) - c.t_begin);
+  c.own_new = (c.slot >= 0 && c.pos >= c.t_begin && c.pos < t_end) ? 1 : 0;
+  c.n_tiles = (c.n_tok + 31) >> 5;
+}
+__device__ __forceinline__ void stream_seek(const DecodeAttnArgs& a, StreamCursor& c, int u) {
+  c.u = u;
+  c.h = u % a.n_head;
   const int bs = u / a.n_head;
-  s.split = bs % a.n_splits;
-  s.b = bs / a.n_splits;
-  s.slot = a.active_slots ? a.active_slots[s.b] : s.b;
-  s.pos = 0, s.t_begin = 0, s.n_tok = 0, s.n_cached = 0, s.own_new = 0, s.n_tiles = 0;
-  if (s.slot < 0) return s;
-  s.pos = a.seq_len[s.slot];
-  const int ctx = s.pos + 1;
-  int chunk = (ctx + a.n_splits - 1) / a.n_splits;
-  chunk = ((chunk + kPageTokens - 1) / kPageTokens) * kPageTokens;
-  s.t_begin = s.split * chunk;
-  const int t_end = min(ctx, s.t_begin + chunk);
-  s.n_tok = max(0, t_end - s.t_begin);
-  s.n_cached = max(0, min(t_end, s.pos) - s.t_begin);
-  s.own_new = (s.pos >= s.t_begin && s.pos < t_end) ? 1 : 0;
-  s.n_tiles = (s.n_tok + kStreamTile - 1) / kStreamTile;
-  return s;
+  c.split = bs % a.n_splits;
+  c.b = bs / a.n_splits;
+  stream_load_row(a, c);
+  stream_derive(c);
+}
+__device__ __forceinline__ void stream_next(const DecodeAttnArgs& a, StreamCursor& c, int u_end) {
+  ++c.u;
+  if (++c.h == a.n_head) {
+    c.h = 0;
+    if (++c.split == a.n_splits) {
+      c.split = 0;
+      ++c.b;
+      if (c.u < u_end) stream_load_row(a, c);
+    }
+    stream_derive(c);
+  }
 }
 
+template <int kStreamWarps, int kStreamStages, int kStreamTile, int kStreamCtasPerSm>
 __global__ void __launch_bounds__(kStreamWarps * 32, kStreamCtasPerSm)
 decode_attn_stream_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
                           const DecodeAttnArgs a) {
-  extern __shared__ uint8_t stream_smem_raw[];
+  using Cfg = StreamCfg<kStreamWarps, kStreamStages, kStreamTile>;
+  constexpr int kStreamTileBytes = Cfg::kTileBytes;
+  constexpr int kStreamMiscBytes = Cfg::kMiscBytes;
+  constexpr int kTilePages = kStreamTile / kPageTokens;
+  static_assert(kStreamTile == 32, "two pages per tile");
+  // (only dynamic shared memory in this kernel: the array starts at offset 0 of the CTA's window, so the
+  // SWIZZLE_128B tiles are 1024-byte aligned; no pointer arithmetic through integers, which would turn
+  // every shared-memory access below into a generic one)
+  extern __shared__ __align__(1024) uint8_t stream_smem_raw[];
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(stream_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* base = stream_smem_raw;
   uint8_t* ring = base + warp * (kStreamStages * kStreamTileBytes);  // [stage]: K rows 0..31, then V rows 0..31
   uint8_t* misc = base + kStreamWarps * (kStreamStages * kStreamTileBytes) + warp * kStreamMiscBytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(base + kStreamWarps * (kStreamStages * kStreamTileBytes + kStreamMiscBytes)) +
                    warp * kStreamStages;
   __nv_bfloat16* sq = reinterpret_cast<__nv_bfloat16*>(misc);  // [2][64] q high / low parts
   float* so = reinterpret_cast<float*>(misc + 256);            // [64] result staging
+  int* apg = reinterpret_cast<int*>(misc + 512);               // [stage] page that takes the new token (set with the unit's last tile)
   const int d = a.n_head * kHeadDim;
+  B200_STRACE_DECL
+  B200_ATRACE_CTA(0);
 
   if (lane == 0) {
 #pragma unroll
@@ -865,145 +920,161 @@ decode_attn_stream_kernel(const __grid_constant__ CUtensorMap map_k, const __gri
   }
   __syncwarp();
 
-  // this warp's units: a contiguous range, ordered (row, split, head) so neighbours share the page list
+  // this warp's units: a contiguous range, ordered (row, split, head) so neighbours share the row's data
   const long long total = static_cast<long long>(a.batch) * a.n_splits * a.n_head;
   const long long gw = static_cast<long long>(blockIdx.x) * kStreamWarps + warp;
   const long long n_gw = static_cast<long long>(gridDim.x) * kStreamWarps;
   const int u_begin = static_cast<int>(gw * total / n_gw);
   const int u_end = static_cast<int>((gw + 1) * total / n_gw);
+  if (u_begin >= u_end) {
+    pdl_wait();
+    pdl_launch_dependents();
+    return;
+  }
 
   // ---- producer cursor: which tile is loaded next ----
-  int pu = u_begin;
-  StreamUnit P = {};
+  StreamCursor P;
+  stream_seek(a, P, u_begin);
   int p_tile = 0;
   uint32_t p_count = 0;        // tiles issued so far
   int p_pg = 0;                // lane l: page id of page (first page of the range + 32 * refill + l)
   int p_pg_slot = -1, p_pg_first = -1;
-  auto p_seek = [&]() {        // move to the next unit that has tiles
-    while (pu < u_end) {
-      P = stream_unit(a, pu);
-      if (P.n_tiles > 0) break;
-      ++pu;
-    }
+  auto p_skip_empty = [&]() {  // move to the next unit that has tiles
+    while (P.u < u_end && P.n_tiles == 0) stream_next(a, P, u_end);
     p_tile = 0;
   };
   auto p_issue = [&]() {       // load tile p_tile of unit P into the next ring slot, advance
-    const int first_page = P.t_begin / kPageTokens + 2 * (p_tile & ~15);
+    const int first_page = P.t_begin / kPageTokens + ((p_tile * kTilePages) & ~31);
     if (p_pg_slot != P.slot || p_pg_first != first_page) {
       const int pi = first_page + lane;
       p_pg = pi < a.max_pages_per_seq ? a.page_table[static_cast<size_t>(P.slot) * a.max_pages_per_seq + pi] : 0;
       p_pg_slot = P.slot;
       p_pg_first = first_page;
     }
-    const int pg0 = __shfl_sync(0xffffffffu, p_pg, (2 * p_tile) & 31);
-    const int pg1 = __shfl_sync(0xffffffffu, p_pg, (2 * p_tile + 1) & 31);
+    const int pgi = lane >> 1;  // lane 2j loads K of the tile's page j, lane 2j + 1 its V
+    const int page = __shfl_sync(0xffffffffu, p_pg, (p_tile * kTilePages + pgi) & 31);
     const int rows = min(P.n_tok - p_tile * kStreamTile, kStreamTile);
-    const int n_pg = (rows + kPageTokens - 1) / kPageTokens;  // 1 or 2
+    const int n_pg = (rows + kPageTokens - 1) / kPageTokens;
     const uint32_t stage = p_count % kStreamStages;
     uint8_t* dst = ring + stage * kStreamTileBytes;
-    fence_proxy_async();  // this warp's reads / writes of the slot are ordered before the TMA writes
     if (lane == 0) mbar_arrive_expect_tx(&full[stage], static_cast<uint32_t>(n_pg) * 2u * kPageTokens * 128u);
-    __syncwarp();
     if (lane < 2 * n_pg) {
       const int which = lane & 1;   // 0: K, 1: V
-      const int pgi = lane >> 1;
-      const int page = pgi ? pg1 : pg0;
       tma_load_2d(dst + which * (kStreamTile * 128) + pgi * (kPageTokens * 128), which ? &map_v : &map_k,
                   &full[stage], 0, (page * a.n_head + P.h) * kPageTokens, kEvictNormal);
+      // the unit's last tile of the split that owns the new token: remember the page it is appended to
+      if (which == 0 && P.own_new && p_tile == P.n_tiles - 1 && pgi == n_pg - 1) apg[stage] = page;
     }
     ++p_count;
     if (++p_tile == P.n_tiles) {
-      ++pu;
-      p_seek();
+      stream_next(a, P, u_end);
+      p_skip_empty();
     }
   };
-  p_seek();
+  p_skip_empty();
 #pragma unroll 1
-  for (int i = 0; i < kStreamStages - 1 && pu < u_end; ++i) p_issue();
+  for (int i = 0; i < kStreamStages - 1 && P.u < u_end; ++i) p_issue();
 
   pdl_wait();
   pdl_launch_dependents();
+  B200_STRACE(0);  // start-up: first units, first tiles issued, grid dependency
 
   // ---- consumer: unit by unit, tile by tile ----
+  // The projection of the NEXT unit is requested before this unit's tiles are walked and used after
+  // them: under the KV stream an L2 access takes microseconds, so nothing on the unit path waits for a
+  // load that could have been asked for earlier.
+  constexpr int kPre = 4;   // planes of the next unit's projection held in registers
+  float2 nx0[kPre], nx1[kPre], nx2[kPre], nb0, nb1, nb2;
+  auto fetch = [&](int b, int h) {  // issue the loads of a unit's q / k / v (lane l: dims 2l, 2l + 1); no use here
+    const size_t col = static_cast<size_t>(h) * kHeadDim + 2 * lane;
+    if (a.qkv_partials != nullptr) {
+      const size_t plane = static_cast<size_t>(a.partial_rows) * 3 * d;
+      const float* src = a.qkv_partials + static_cast<size_t>(b) * 3 * d + col;
+      nb0 = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + col));
+      nb1 = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + d + col));
+      nb2 = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + 2 * d + col));
+#pragma unroll
+      for (int j = 0; j < kPre; ++j) {
+        const bool on = j < a.n_qkv_partials;
+        const float* p = src + static_cast<size_t>(j) * plane;
+        nx0[j] = on ? __ldcg(reinterpret_cast<const float2*>(p)) : make_float2(0.f, 0.f);
+        nx1[j] = on ? __ldcg(reinterpret_cast<const float2*>(p + d)) : make_float2(0.f, 0.f);
+        nx2[j] = on ? __ldcg(reinterpret_cast<const float2*>(p + 2 * d)) : make_float2(0.f, 0.f);
+      }
+    } else {
+      const __nv_bfloat16* src = a.qkv + static_cast<size_t>(b) * 3 * d + col;
+      nx0[0].x = __uint_as_float(__ldcg(reinterpret_cast<const unsigned int*>(src)));
+      nx1[0].x = __uint_as_float(__ldcg(reinterpret_cast<const unsigned int*>(src + d)));
+      nx2[0].x = __uint_as_float(__ldcg(reinterpret_cast<const unsigned int*>(src + 2 * d)));
+    }
+  };
+  StreamCursor C;
+  stream_seek(a, C, u_begin);
+  fetch(C.b, C.h);
+
   uint32_t c_count = 0;  // tiles consumed so far
 #pragma unroll 1
-  for (int u = u_begin; u < u_end; ++u) {
-    const StreamUnit C = stream_unit(a, u);
-    if (C.slot < 0) continue;
-    const int bh = C.b * a.n_head + C.h;
-
-    // This token's q (every split) and k, v (the split that owns the new position): lane l holds
-    // dims 2l, 2l + 1. Split-K planes are summed in plane order (deterministic), bias added here.
-    float2 qv = make_float2(0.f, 0.f), kv = qv, vv = qv;
-    {
-      const size_t col = static_cast<size_t>(C.h) * kHeadDim + 2 * lane;
-      if (a.qkv_partials != nullptr) {
+  for (; C.u < u_end; stream_next(a, C, u_end)) {
+    // this unit's q, k, v from the prefetched values (split-K planes summed in plane order, bias added)
+    float2 vq, vk, vv;
+    if (a.qkv_partials != nullptr) {
+      vq = nb0, vk = nb1, vv = nb2;
+#pragma unroll
+      for (int j = 0; j < kPre; ++j) {
+        vq.x += nx0[j].x, vq.y += nx0[j].y;
+        vk.x += nx1[j].x, vk.y += nx1[j].y;
+        vv.x += nx2[j].x, vv.y += nx2[j].y;
+      }
+      if (a.n_qkv_partials > kPre) {  // more planes than the prefetch holds: the rest on demand
         const size_t plane = static_cast<size_t>(a.partial_rows) * 3 * d;
-        const float* src = a.qkv_partials + static_cast<size_t>(C.b) * 3 * d + col;
-        qv = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + col));
-        if (C.own_new) {
-          kv = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + d + col));
-          vv = __ldg(reinterpret_cast<const float2*>(a.qkv_bias + 2 * d + col));
-        }
-        for (int s0 = 0; s0 < a.n_qkv_partials; s0 += 4) {
-          float2 x[3][4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {  // all planes of the group requested before anything is summed
-            const bool on = s0 + j < a.n_qkv_partials;
-            const float* p = src + static_cast<size_t>(s0 + j) * plane;
-            x[0][j] = on ? __ldcg(reinterpret_cast<const float2*>(p)) : make_float2(0.f, 0.f);
-            x[1][j] = (on && C.own_new) ? __ldcg(reinterpret_cast<const float2*>(p + d)) : make_float2(0.f, 0.f);
-            x[2][j] = (on && C.own_new) ? __ldcg(reinterpret_cast<const float2*>(p + 2 * d)) : make_float2(0.f, 0.f);
-          }
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            qv.x += x[0][j].x, qv.y += x[0][j].y;
-            kv.x += x[1][j].x, kv.y += x[1][j].y;
-            vv.x += x[2][j].x, vv.y += x[2][j].y;
-          }
-        }
-      } else {
-        const __nv_bfloat16* src = a.qkv + static_cast<size_t>(C.b) * 3 * d + col;
-        qv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src));
-        if (C.own_new) {
-          kv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src + d));
-          vv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src + 2 * d));
+        const float* src = a.qkv_partials + static_cast<size_t>(C.b) * 3 * d + static_cast<size_t>(C.h) * kHeadDim + 2 * lane;
+        for (int j = kPre; j < a.n_qkv_partials; ++j) {
+          const float* p = src + static_cast<size_t>(j) * plane;
+          const float2 x0 = __ldcg(reinterpret_cast<const float2*>(p));
+          const float2 x1 = __ldcg(reinterpret_cast<const float2*>(p + d));
+          const float2 x2 = __ldcg(reinterpret_cast<const float2*>(p + 2 * d));
+          vq.x += x0.x, vq.y += x0.y, vk.x += x1.x, vk.y += x1.y, vv.x += x2.x, vv.y += x2.y;
         }
       }
+    } else {
+      const uint32_t w0 = __float_as_uint(nx0[0].x), w1 = __float_as_uint(nx1[0].x), w2 = __float_as_uint(nx2[0].x);
+      vq = make_float2(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xffff0000u));
+      vk = make_float2(__uint_as_float(w1 << 16), __uint_as_float(w1 & 0xffff0000u));
+      vv = make_float2(__uint_as_float(w2 << 16), __uint_as_float(w2 & 0xffff0000u));
     }
-    const uint32_t k_new = pack_bf16x2(kv.x, kv.y);  // rounded to the cache dtype
+    if (C.u + 1 < u_end) {  // the next unit: next head of this row, or head 0 of the next (row, split)
+      const bool wrap = C.h + 1 == a.n_head;
+      fetch((wrap && C.split + 1 == a.n_splits) ? C.b + 1 : C.b, wrap ? 0 : C.h + 1);
+    }
+    if (C.slot < 0) continue;
+    const int bh = C.b * a.n_head + C.h;
+    const uint32_t k_new = pack_bf16x2(vk.x, vk.y);  // rounded to the cache dtype
     const uint32_t v_new = pack_bf16x2(vv.x, vv.y);
+    // q (scaled for exp2) as the A operand of the score MMAs: lanes 0..3 carry row 0 (bf16 high part) and
+    // row 8 (low part) of the four 16-dim steps, so c0 + c2 is the score at ~fp32 query precision
+    uint32_t qa[4][4];
     {
-      const float x0 = qv.x * kScaleLog2, x1 = qv.y * kScaleLog2;
+      const float x0 = vq.x * kScaleLog2, x1 = vq.y * kScaleLog2;
       const __nv_bfloat16 h0 = __float2bfloat16(x0), h1 = __float2bfloat16(x1);
       __nv_bfloat162 hi, lo;
       hi.x = h0, hi.y = h1;
       lo.x = __float2bfloat16(x0 - __bfloat162float(h0));
       lo.y = __float2bfloat16(x1 - __bfloat162float(h1));
-      __syncwarp();  // the previous unit's readers of this staging area are done
+      __syncwarp();  // the previous unit's readers of the staging area are done
       reinterpret_cast<__nv_bfloat162*>(sq)[lane] = hi;
       reinterpret_cast<__nv_bfloat162*>(sq + kHeadDim)[lane] = lo;
       __syncwarp();
-    }
-    // q as the A operand of all four 16-dim steps: lanes 0..3 carry row 0 (high) and row 8 (low)
-    uint32_t qa[4][4];
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
       const int j2 = 2 * (lane & 3);
       const bool on = lane < 4;
-      qa[s][0] = on ? *reinterpret_cast<const uint32_t*>(&sq[16 * s + j2]) : 0u;
-      qa[s][1] = on ? *reinterpret_cast<const uint32_t*>(&sq[kHeadDim + 16 * s + j2]) : 0u;
-      qa[s][2] = on ? *reinterpret_cast<const uint32_t*>(&sq[16 * s + 8 + j2]) : 0u;
-      qa[s][3] = on ? *reinterpret_cast<const uint32_t*>(&sq[kHeadDim + 16 * s + 8 + j2]) : 0u;
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        qa[s][0] = on ? *reinterpret_cast<const uint32_t*>(&sq[16 * s + j2]) : 0u;
+        qa[s][1] = on ? *reinterpret_cast<const uint32_t*>(&sq[kHeadDim + 16 * s + j2]) : 0u;
+        qa[s][2] = on ? *reinterpret_cast<const uint32_t*>(&sq[16 * s + 8 + j2]) : 0u;
+        qa[s][3] = on ? *reinterpret_cast<const uint32_t*>(&sq[kHeadDim + 16 * s + 8 + j2]) : 0u;
+      }
     }
-    // append this token to its page (kept out of the tile loop: nothing below reads it from global)
-    const bool fin = a.finished != nullptr && a.finished[C.slot] != 0;
-    if (C.own_new && !fin) {
-      const int page = a.page_table[static_cast<size_t>(C.slot) * a.max_pages_per_seq + C.pos / kPageTokens];
-      const size_t dst = ((static_cast<size_t>(page) * a.n_head + C.h) * kPageTokens + C.pos % kPageTokens) * kHeadDim + 2 * lane;
-      *reinterpret_cast<uint32_t*>(a.k_pool + dst) = k_new;
-      *reinterpret_cast<uint32_t*>(a.v_pool + dst) = v_new;
-    }
+    B200_STRACE(1);  // unit set-up
 
     float m_run = -INFINITY;  // warp-uniform running max (log2 domain)
     float l_part = 0.f;       // this lane's share of the running sum (lanes 0..3 matter)
@@ -1017,87 +1088,90 @@ decode_attn_stream_kernel(const __grid_constant__ CUtensorMap map_k, const __gri
     for (int t = 0; t < C.n_tiles; ++t) {
       // keep the ring full: the slot this load goes to was consumed in the previous iteration
       __syncwarp();
-      if (pu < u_end) p_issue();
+      if (P.u < u_end) p_issue();
+      B200_STRACE(2);  // issuing the next tile
       const uint32_t stage = c_count % kStreamStages;
       mbar_wait(&full[stage], (c_count / kStreamStages) & 1u);
       ++c_count;
+      B200_STRACE(3);  // waiting for the tile
       uint4 (*sk)[8] = reinterpret_cast<uint4 (*)[8]>(ring + stage * kStreamTileBytes);
       uint4 (*sv)[8] = reinterpret_cast<uint4 (*)[8]>(ring + stage * kStreamTileBytes + kStreamTile * 128);
       const int rows = min(C.n_tok - t * kStreamTile, kStreamTile);
-      {
-        bool touched = false;
-        if (C.own_new && t == C.n_cached / kStreamTile) {  // the new token's row (the page holds no data there yet)
-          const int row = C.n_cached - t * kStreamTile;
+      if (t == C.n_tiles - 1) {  // the unit's last tile: the new token's row, rows past the last token
+        if (C.own_new) {
+          const int row = C.n_cached - t * kStreamTile;  // (the page holds no data there yet)
           const int c = (lane >> 2) ^ (row & 7);
           reinterpret_cast<uint32_t*>(&sk[row][c])[lane & 3] = k_new;
           reinterpret_cast<uint32_t*>(&sv[row][c])[lane & 3] = v_new;
-          touched = true;
-        }
-        const int rows_pad = ((rows + kPageTokens - 1) / kPageTokens) * kPageTokens;
-        if (rows < rows_pad) {  // V rows of the last page that hold no token: 0 * stale must not be NaN
-          for (int i = rows * 8 + lane; i < rows_pad * 8; i += 32) sv[i >> 3][i & 7] = make_uint4(0u, 0u, 0u, 0u);
-          touched = true;
-        }
-        if (touched) __syncwarp();
-      }
-      float sacc[4][4];
-#pragma unroll
-      for (int tt = 0; tt < 4; ++tt) {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) sacc[tt][e] = 0.f;
-      }
-#pragma unroll
-      for (int sp = 0; sp < 2; ++sp) {  // 32 dims per ldmatrix.x4
-#pragma unroll
-        for (int tt = 0; tt < 4; ++tt) {  // 8 tokens per score tile
-          if (8 * tt < rows) {            // warp-uniform; pages that were not loaded are never read
-            uint32_t kb[4];
-            const int row = 8 * tt + (lane & 7);
-            const int c = 4 * sp + (lane >> 3);
-            ldmatrix_x4(kb, &sk[row][c ^ (row & 7)]);
-            mma_bf16_16816(sacc[tt], qa[2 * sp], kb[0], kb[1]);
-            mma_bf16_16816(sacc[tt], qa[2 * sp + 1], kb[2], kb[3]);
+          if (!C.fin) {  // ... and it is appended to its page (nothing here reads it back from global memory)
+            __syncwarp();
+            const size_t dst = ((static_cast<size_t>(apg[stage]) * a.n_head + C.h) * kPageTokens + C.pos % kPageTokens) * kHeadDim + 2 * lane;
+            *reinterpret_cast<uint32_t*>(a.k_pool + dst) = k_new;
+            *reinterpret_cast<uint32_t*>(a.v_pool + dst) = v_new;
           }
         }
+        const int rows_pad = ((rows + kPageTokens - 1) / kPageTokens) * kPageTokens;
+        // V rows of the last page that hold no token: 0 * stale must not be NaN
+        for (int i = rows * 8 + lane; i < rows_pad * 8; i += 32) sv[i >> 3][i & 7] = make_uint4(0u, 0u, 0u, 0u);
+        fence_proxy_async();  // these writes are ordered before the TMA load that reuses the slot
+        __syncwarp();
       }
-      float s[4][2];
+      // scores = K rows (ldmatrix) x q: 8 tokens per tile; the two 32-dim halves accumulate separately
+      // (two dependent MMAs per chain instead of four). Rows without a token are masked below.
+      float sacc[2][4][4];
+#pragma unroll
+      for (int sp = 0; sp < 2; ++sp) {
+#pragma unroll
+        for (int tt = 0; tt < 4; ++tt) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) sacc[sp][tt][e] = 0.f;
+          uint32_t kb[4];
+          const int row = 8 * tt + (lane & 7);
+          const int c = 4 * sp + (lane >> 3);
+          ldmatrix_x4(kb, &sk[row][c ^ (row & 7)]);
+          mma_bf16_16816(sacc[sp][tt], qa[2 * sp], kb[0], kb[1]);
+          mma_bf16_16816(sacc[sp][tt], qa[2 * sp + 1], kb[2], kb[3]);
+        }
+      }
+      float sc[4][2];
       bool ok[4][2];
       float m_loc = -INFINITY;
 #pragma unroll
       for (int tt = 0; tt < 4; ++tt) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-          ok[tt][e] = lane < 4 && (8 * tt + 2 * (lane & 3) + e) < rows;
-          s[tt][e] = sacc[tt][e] + sacc[tt][e + 2];
-          m_loc = ok[tt][e] ? fmaxf(m_loc, s[tt][e]) : m_loc;
+          ok[tt][e] = lane < 4 && (8 * tt + 2 * (lane & 3) + e) < rows;  // lanes 0..3 own the real scores
+          sc[tt][e] = (sacc[0][tt][e] + sacc[0][tt][e + 2]) + (sacc[1][tt][e] + sacc[1][tt][e + 2]);
+          m_loc = ok[tt][e] ? fmaxf(m_loc, sc[tt][e]) : m_loc;
         }
       }
-      m_loc = fmaxf(m_loc, __shfl_xor_sync(0xffffffffu, m_loc, 1));
-      m_loc = fmaxf(m_loc, __shfl_xor_sync(0xffffffffu, m_loc, 2));
-      m_loc = __shfl_sync(0xffffffffu, m_loc, 0);  // lanes 0..3 own the real scores
-      const float m_new = fmaxf(m_run, m_loc);     // finite: row 0 of a tile is a real token
-      if (m_run != -INFINITY) {                    // warp-uniform
-        const float f = exp2f(m_run - m_new);
-        l_part *= f;
-#pragma unroll
-        for (int mt = 0; mt < 4; ++mt) {
-#pragma unroll
-          for (int e = 0; e < 4; ++e) oacc[mt][e] *= f;
-        }
-      }
+      // warp maximum with one redux: floats ordered as signed integers
+      int key = __float_as_int(m_loc);
+      key = key >= 0 ? key : key ^ 0x7fffffff;
+      key = __reduce_max_sync(0xffffffffu, key);
+      m_loc = __int_as_float(key >= 0 ? key : key ^ 0x7fffffff);
+      const float m_new = fmaxf(m_run, m_loc);  // finite: row 0 of a tile is a real token
+      const float f = exp2f(m_run - m_new);     // 0 on the first tile
       m_run = m_new;
+      l_part *= f;
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) oacc[mt][e] *= f;
+      }
       float p[4][2];
 #pragma unroll
       for (int tt = 0; tt < 4; ++tt) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-          p[tt][e] = ok[tt][e] ? exp2f(s[tt][e] - m_new) : 0.f;
+          p[tt][e] = ok[tt][e] ? exp2f(sc[tt][e] - m_new) : 0.f;
           l_part += p[tt][e];
         }
       }
+      // output = V^T (ldmatrix.trans) x weights, which sit in the B-fragment layout the score tiles left them in
 #pragma unroll
-      for (int uu = 0; uu < 2; ++uu) {  // 16 tokens (one page) per output tile
-        if (16 * uu < rows) {           // warp-uniform
+      for (int uu = 0; uu < kTilePages; ++uu) {
+        if (16 * uu < rows) {  // warp-uniform: a page that was not loaded is never read
           const uint32_t b0 = pack_bf16x2(p[2 * uu][0], p[2 * uu][1]);
           const uint32_t b1 = pack_bf16x2(p[2 * uu + 1][0], p[2 * uu + 1][1]);
 #pragma unroll
@@ -1110,9 +1184,11 @@ decode_attn_stream_kernel(const __grid_constant__ CUtensorMap map_k, const __gri
           }
         }
       }
+      B200_STRACE(4);  // math
     }
 
-    // the unit's result: column 0 of the output tiles lives in lanes 0, 4, ..., 28
+    // the unit's result: column 0 of the output tiles lives in lanes 0, 4, ..., 28; through shared memory
+    // to lane l = dims 2l, 2l + 1
     float l_unit = l_part + __shfl_xor_sync(0xffffffffu, l_part, 1);
     l_unit += __shfl_xor_sync(0xffffffffu, l_unit, 2);
     l_unit = __shfl_sync(0xffffffffu, l_unit, 0);
@@ -1131,14 +1207,46 @@ decode_attn_stream_kernel(const __grid_constant__ CUtensorMap map_k, const __gri
       *reinterpret_cast<uint32_t*>(a.out + static_cast<size_t>(C.b) * d + C.h * kHeadDim + 2 * lane) =
           pack_bf16x2(o2.x * inv, o2.y * inv);
     } else {
-      float* sc = a.scratch + (static_cast<size_t>(bh) * a.n_splits + C.split) * kScratchStride;
+      float* sc0 = a.scratch + static_cast<size_t>(bh) * a.n_splits * kScratchStride;
+      float* sc = sc0 + C.split * kScratchStride;
       *reinterpret_cast<float2*>(&sc[2 * lane]) = o2;  // an empty split leaves (0, -inf, 0)
       if (lane == 0) {
         sc[kHeadDim] = m_run;
         sc[kHeadDim + 1] = l_unit;
       }
+      if (a.split_counters != nullptr) {
+        // The split that finishes last merges all of them, in split order (so the result does not depend
+        // on who that is), and leaves the counter at zero for the next launch: no combine kernel.
+        __threadfence();
+        __syncwarp();
+        int prev = 0;
+        if (lane == 0) prev = atomicAdd(a.split_counters + bh, 1);
+        prev = __shfl_sync(0xffffffffu, prev, 0);
+        if (prev == a.n_splits - 1) {
+          __threadfence();
+          float m = -INFINITY;
+          for (int s = 0; s < a.n_splits; ++s) m = fmaxf(m, __ldcg(sc0 + s * kScratchStride + kHeadDim));
+          float l = 0.f;
+          float2 o = make_float2(0.f, 0.f);
+          for (int s = 0; s < a.n_splits; ++s) {
+            const float ms = __ldcg(sc0 + s * kScratchStride + kHeadDim);
+            const float fs = (ms == -INFINITY) ? 0.f : exp2f(ms - m);
+            const float2 os = __ldcg(reinterpret_cast<const float2*>(sc0 + s * kScratchStride + 2 * lane));
+            l = fmaf(__ldcg(sc0 + s * kScratchStride + kHeadDim + 1), fs, l);
+            o.x = fmaf(os.x, fs, o.x);
+            o.y = fmaf(os.y, fs, o.y);
+          }
+          const float inv = 1.f / l;
+          *reinterpret_cast<uint32_t*>(a.out + static_cast<size_t>(C.b) * d + C.h * kHeadDim + 2 * lane) =
+              pack_bf16x2(o.x * inv, o.y * inv);
+          if (lane == 0) a.split_counters[bh] = 0;
+        }
+      }
     }
+    B200_STRACE(5);  // result
   }
+  B200_STRACE_END;
+  B200_ATRACE_CTA(2);
 }
 
 int launch_with_pdl(void (*kernel)(DecodeAttnArgs), dim3 grid, dim3 block, cudaStream_t stream,
@@ -1282,6 +1390,30 @@ extern "C" int b200llm_debug_attn_cta_trace(unsigned long long* out, int n_ctas)
 namespace b200llm {
 #endif
 
+template <int kWarps, int kStages, int kTile, int kCtasPerSm>
+int launch_stream(const CUtensorMap& map_k, const CUtensorMap& map_v, const DecodeAttnArgs& a, cudaStream_t stream) {
+  auto kernel = decode_attn_stream_kernel<kWarps, kStages, kTile, kCtasPerSm>;
+  constexpr int smem = StreamCfg<kWarps, kStages, kTile>::kSmemBytes;
+  B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  // Persistent: every SM gets its full set of CTAs when there are units enough (warps of one SM share its
+  // bandwidth and issue slots, so what has to be even is the work per SM, not per warp).
+  const long long units = static_cast<long long>(a.batch) * a.n_head * a.n_splits;
+  const long long want = (units + kWarps - 1) / kWarps;
+  const long long cap = static_cast<long long>(device_sm_count()) * kCtasPerSm;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(want < cap ? want : cap));
+  cfg.blockDim = dim3(kWarps * 32);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = a.pdl ? 1 : 0;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, map_k, map_v, a));
+  return kOk;
+}
+
 int decode_attention_stream(const DecodeAttnArgs& a, cudaStream_t stream) {
   B200_CHECK_ARG(a.n_pages > 0, "decode_attention: the streaming kernel needs n_pages (extent of its tensor maps)");
   const long long pool_rows = static_cast<long long>(a.n_pages) * a.n_head * kPageTokens;
@@ -1289,23 +1421,15 @@ int decode_attention_stream(const DecodeAttnArgs& a, cudaStream_t stream) {
   CUtensorMap map_k, map_v;
   B200_PROPAGATE(gemm_tensor_map(a.k_pool, static_cast<int>(pool_rows), kHeadDim, kPageTokens, &map_k));
   B200_PROPAGATE(gemm_tensor_map(a.v_pool, static_cast<int>(pool_rows), kHeadDim, kPageTokens, &map_v));
-  B200_CUDA_OK(cudaFuncSetAttribute(decode_attn_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    kStreamSmemBytes));
-  const long long units = static_cast<long long>(a.batch) * a.n_head * a.n_splits;
-  const long long want = (units + kStreamWarps - 1) / kStreamWarps;
-  const long long cap = static_cast<long long>(device_sm_count()) * kStreamCtasPerSm;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(static_cast<unsigned>(want < cap ? want : cap));
-  cfg.blockDim = dim3(kStreamWarps * 32);
-  cfg.dynamicSmemBytes = kStreamSmemBytes;
-  cfg.stream = stream;
-  cudaLaunchAttribute attrs[1];
-  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attrs[0].val.programmaticStreamSerializationAllowed = a.pdl ? 1 : 0;
-  cfg.attrs = attrs;
-  cfg.numAttrs = 1;
-  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, decode_attn_stream_kernel, map_k, map_v, a));
-  if (a.n_splits > 1) {
+  // stream_kernel selects the instance: 1 = the engine's (see the table in DESIGN.md), others for A/B runs
+  switch (a.stream_kernel) {
+    case 2: B200_PROPAGATE((launch_stream<3, 3, 32, 3>(map_k, map_v, a, stream))); break;
+    case 3: B200_PROPAGATE((launch_stream<4, 3, 32, 2>(map_k, map_v, a, stream))); break;
+    case 4: B200_PROPAGATE((launch_stream<2, 2, 32, 6>(map_k, map_v, a, stream))); break;
+    case 5: B200_PROPAGATE((launch_stream<2, 4, 32, 3>(map_k, map_v, a, stream))); break;
+    default: B200_PROPAGATE((launch_stream<4, 2, 32, 3>(map_k, map_v, a, stream))); break;
+  }
+  if (a.n_splits > 1 && a.split_counters == nullptr) {
     B200_PROPAGATE(
         launch_with_pdl(decode_combine_kernel, dim3(a.batch * a.n_head), dim3(64), stream, a.pdl, a));
   }

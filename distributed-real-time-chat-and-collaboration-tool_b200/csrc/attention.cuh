@@ -88,6 +88,10 @@ struct DecodeAttnArgs {
   // run to several 128-row passes. Needs n_pages (extent of the tensor maps over the pools).
   int stream_kernel;
   int n_pages;
+  // Streaming form with n_splits > 1: [batch * n_head] counters, zero before the first launch and left
+  // at zero by every launch; the split of a (row, head) that finishes last merges them in the kernel.
+  // Null: decode_combine_kernel is launched instead.
+  int32_t* split_counters;
 };
 // One decode step of attention: appends this token's K/V to its pages, then attends over
 // positions 0..seq_len (inclusive).

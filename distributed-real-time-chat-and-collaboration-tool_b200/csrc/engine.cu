@@ -221,6 +221,7 @@ struct b200llm_engine {
   float* partials = nullptr;
   size_t partials_floats = 0;
   float* attn_scratch = nullptr;
+  int32_t* attn_counters = nullptr;
   size_t attn_scratch_floats = 0;
   int32_t *ids_dev = nullptr, *row_pos = nullptr, *row_slot = nullptr, *cu_dev = nullptr,
           *slots_dev = nullptr, *last_rows = nullptr, *active_dev = nullptr, *status_dev = nullptr;
@@ -267,7 +268,8 @@ struct b200llm_engine {
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
   int tune_splits[4] = {0, 0, 0, 0};  // tune build: split-K overrides for qkv, o, fc, proj
   int tune_attn_splits = 0;           // tune build: KV split override
-  int tune_attn_stream = -1;          // tune build: -1 auto, 0 never, 1 always the streaming decode attention (B200LLM_ATTN_STREAM)
+  int tune_attn_stream = -1;          // tune build: -1 auto, 0 never, >= 1 always the streaming decode attention, instance n (B200LLM_ATTN_STREAM)
+  int tune_attn_merge = 0;            // tune build: 1 = in-kernel split merge instead of the combine kernel (B200LLM_ATTN_MERGE; measured slower)
   int prefill_attn_mode = -1;         // -1 auto, 0 tcgen05 always, 1 mma.sync always (tune build: B200LLM_PREFILL_ATTN)
   int tune_fused_qkv = -1;            // tune build: 0 / 1 force ln_1 + c_attn as LayerNorm + planes / as the fused kernel
   int tune_lnqkv_split = 0;           // tune build: K split of the light ln_1 + c_attn kernel (0 = LayerNorm + planes GEMM)
@@ -341,6 +343,7 @@ struct StepPlan {
   int cl_qkv = 1, cl_o = 1, cl_fc = 1, cl_p = 1;
   int attn_splits = 1;
   bool attn_stream = false;  // decode attention on the streaming kernel (many units per SM / long contexts)
+  int attn_stream_instance = 1;
   int live_rows = 1 << 30;  // decode: sequences in the call (the bucket's other rows are padding)
   int pdl = 0;
   int batch = 0;       // sequences (prefill) / bucket rows (decode)
@@ -492,10 +495,11 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       a.scratch = e->attn_scratch;
       a.pdl = pdl;
       a.cluster_combine = (!p.attn_stream && p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
-      a.stream_kernel = p.attn_stream ? 1 : 0;
+      a.stream_kernel = p.attn_stream ? p.attn_stream_instance : 0;
       a.n_pages = static_cast<int>(e->n_pages);
+      a.split_counters = (p.attn_stream && e->tune_attn_merge) ? e->attn_counters : nullptr;
       if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
-      if (p.attn_splits > 1 && !(a.cluster_combine && p.attn_splits <= 8)) {
+      if (p.attn_splits > 1 && a.split_counters == nullptr && !(a.cluster_combine && p.attn_splits <= 8)) {
         e->launches += 1, e->launches_in_capture += 1;  // separate combine kernel
       }
       // attn c_proj + residual (:223, :282): x += attn . W_o + b_o, K splits added in L2
@@ -570,10 +574,11 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       // With a thousand CTAs the co-scheduling of whole clusters costs more than the launch it saves
       // (GPT-2 medium, 16 rows x 16 heads x 4 splits: 1148 vs 1014 us per step).
       a.cluster_combine = (!p.attn_stream && p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
-      a.stream_kernel = p.attn_stream ? 1 : 0;
+      a.stream_kernel = p.attn_stream ? p.attn_stream_instance : 0;
       a.n_pages = static_cast<int>(e->n_pages);
+      a.split_counters = (p.attn_stream && e->tune_attn_merge) ? e->attn_counters : nullptr;
       if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
-      if (p.attn_splits > 1 && !(a.cluster_combine && p.attn_splits <= 8)) {
+      if (p.attn_splits > 1 && a.split_counters == nullptr && !(a.cluster_combine && p.attn_splits <= 8)) {
         e->launches += 1, e->launches_in_capture += 1;  // separate combine kernel
       }
     } else {
@@ -968,6 +973,7 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   }
   if (const char* env = std::getenv("B200LLM_ATTN_SPLITS")) e->tune_attn_splits = std::max(1, std::min(16, std::atoi(env)));
   if (const char* env = std::getenv("B200LLM_ATTN_STREAM")) e->tune_attn_stream = std::atoi(env);
+  if (const char* env = std::getenv("B200LLM_ATTN_MERGE")) e->tune_attn_merge = std::atoi(env);
 #endif
   e->d = cfg->d_model;
   e->H = cfg->n_head;
@@ -1135,6 +1141,9 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   E_TRY(dev_alloc_t(e.get(), &e->partials, e->partials_floats));
   e->attn_scratch_floats = decode_attention_scratch_floats(dec_rows, H, 16);
   E_TRY(dev_alloc_t(e.get(), &e->attn_scratch, e->attn_scratch_floats));
+  // counters of the in-kernel split merge: zero now, and every launch leaves them at zero
+  E_TRY(dev_alloc_t(e.get(), &e->attn_counters, static_cast<size_t>(dec_rows) * H));
+  E_CUDA(cudaMemset(e->attn_counters, 0, static_cast<size_t>(dec_rows) * H * sizeof(int32_t)));
   E_TRY(dev_alloc_t(e.get(), &e->ids_dev, R));
   E_TRY(dev_alloc_t(e.get(), &e->row_pos, R));
   E_TRY(dev_alloc_t(e.get(), &e->row_slot, R));
@@ -1498,23 +1507,40 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     }
     p.attn_splits = splits;
     // More units than resident CTAs, or several passes per CTA: the streaming kernel (persistent warps,
-    // nine per SM, each walking whole units in 32-token tiles). Its cut: rounds of units per warp x
+    // twelve per SM, each walking whole units in 32-token tiles). Its cut: rounds of units per warp x
     // (tiles per unit + two tiles' worth of per-unit set-up).
-    p.attn_stream = ctas > slots || max_ctx > 2 * 128;
+    // (one or a few live rows stay on the kernel above, whose splits merge inside a cluster: one request
+    // at context 500 takes 233 us per step there, 273 us here)
+    p.attn_stream = ctas > slots || (max_ctx > 2 * 128 && p.live_rows * e->H * splits > 2 * sms);
     if (e->tune_attn_stream >= 0) p.attn_stream = e->tune_attn_stream != 0;
     if (p.attn_stream) {
-      const int warps = 9 * sms;
-      best = 1e30f;
-      for (int s = 1; s <= 16; ++s) {
-        const int per = (max_ctx + s - 1) / s;
-        if (s > 1 && per < 64) break;
-        const int rounds = (ctas * s + warps - 1) / warps;
-        const float cost = static_cast<float>(rounds) * (static_cast<float>((per + 31) / 32) + 2.f);
-        if (cost < best - 1e-3f) {
-          best = cost;
-          p.attn_splits = s;
+      // Two instances: nine warps per SM with three tiles in their rings when that seats every unit at
+      // once (long contexts: GPT-2 medium, 16 rows x 16 heads x 5 splits at context 1100: 835 vs 853 us
+      // per step), twelve warps with two tiles otherwise (GPT-2 large, 256 rows: 2690 vs 2748 us).
+      auto cut = [&](int warps, int* out_splits) {
+        float best_cost = 1e30f;
+        for (int s = 1; s <= 16; ++s) {
+          const int per = (max_ctx + s - 1) / s;
+          if (s > 1 && per < 64) break;
+          const int rounds = (ctas * s + warps - 1) / warps;
+          const float cost = static_cast<float>(rounds) * (static_cast<float>((per + 31) / 32) + 2.f);
+          if (cost < best_cost - 1e-3f) {
+            best_cost = cost;
+            *out_splits = s;
+          }
         }
+      };
+      int s9 = 1, s12 = 1;
+      cut(9 * sms, &s9);
+      cut(12 * sms, &s12);
+      if (ctas * s9 <= 9 * sms) {
+        p.attn_stream_instance = 2;
+        p.attn_splits = s9;
+      } else {
+        p.attn_stream_instance = 1;
+        p.attn_splits = s12;
       }
+      if (e->tune_attn_stream >= 1 && e->tune_attn_stream <= 5) p.attn_stream_instance = e->tune_attn_stream;  // (9: forced on, instance by the rule)
     }
     if (e->tune_attn_splits > 0) p.attn_splits = e->tune_attn_splits;
   }
@@ -1543,7 +1569,7 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     // (~4 us). The remainder runs on the single-step graph.
     auto get_graph = [&](int steps, b200llm_engine::GraphEntry** out) -> int {
       // (the in-kernel split combine depends on the live row count, so it is part of the key)
-      const int attn_cluster = p.attn_stream ? 2 : (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
+      const int attn_cluster = p.attn_stream ? 1 + p.attn_stream_instance : (p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
       b200llm_engine::GraphKey key{bucket, p.attn_splits, need_logits ? 1 : 0, steps, attn_cluster};
       auto it = e->graphs.find(key);
       if (it == e->graphs.end()) {
@@ -1910,7 +1936,7 @@ int b200llm_op_decode_attention(const void* qkv, const int32_t* seq_len, const i
 int b200llm_op_decode_attention_stream(const void* qkv, const int32_t* seq_len, const int32_t* page_table,
                                        int32_t max_pages_per_seq, void* k_pool, void* v_pool, int32_t n_pages,
                                        void* out, int32_t batch, int32_t n_head, int32_t n_splits,
-                                       float* scratch, void* stream) {
+                                       float* scratch, int32_t* split_counters, void* stream) {
   B200_CHECK_ARG(qkv && seq_len && page_table && k_pool && v_pool && out,
                  "op_decode_attention_stream: null argument");
   B200_CHECK_ARG(n_splits >= 1 && n_pages > 0, "op_decode_attention_stream: n_splits and n_pages must be positive");
@@ -1928,6 +1954,7 @@ int b200llm_op_decode_attention_stream(const void* qkv, const int32_t* seq_len, 
   a.scratch = scratch;
   a.stream_kernel = 1;
   a.n_pages = n_pages;
+  a.split_counters = split_counters;
   return decode_attention(a, reinterpret_cast<cudaStream_t>(stream));
 }
 

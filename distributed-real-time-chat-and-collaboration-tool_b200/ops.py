@@ -77,10 +77,11 @@ def decode_attention_scratch_floats(batch: int, n_head: int, n_splits: int) -> i
 def decode_attention(qkv: torch.Tensor, seq_len: torch.Tensor, page_table: torch.Tensor,
                      k_pool: torch.Tensor, v_pool: torch.Tensor, n_head: int, n_splits: int = 1,
                      scratch: torch.Tensor | None = None, cluster: bool = False,
-                     streaming: bool = False) -> torch.Tensor:
+                     streaming: bool = False, counters: torch.Tensor | None = None) -> torch.Tensor:
     """`cluster`: merge the 2..8 KV splits inside the kernel over a thread-block cluster (what the
     engine does for a few live rows) instead of through scratch + a combine launch. `streaming`: the
-    persistent-warp / TMA form of the kernel (large batches, long contexts)."""
+    persistent-warp / TMA form of the kernel (large batches, long contexts); with `counters` (zeroed
+    int32 [batch * n_head]) its KV splits are merged inside the kernel, without the combine launch."""
     batch = qkv.shape[0]
     d = n_head * 64
     out = torch.zeros(batch, d, dtype=torch.bfloat16, device=qkv.device)
@@ -91,7 +92,7 @@ def decode_attention(qkv: torch.Tensor, seq_len: torch.Tensor, page_table: torch
         check(lib.b200llm_op_decode_attention_stream(_ptr(qkv), _ptr(seq_len), _ptr(page_table),
                                                      page_table.shape[1], _ptr(k_pool), _ptr(v_pool),
                                                      k_pool.shape[0], _ptr(out), batch, n_head, n_splits,
-                                                     _ptr(scratch), _stream()))
+                                                     _ptr(scratch), _ptr(counters), _stream()))
         return out
     check(lib.b200llm_op_decode_attention(_ptr(qkv), _ptr(seq_len), _ptr(page_table),
                                           page_table.shape[1], _ptr(k_pool), _ptr(v_pool), _ptr(out),

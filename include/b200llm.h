@@ -321,12 +321,15 @@ size_t b200llm_decode_attention_scratch_floats(int32_t batch, int32_t n_head, in
  * (row, head, split) units, K/V tiles of two pages fetched by TMA into a per-warp ring. The engine
  * runs it when the units outnumber the resident CTAs of the kernel above or contexts run to several
  * 128-row passes (large batches, long conversations). n_pages = pages in each pool (extent of the
- * tensor maps); n_splits >= 1, scratch as above. Same results up to fp32 summation order. */
+ * tensor maps); n_splits >= 1, scratch as above. split_counters_dev: null, or batch * n_head int32
+ * that are zero before the first call (every call leaves them at zero): the split of a (row, head)
+ * that finishes last then merges them inside the kernel (in split order) and no combine kernel is
+ * launched -- the engine's setting. Same results up to fp32 summation order. */
 int b200llm_op_decode_attention_stream(const void* qkv_dev, const int32_t* seq_len_dev,
                                        const int32_t* page_table_dev, int32_t max_pages_per_seq,
                                        void* k_pool_dev, void* v_pool_dev, int32_t n_pages, void* out_dev,
                                        int32_t batch, int32_t n_head, int32_t n_splits, float* scratch_dev,
-                                       void* stream);
+                                       int32_t* split_counters_dev, void* stream);
 
 /*
  * b200llm_op_decode_attention without a scratch argument. (No counterpart in the reference: it

@@ -1,8 +1,8 @@
 """Decode-step time with the two decode-attention kernels (tune build, one process, several engines).
 
     B200LLM_LIB=<pkg>/libb200llm_tune.so python profiles/attn_stream_probe.py workload [K=V;K=V ...]
-Without extra arguments: B200LLM_ATTN_STREAM=0 (one CTA per unit, cp.async passes) against =1 (persistent
-warps, TMA tiles), each with the engine's own split choice; further arguments are environments to add,
+Without extra arguments: B200LLM_ATTN_STREAM=0 (one CTA per unit, cp.async passes) against =9 (persistent
+warps, TMA tiles; 1..5 force an instance) and the engine's own choice, each with the engine's split rule; further arguments are environments to add,
 e.g. "B200LLM_ATTN_STREAM=1;B200LLM_ATTN_SPLITS=4"."""
 import importlib
 import os
@@ -31,7 +31,7 @@ stream = torch.cuda.Stream()
 chunk = max(1, min(B, 16384 // T))
 SP = E.SamplingParams(N, N)
 steps = min(N - 1, 63)
-KNOBS = ("B200LLM_ATTN_STREAM", "B200LLM_ATTN_SPLITS", "B200LLM_SKIP")
+KNOBS = ("B200LLM_ATTN_STREAM", "B200LLM_ATTN_SPLITS", "B200LLM_ATTN_MERGE", "B200LLM_SKIP")
 
 
 def run(env: dict):
@@ -59,7 +59,7 @@ def run(env: dict):
     return best, toks
 
 
-cases = [{"B200LLM_ATTN_STREAM": "0"}, {"B200LLM_ATTN_STREAM": "1"}]
+cases = [{"B200LLM_ATTN_STREAM": "0"}, {"B200LLM_ATTN_STREAM": "9"}, {}]
 for sp in sys.argv[2:]:
     cases.append(dict(kv.split("=") for kv in sp.split(";")))
 ref = None

@@ -1,0 +1,127 @@
+// Profiling tool: the streaming decode attention kernel alone, at a (rows, heads, context, splits)
+// shape, scattered pages, cold L2: event timing per instance and the achieved algorithmic GB/s.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -I<pkg>/csrc profiles/attn_stream_trace.cu -lcuda -o /tmp/attn_stream_trace
+//   /tmp/attn_stream_trace rows heads ctx splits [qkv planes]
+#include <cstdio>
+#include <string>
+#include <vector>
+#include <numeric>
+#include <algorithm>
+#include <random>
+
+#include <cuda.h>
+#include "attention.cu"
+
+namespace b200llm {
+static thread_local std::string g_err;
+void set_last_error(const std::string& m) { g_err = m; }
+int fail(int code, const std::string& m) { g_err = m; fprintf(stderr, "error: %s\n", m.c_str()); return code; }
+int device_sm_count() { int n = 0; cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, 0); return n; }
+int gemm_tensor_map(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = cuTensorMapEncodeTiled(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
+                                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : fail(2, "cuTensorMapEncodeTiled");
+}
+}  // namespace b200llm
+using namespace b200llm;
+
+// keeps the SMs busy long enough for the clocks to reach their boost state before anything is timed
+__global__ void spin_kernel(float* out, long long iters) {
+  float x = threadIdx.x;
+  for (long long i = 0; i < iters; ++i) x = fmaf(x, 1.0000001f, 0.5f);
+  if (x == 123.f) *out = x;
+}
+
+int main(int argc, char** argv) {
+  const int B = argc > 1 ? atoi(argv[1]) : 256, H = argc > 2 ? atoi(argv[2]) : 20, d = H * 64;
+  const int ctx = argc > 3 ? atoi(argv[3]) : 96, splits = argc > 4 ? atoi(argv[4]) : 1;
+  const int planes = argc > 5 ? atoi(argv[5]) : 0;
+  const int max_pages = (ctx + 1 + 15) / 16 + 1;
+  const int n_pages = B * max_pages;
+  std::vector<int> perm(n_pages); std::iota(perm.begin(), perm.end(), 0);
+  std::shuffle(perm.begin(), perm.end(), std::mt19937(1));
+  int *pt, *seq; __nv_bfloat16 *kp, *vp, *qkv, *out; float *scratch, *partials, *bias;
+  cudaMalloc(&pt, n_pages * 4); cudaMemcpy(pt, perm.data(), n_pages * 4, cudaMemcpyHostToDevice);
+  std::vector<int> sl(B, ctx);
+  cudaMalloc(&seq, B * 4); cudaMemcpy(seq, sl.data(), B * 4, cudaMemcpyHostToDevice);
+  size_t pool = (size_t)n_pages * H * 16 * 64;
+  cudaMalloc(&kp, pool * 2); cudaMalloc(&vp, pool * 2); cudaMemset(kp, 0, pool * 2); cudaMemset(vp, 0, pool * 2);
+  cudaMalloc(&qkv, (size_t)B * 3 * d * 2); cudaMemset(qkv, 0, (size_t)B * 3 * d * 2);
+  cudaMalloc(&partials, (size_t)std::max(planes, 1) * B * 3 * d * 4); cudaMemset(partials, 0, (size_t)std::max(planes, 1) * B * 3 * d * 4);
+  cudaMalloc(&bias, 3 * d * 4); cudaMemset(bias, 0, 3 * d * 4);
+  cudaMalloc(&out, (size_t)B * d * 2);
+  cudaMalloc(&scratch, decode_attention_scratch_floats(B, H, 16) * 4 + 16);
+  int* counters; cudaMalloc(&counters, (size_t)B * H * 4); cudaMemset(counters, 0, (size_t)B * H * 4);
+  DecodeAttnArgs a = {};
+  a.qkv = planes ? nullptr : qkv; a.qkv_partials = planes ? partials : nullptr; a.n_qkv_partials = planes; a.partial_rows = B;
+  a.qkv_bias = bias;
+  a.seq_len = seq; a.page_table = pt; a.max_pages_per_seq = max_pages; a.k_pool = kp; a.v_pool = vp;
+  a.out = out; a.batch = B; a.n_head = H; a.n_splits = splits; a.scratch = scratch; a.n_pages = n_pages;
+  void* flush; cudaMalloc(&flush, 256 << 20);
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const double bytes = (double)B * H * ctx * 256;
+  printf("rows %d heads %d ctx %d splits %d planes %d: %.1f MB of KV\n", B, H, ctx, splits, planes, bytes / 1e6);
+  spin_kernel<<<148 * 4, 256>>>(reinterpret_cast<float*>(flush), 60000000ll);  // ~0.3 s
+  cudaDeviceSynchronize();
+  for (int variant = 0; variant <= 5; ++variant) {
+    a.stream_kernel = variant;
+    a.split_counters = (variant > 0 && argc > 6) ? counters : nullptr;  // 6th argument: merge the splits in the kernel
+    if (decode_attention(a, 0) != 0) return 1;
+    cudaDeviceSynchronize();
+    float best = 1e9;
+    for (int r = 0; r < 5; ++r) {
+      cudaMemset(flush, r, 256 << 20);
+      // what the step has just written is L2-resident: the projection, and the small tables
+      cudaMemset(partials, 0, (size_t)std::max(planes, 1) * B * 3 * d * 4); cudaMemset(qkv, 0, (size_t)B * 3 * d * 2);
+      cudaMemcpy(seq, sl.data(), B * 4, cudaMemcpyHostToDevice); cudaMemcpy(pt, perm.data(), n_pages * 4, cudaMemcpyHostToDevice);
+      spin_kernel<<<148 * 4, 256>>>(reinterpret_cast<float*>(flush), 2000000ll);  // ~10 ms: clocks stay up
+#ifdef B200_ATTN_TRACE
+      { static unsigned long long zero[4096][4]; cudaMemcpyToSymbol(g_attn_cta_trace, zero, sizeof(zero)); }
+#endif
+      cudaDeviceSynchronize();
+      cudaEventRecord(e0); decode_attention(a, 0); cudaEventRecord(e1); cudaDeviceSynchronize();
+      float ms; cudaEventElapsedTime(&ms, e0, e1); best = std::min(best, ms);
+    }
+    cudaError_t err = cudaGetLastError();
+    printf("  variant %d%s: cold %.2f us (%.0f GB/s algorithmic)%s\n", variant, variant == 0 ? " (one CTA per unit)" : "", best * 1e3,
+           bytes / (best * 1e-3) / 1e9, err == cudaSuccess ? "" : cudaGetErrorString(err));
+#ifdef B200_ATTN_TRACE
+    if (variant > 0) {
+      unsigned long long t[16]; cudaMemcpyFromSymbol(t, g_attn_trace, sizeof(t));
+      printf("      one warp, cycles: start-up %llu, unit set-up %llu, issue %llu, wait %llu, math %llu, result %llu | total %llu in %llu ns\n",
+             t[8], t[9], t[10], t[11], t[12], t[13], t[14], t[15]);
+      static unsigned long long ct[4096][4];
+      cudaMemcpyFromSymbol(ct, g_attn_cta_trace, sizeof(ct));
+      const int n = 4096;
+      unsigned long long s_min = ~0ull, s_max = 0, e_min = ~0ull, e_max = 0; double dur = 0; int cnt = 0;
+      for (int i = 0; i < n; ++i) {
+        if (ct[i][0] == 0 || ct[i][2] < ct[i][0]) continue;
+        s_min = std::min(s_min, ct[i][0]); s_max = std::max(s_max, ct[i][0]); e_min = std::min(e_min, ct[i][2]); e_max = std::max(e_max, ct[i][2]);
+        dur += ct[i][2] - ct[i][0]; ++cnt;
+      }
+      printf("      warp 0 of %d CTAs: starts spread over %llu ns, first end +%llu ns, last end +%llu ns, mean lifetime %.0f ns\n", cnt,
+             s_max - s_min, e_min - s_min, e_max - s_min, dur / std::max(cnt, 1));
+      if (variant == 1) {  // which SMs finish when
+        std::vector<std::pair<unsigned long long, int>> by_sm;
+        std::vector<unsigned long long> sm_end(256, 0);
+        for (int i = 0; i < n; ++i) {
+          if (ct[i][0] == 0 || ct[i][2] < ct[i][0]) continue;
+          const int sm = (int)ct[i][3];
+          sm_end[sm] = std::max(sm_end[sm], ct[i][2] - s_min);
+        }
+        for (int sm = 0; sm < 256; ++sm) if (sm_end[sm]) by_sm.push_back({sm_end[sm], sm});
+        std::sort(by_sm.begin(), by_sm.end());
+        printf("      SM end times (us:sm):");
+        for (size_t i = 0; i < by_sm.size(); i += 6) printf(" %.1f:%d", by_sm[i].first / 1e3, by_sm[i].second);
+        printf(" ... last %.1f:%d\n", by_sm.back().first / 1e3, by_sm.back().second);
+      }
+    }
+#endif
+  }
+  return 0;
+}

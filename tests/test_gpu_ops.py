@@ -252,12 +252,13 @@ def test_prefill_attention(ops, cuda, lens, n_head):
     ([1100, 3, 64, 700], 16, 16),
     ([300, 299], 20, 2),
 ])
-@pytest.mark.parametrize("mode", ["scratch-combine", "cluster-combine", "streaming"])
+@pytest.mark.parametrize("mode", ["scratch-combine", "cluster-combine", "streaming", "streaming-merge"])
 def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, mode):
     """seq_len[b] tokens are cached; the new token (position seq_len[b]) is appended by the
     kernel, then attends over everything including itself. `cluster` = 1 makes 2..8 KV splits merge
     inside the kernel (the engine's setting) instead of through scratch + a combine launch; `streaming`
-    is the persistent-warp / TMA form of the kernel the engine runs for large batches and long contexts."""
+    is the persistent-warp / TMA form of the kernel the engine runs for large batches and long contexts
+    (`streaming-merge`: its splits merged inside the kernel through zeroed counters, as the engine does)."""
     cluster = mode == "cluster-combine"
     if cluster and not 2 <= n_splits <= 8:
         pytest.skip("the in-cluster combine only exists for 2..8 splits")
@@ -283,9 +284,16 @@ def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, mode):
             v_pool[p, :, t % page] = v[t]
     qkv = (torch.randn(B, 3 * d, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
     seq_len = torch.tensor(ctx_lens, dtype=torch.int32, device=cuda)
+    counters = torch.zeros(B * n_head, dtype=torch.int32, device=cuda) if mode == "streaming-merge" else None
     out = ops.decode_attention(qkv, seq_len, page_table, k_pool, v_pool, n_head, n_splits, cluster=cluster,
-                               streaming=mode == "streaming")
+                               streaming=mode.startswith("streaming"), counters=counters)
     torch.cuda.synchronize()
+    if counters is not None:
+        assert int(counters.abs().sum()) == 0  # left at zero for the next launch ...
+        again = ops.decode_attention(qkv, seq_len, page_table, k_pool, v_pool, n_head, n_splits, streaming=True,
+                                     counters=counters)
+        torch.cuda.synchronize()
+        assert torch.equal(out, again)         # ... whose merge runs in split order whoever finishes last
     for b, L in enumerate(ctx_lens):
         cur = qkv[b].view(3, n_head, 64)
         k_all = torch.cat([ks[b], cur[1][None]], 0)
