@@ -1509,9 +1509,12 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
     // More units than resident CTAs, or several passes per CTA: the streaming kernel (persistent warps,
     // twelve per SM, each walking whole units in 32-token tiles). Its cut: rounds of units per warp x
     // (tiles per unit + two tiles' worth of per-unit set-up).
-    // (one or a few live rows stay on the kernel above, whose splits merge inside a cluster: one request
-    // at context 500 takes 233 us per step there, 273 us here)
-    p.attn_stream = ctas > slots || (max_ctx > 2 * 128 && p.live_rows * e->H * splits > 2 * sms);
+    // It takes over by KV volume: from ~4096 tiles of 32 tokens per layer (~33 MB). Measured, us per step,
+    // kernel above -> streaming: 64 x 12 heads at context 144 (3456 tiles) 343 -> 345, at 192 387 -> 380, at
+    // 256 445 -> 408, at 512 641 -> 515; 16 x 12 at 512 (3072 tiles) 321 -> 335; 32 x 20 at 96 1094 -> 1139,
+    // at 256 1417 -> 1302; 16 x 16 at 1100 968 -> 835; 256 x 20 at 96 3300 -> 2675; one request at context
+    // 500 (192 tiles; the kernel above merges its splits inside a cluster) 233 -> 273.
+    p.attn_stream = static_cast<long long>(p.live_rows) * e->H * ((max_ctx + 31) / 32) >= 4096;
     if (e->tune_attn_stream >= 0) p.attn_stream = e->tune_attn_stream != 0;
     if (p.attn_stream) {
       // Two instances: nine warps per SM with three tiles in their rings when that seats every unit at
