@@ -12,6 +12,10 @@
 //   K/V byte read once; both products on the tensor cores (mma.sync m16n8k16, query split into
 //   two bf16 parts), online softmax per warp. Optional split-KV for long contexts, merged
 //   deterministically by a combine pass or, for small grids, inside a thread-block cluster.
+//
+// decode_attn_stream_kernel : the same step when the KV volume is large (many (row, head) units per SM,
+//   long contexts): persistent warps that each walk whole units in 32-token tiles fetched by TMA from
+//   the paged pools into a per-warp mbarrier ring; see the comment above the kernel.
 #include "attention.cuh"
 
 #include <cuda.h>
@@ -1421,12 +1425,15 @@ int decode_attention_stream(const DecodeAttnArgs& a, cudaStream_t stream) {
   CUtensorMap map_k, map_v;
   B200_PROPAGATE(gemm_tensor_map(a.k_pool, static_cast<int>(pool_rows), kHeadDim, kPageTokens, &map_k));
   B200_PROPAGATE(gemm_tensor_map(a.v_pool, static_cast<int>(pool_rows), kHeadDim, kPageTokens, &map_v));
-  // stream_kernel selects the instance: 1 = the engine's (see the table in DESIGN.md), others for A/B runs
+  // stream_kernel selects the instance (the engine's rule is next to its plan): 1 = four warps x two-tile
+  // rings, 2 = three warps x three-tile rings; the others exist in tune / profiling builds only
   switch (a.stream_kernel) {
     case 2: B200_PROPAGATE((launch_stream<3, 3, 32, 3>(map_k, map_v, a, stream))); break;
+#ifdef B200_TUNE_KNOBS
     case 3: B200_PROPAGATE((launch_stream<4, 3, 32, 2>(map_k, map_v, a, stream))); break;
     case 4: B200_PROPAGATE((launch_stream<2, 2, 32, 6>(map_k, map_v, a, stream))); break;
     case 5: B200_PROPAGATE((launch_stream<2, 4, 32, 3>(map_k, map_v, a, stream))); break;
+#endif
     default: B200_PROPAGATE((launch_stream<4, 2, 32, 3>(map_k, map_v, a, stream))); break;
   }
   if (a.n_splits > 1 && a.split_counters == nullptr) {

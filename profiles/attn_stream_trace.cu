@@ -1,6 +1,7 @@
 // Profiling tool: the streaming decode attention kernel alone, at a (rows, heads, context, splits)
 // shape, scattered pages, cold L2: event timing per instance and the achieved algorithmic GB/s.
-//   nvcc -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -I<pkg>/csrc profiles/attn_stream_trace.cu -lcuda -o /tmp/attn_stream_trace
+//   nvcc -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -DB200_ATTN_TRACE -DB200_TUNE_KNOBS -I<pkg>/csrc \
+//        profiles/attn_stream_trace.cu -lcuda -o profiles/attn_stream_trace
 //   /tmp/attn_stream_trace rows heads ctx splits [qkv planes]
 #include <cstdio>
 #include <string>
