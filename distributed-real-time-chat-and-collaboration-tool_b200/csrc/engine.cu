@@ -266,6 +266,8 @@ struct b200llm_engine {
   int steps_per_graph = 4;  // decode steps captured per CUDA graph (B200LLM_STEPS_PER_GRAPH overrides)
   int act_via_tma = 0;  // B200LLM_ACT_TMA=1: decode GEMMs fetch activations through TMA (comparison aid)
   int pair_mode = -1;  // GemmArgs::use_pair for the prefill GEMMs (env B200LLM_PAIR overrides)
+  int pair_split = -1; // GemmArgs::pair_split: K splits of the residual prefill GEMMs (-1 by the wave model; 1 when
+                       // cfg.decode_reduce == 1 asks for the ordered, bit-reproducible path; tune build: B200LLM_PAIR_SPLIT)
   int tune_splits[4] = {0, 0, 0, 0};  // tune build: split-K overrides for qkv, o, fc, proj
   int tune_attn_splits = 0;           // tune build: KV split override
   int tune_attn_stream = -1;          // tune build: -1 auto, 0 never, >= 1 always the streaming decode attention, instance n (B200LLM_ATTN_STREAM)
@@ -378,6 +380,7 @@ int gemm(b200llm_engine* e, const __nv_bfloat16* act, const __nv_bfloat16* w, co
   GemmArgs g = {};
   g.cluster_split = cluster_split;
   g.use_pair = e->pair_mode;
+  g.pair_split = e->pair_split;
   g.act = act;
   g.w = w;
   g.bias = bias;
@@ -974,7 +977,10 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   if (const char* env = std::getenv("B200LLM_ATTN_SPLITS")) e->tune_attn_splits = std::max(1, std::min(16, std::atoi(env)));
   if (const char* env = std::getenv("B200LLM_ATTN_STREAM")) e->tune_attn_stream = std::atoi(env);
   if (const char* env = std::getenv("B200LLM_ATTN_MERGE")) e->tune_attn_merge = std::atoi(env);
+  if (const char* env = std::getenv("B200LLM_PAIR_SPLIT")) e->pair_split = std::atoi(env);
 #endif
+  // the ordered reductions (planes, cluster) promise bit-reproducible results: one add per output element
+  if (cfg->decode_reduce == 1 || cfg->decode_reduce == 2) e->pair_split = 1;
   e->d = cfg->d_model;
   e->H = cfg->n_head;
   e->L = cfg->n_layer;
@@ -1864,6 +1870,10 @@ int b200llm_op_gemm(const void* act, const void* w, const float* bias, void* out
   g.act_rows_alloc = tokens;
   g.force_orientation = orientation == 2 ? 0 : orientation;
   g.use_pair = orientation == 2 ? 1 : (orientation == 0 ? 0 : -1);  // 2: CTA pairs, 0: single-CTA tiles
+  if (orientation == 2 && epilogue == kEpiBiasResidF32 && split_k > 1) {  // K splits of a pair tile (reduce-add)
+    g.pair_split = split_k;
+    g.split_k = 1;
+  }
   g.pdl = 0;
   return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));
 }

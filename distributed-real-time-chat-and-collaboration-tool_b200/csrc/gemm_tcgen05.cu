@@ -1019,6 +1019,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const int num_n = (args.b_rows + kPairN - 1) / kPairN;
   const int num_tiles = num_m2 * num_n;
   const int num_kb = args.k_blocks_total;
+  // Work item = (tile, K split). The residual epilogue adds into the output (TMA reduce-add), so a tile's
+  // K range can be cut into several items at no extra pass: with 96 tiles on 74 CTA pairs, three items per
+  // tile make four short waves out of two long ones. Items are ordered split-major, so the adds into one
+  // output tile are far apart in time. Other epilogues run with one split.
+  const int kb_per = args.k_blocks_per_split;
+  const int n_split = (num_kb + kb_per - 1) / kb_per;
+  const int num_items = num_tiles * n_split;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
@@ -1053,9 +1060,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (lane == 0) {
       pdl_wait();
       int it = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile += n_clusters) {
+      for (int item = cluster_id; item < num_items; item += n_clusters) {
+        const int tile = item % num_tiles, ks = item / num_tiles;
         const int m2 = tile % num_m2, n_blk = tile / num_m2;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int kb_end = min(num_kb, (ks + 1) * kb_per);
+        for (int kb = ks * kb_per; kb < kb_end; ++kb, ++it) {
           const int stage = it % kPairStages;
           const uint32_t phase = static_cast<uint32_t>(it / kPairStages) & 1u;
           mbar_wait(&empty_bar[stage], phase ^ 1u);
@@ -1076,11 +1085,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       constexpr uint32_t idesc = umma_idesc_bf16(2 * kBlockM, kPairN);
       int it = 0, astage = 0;
       uint32_t aphase = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile += n_clusters) {
+      for (int item = cluster_id; item < num_items; item += n_clusters) {
+        const int kb_begin = (item / num_tiles) * kb_per;
+        const int kb_end = min(num_kb, kb_begin + kb_per);
         mbar_wait(&tmem_empty_bar[astage], aphase ^ 1u);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(astage * kPairN);
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const int stage = it % kPairStages;
           const uint32_t phase = static_cast<uint32_t>(it / kPairStages) & 1u;
           mbar_wait(&full_bar[stage], phase);
@@ -1091,7 +1102,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             umma_bf16_ss_pair(tmem_d, desc_a + static_cast<uint64_t>(k * 2), desc_b + static_cast<uint64_t>(k * 2),
-                              idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                              idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
           }
           umma_commit_pair(&empty_bar[stage]);
         }
@@ -1111,7 +1122,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     int astage = 0, epi_box = 0;
     uint32_t aphase = 0;
     pdl_wait();
-    for (int tile = cluster_id; tile < num_tiles; tile += n_clusters) {
+    for (int item = cluster_id; item < num_items; item += n_clusters) {
+      const int tile = item % num_tiles;
+      const bool with_bias = args.bias != nullptr && item < num_tiles;  // the first K split adds the bias
       const int m2 = tile % num_m2, n_blk = tile / num_m2;
       mbar_wait(&tmem_full_bar[astage], aphase);
       tc_fence_after();
@@ -1134,7 +1147,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           for (int j = 0; j < 32; j += 8) {
             float v[8];
             float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
-            if (args.bias != nullptr && f0 + j + 7 < args.b_rows) {
+            if (with_bias && f0 + j + 7 < args.b_rows) {
               b0 = __ldg(reinterpret_cast<const float4*>(args.bias + f0 + j));
               b1 = __ldg(reinterpret_cast<const float4*>(args.bias + f0 + j + 4));
             }
@@ -1528,13 +1541,35 @@ int launch_pair(const GemmArgs& g, cudaStream_t stream) {
   ka.a_rows = g.tokens;
   ka.b_rows = g.features;
   ka.k_blocks_total = g.k / kBlockK;
-  ka.k_blocks_per_split = ka.k_blocks_total;
   ka.ld_out = g.ld_out;
   ka.tokens = g.tokens;
   ka.stages = kPairStages;
   const int num_tiles = ((g.tokens + 2 * kBlockM - 1) / (2 * kBlockM)) * ((g.features + kPairN - 1) / kPairN);
   const int max_clusters = num_sms() / 2;
-  const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
+  // K splits of a tile (residual epilogue only: its reduce-add needs no extra pass). Cost model: waves of
+  // work items x (k-blocks per item + 12: the fill, and every item sends its whole fp32 tile through the
+  // L2 adders again); an item keeps at least 12 k-blocks. GPT-2 small, 8192 tokens, MLP down-projection
+  // (96 tiles on 74 CTA pairs, 48 k-blocks): two waves become three of half the length; GPT-2 medium
+  // (256 tiles: 3.46 waves) stays unsplit -- measured 12.32 vs 12.37 ms per prefill with two splits.
+  int split = 1;
+  if (EPI == kEpiBiasResidF32 && g.pair_split > 1) {
+    split = g.pair_split < ka.k_blocks_total ? g.pair_split : ka.k_blocks_total;  // forced (tests, sweeps)
+  } else if (EPI == kEpiBiasResidF32 && g.pair_split < 0) {
+    int best = 1 << 30;
+    for (int s = 1; s <= 8; ++s) {
+      if (s > 1 && ka.k_blocks_total / s < 12) break;
+      const int per = (ka.k_blocks_total + s - 1) / s;
+      const int waves = (num_tiles * s + max_clusters - 1) / max_clusters;
+      const int cost = waves * (per + 12);
+      if (cost < best) {
+        best = cost;
+        split = s;
+      }
+    }
+  }
+  ka.k_blocks_per_split = (ka.k_blocks_total + split - 1) / split;
+  const int num_items = num_tiles * ((ka.k_blocks_total + ka.k_blocks_per_split - 1) / ka.k_blocks_per_split);
+  const int clusters = num_items < max_clusters ? num_items : max_clusters;
 
   auto kernel = gemm_pair_kernel<EPI>;
   static bool attr_set[64] = {};

@@ -48,6 +48,10 @@ struct GemmArgs {
   // large enough, 0 = never, 1 = always when legal. Zero-initialised structs get "never"; the
   // engine and the op-level ABI pass -1.
   int use_pair;
+  // CTA pairs with the residual epilogue (out += act . w^T + bias by TMA reduce-add): K splits per output
+  // tile. 0 / 1 = one (every output element receives ONE add: bit-reproducible), -1 = chosen by the wave
+  // cost model, n > 1 = forced. With splits the fp32 adds of a tile land in no fixed order.
+  int pair_split;
   // swap-AB launches whose CTAs keep all their k-blocks in the ring copy the activation operand
   // with ordinary loads; 1 forces the TMA path for it (A/B comparisons, tests)
   int act_via_tma;

@@ -1,4 +1,6 @@
-"""Prefill time of a workload under the tune build's B200LLM_PREFILL_ATTN switch (0 tcgen05, 1 mma.sync, -1 auto)."""
+"""Prefill time of a workload under the tune build's switches: B200LLM_PREFILL_ATTN (0 tcgen05, 1 mma.sync,
+-1 auto) or, with PROBE=pair_split, B200LLM_PAIR_SPLIT (K splits of the residual pair GEMMs: 1 none, -1 by
+the wave model, n forced)."""
 import importlib
 import os
 import sys
@@ -22,8 +24,10 @@ for workload in sys.argv[1:] or ["smart_reply_b64"]:
     prompts = np.random.default_rng(0).integers(0, shape.vocab_size - 1, size=(B, T), dtype=np.int32)
     stream = torch.cuda.Stream()
     chunk = max(1, min(B, 16384 // T))
-    for mode in ("0", "1", "-1"):
-        os.environ["B200LLM_PREFILL_ATTN"] = mode
+    knob, modes = ("B200LLM_PAIR_SPLIT", ("1", "-1", "2", "3", "4")) if os.environ.get("PROBE") == "pair_split" \
+        else ("B200LLM_PREFILL_ATTN", ("0", "1", "-1"))
+    for mode in modes:
+        os.environ[knob] = mode
         eng = E.Engine(shape, blob, max_seqs=B, max_seq_len=T + N, max_batch_tokens=min(B * T, 16384), max_new_tokens=N)
         eng.set_stream(stream.cuda_stream)
         best = 1e9

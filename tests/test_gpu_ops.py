@@ -48,21 +48,26 @@ def test_gemm_bias_bf16(ops, cuda, tokens, features, k, orientation):
     assert err <= 2e-3 * scale + 2 ** -8 * scale, (err, scale)
 
 
-@pytest.mark.parametrize("tokens,features,k,epi", [
-    (8192, 2304, 768, "bias"),    # BASELINE config 2 prefill QKV: 288 pair tiles, persistent clusters
-    (512, 3072, 768, "gelu"),
-    (640, 768, 3072, "resid"),    # TMA reduce-add into the fp32 residual stream
-    (300, 768, 768, "resid"),     # ragged: the second CTA of the last pair has only out-of-range rows
-    (129, 1024, 1024, "bias"),
+@pytest.mark.parametrize("tokens,features,k,epi,split", [
+    (8192, 2304, 768, "bias", 1),    # BASELINE config 2 prefill QKV: 288 pair tiles, persistent clusters
+    (512, 3072, 768, "gelu", 1),
+    (640, 768, 3072, "resid", 1),    # TMA reduce-add into the fp32 residual stream
+    (300, 768, 768, "resid", 1),     # ragged: the second CTA of the last pair has only out-of-range rows
+    (129, 1024, 1024, "bias", 1),
+    (8192, 768, 3072, "resid", 3),   # config 2 MLP down-projection: 96 tiles x 3 K splits = 288 work items
+    (640, 768, 3072, "resid", 4),
+    (300, 1024, 4096, "resid", 2),   # ragged rows with K splits (the bias is added by the first split only)
+    (1000, 768, 3072, "resid", 5),   # a split count that does not divide the 48 k-blocks (10, 10, 10, 10, 8)
 ])
-def test_gemm_cta_pair_umma(ops, cuda, tokens, features, k, epi):
-    """tcgen05.mma.cta_group::2: two CTAs share one 256 x 256 tile (orientation code 2)."""
+def test_gemm_cta_pair_umma(ops, cuda, tokens, features, k, epi, split):
+    """tcgen05.mma.cta_group::2: two CTAs share one 256 x 256 tile (orientation code 2). `split` > 1: the K
+    range of a tile is cut into work items whose partial products meet in the TMA reduce-add."""
     act, w, bias = _gemm_inputs(tokens, features, k, cuda, seed=8)
     ref = act.float() @ w.float().t() + bias
     if epi == "resid":
         resid = torch.randn(tokens, features, device=cuda)
         out = resid.clone()
-        ops.gemm(act, w, bias, out, ops.EPI_BIAS_RESID_F32, orientation=2)
+        ops.gemm(act, w, bias, out, ops.EPI_BIAS_RESID_F32, split_k=split, orientation=2)
         ref, got = ref + resid, out
     else:
         out = torch.zeros(tokens, features, dtype=torch.bfloat16, device=cuda)
