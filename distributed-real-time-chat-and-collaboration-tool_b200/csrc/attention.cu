@@ -925,7 +925,8 @@ decode_attn_stream_kernel(const __grid_constant__ CUtensorMap map_k, const __gri
   __syncwarp();
 
   // this warp's units: a contiguous range, ordered (row, split, head) so neighbours share the row's data
-  const long long total = static_cast<long long>(a.batch) * a.n_splits * a.n_head;
+  const int live = a.n_live != nullptr ? min(*a.n_live, a.batch) : a.batch;
+  const long long total = static_cast<long long>(live) * a.n_splits * a.n_head;
   const long long gw = static_cast<long long>(blockIdx.x) * kStreamWarps + warp;
   const long long n_gw = static_cast<long long>(gridDim.x) * kStreamWarps;
   const int u_begin = static_cast<int>(gw * total / n_gw);

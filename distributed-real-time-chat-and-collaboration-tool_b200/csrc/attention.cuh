@@ -92,6 +92,10 @@ struct DecodeAttnArgs {
   // at zero by every launch; the split of a (row, head) that finishes last merges them in the kernel.
   // Null: decode_combine_kernel is launched instead.
   int32_t* split_counters;
+  // Streaming form: device int with the number of rows that hold a sequence (they are the first rows of
+  // the batch); null = all `batch` rows. The units of the padding rows are then not handed out at all,
+  // so a partly filled bucket still spreads over every SM.
+  const int32_t* n_live;
 };
 // One decode step of attention: appends this token's K/V to its pages, then attends over
 // positions 0..seq_len (inclusive).

@@ -225,6 +225,7 @@ struct b200llm_engine {
   size_t attn_scratch_floats = 0;
   int32_t *ids_dev = nullptr, *row_pos = nullptr, *row_slot = nullptr, *cu_dev = nullptr,
           *slots_dev = nullptr, *last_rows = nullptr, *active_dev = nullptr, *status_dev = nullptr;
+  int32_t* live_count_dev = nullptr;  // rows of the active set that hold a sequence (they come first)
   SlotInit* init_dev = nullptr;
 
   // pinned staging
@@ -500,6 +501,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       a.cluster_combine = (!p.attn_stream && p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
       a.stream_kernel = p.attn_stream ? p.attn_stream_instance : 0;
       a.n_pages = static_cast<int>(e->n_pages);
+      a.n_live = e->live_count_dev;
       a.split_counters = (p.attn_stream && e->tune_attn_merge) ? e->attn_counters : nullptr;
       if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
       if (p.attn_splits > 1 && a.split_counters == nullptr && !(a.cluster_combine && p.attn_splits <= 8)) {
@@ -579,6 +581,7 @@ int run_stack(b200llm_engine* e, const StepPlan& p) {
       a.cluster_combine = (!p.attn_stream && p.live_rows * e->H * p.attn_splits <= 2 * e->sm_count) ? 1 : 0;
       a.stream_kernel = p.attn_stream ? p.attn_stream_instance : 0;
       a.n_pages = static_cast<int>(e->n_pages);
+      a.n_live = e->live_count_dev;
       a.split_counters = (p.attn_stream && e->tune_attn_merge) ? e->attn_counters : nullptr;
       if (!(e->skip_mask & kSkipAttn)) B200_PROPAGATE(count(e, decode_attention(a, e->stream)));
       if (p.attn_splits > 1 && a.split_counters == nullptr && !(a.cluster_combine && p.attn_splits <= 8)) {
@@ -1156,7 +1159,8 @@ int b200llm_engine_create(const b200llm_config* cfg, const float* weights_host, 
   E_TRY(dev_alloc_t(e.get(), &e->cu_dev, S + 1));
   E_TRY(dev_alloc_t(e.get(), &e->slots_dev, S));
   E_TRY(dev_alloc_t(e.get(), &e->last_rows, S));
-  E_TRY(dev_alloc_t(e.get(), &e->active_dev, static_cast<size_t>(dec_rows)));
+  E_TRY(dev_alloc_t(e.get(), &e->active_dev, static_cast<size_t>(dec_rows) + 1));  // [dec_rows]: live row count
+  e->live_count_dev = e->active_dev + dec_rows;
   E_TRY(dev_alloc_t(e.get(), &e->status_dev, 2 * S));
   E_TRY(dev_alloc_t(e.get(), &e->init_dev, S));
   E_TRY(dev_alloc_t(e.get(), &e->prefix_dev, S));
@@ -1445,9 +1449,12 @@ int b200llm_decode(b200llm_engine* e, const int32_t* slots, int32_t batch, int32
   std::copy(slots, slots + batch, active.begin());
   if (active != e->active_host) {
     B200_PROPAGATE(wait_pinned_free(e));
-    B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(bucket)));
+    B200_PROPAGATE(ensure_pinned(e, static_cast<size_t>(bucket) + 1));
     std::memcpy(e->pin_i32, active.data(), bucket * sizeof(int32_t));
+    e->pin_i32[bucket] = batch;
     B200_CUDA_OK(cudaMemcpyAsync(e->active_dev, e->pin_i32, bucket * sizeof(int32_t),
+                                 cudaMemcpyHostToDevice, st));
+    B200_CUDA_OK(cudaMemcpyAsync(e->live_count_dev, e->pin_i32 + bucket, sizeof(int32_t),
                                  cudaMemcpyHostToDevice, st));
     B200_PROPAGATE(mark_pinned_used(e));
     e->active_host = active;

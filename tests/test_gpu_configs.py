@@ -147,3 +147,43 @@ def test_config4_large_32_rows(cuda):
     w = O.synthetic_weights(shape, seed=0)
     ids = O.synthetic_prompts(32, 64, seed=33)
     _run_both_ways(shape, w, ids, 36, [0, 11, 22, 31], "large rows=32 T=64")
+
+
+def test_streaming_attention_ragged_padded_finished_rows(cuda):
+    """The streaming decode attention (the engine picks it by KV volume) in the situations the BASELINE
+    shapes above never produce together: 40 live rows in the 64-row bucket (24 padding rows), ragged
+    contexts of 300..520 tokens (tiles of 32 with ragged last pages, page lists longer than one tile),
+    and rows that reach their own max_new_tokens early and stay in the batch as finished rows (no KV
+    append) while the others go on. Checked rows -- finished and unfinished ones -- against the oracle,
+    teacher-forced with the engine's tokens, one row at a time (ragged prompts)."""
+    shape = O.SMALL
+    w = O.synthetic_weights(shape, seed=0)
+    B, N = 40, 14
+    lens = [300 + (37 * i) % 221 for i in range(B)]
+    prompts = [O.synthetic_prompts(1, L, seed=100 + i)[0] for i, L in enumerate(lens)]
+    new = [4 if i % 3 == 0 else N for i in range(B)]          # every third row stops after 4 tokens
+    cap = max(lens) + N
+    eng, E = _engine(shape, w, max_seqs=B, max_seq_len=cap, max_batch_tokens=16384, max_new_tokens=N)
+    sps = [E.SamplingParams(max_new_tokens=n, min_new_tokens=n) for n in new]
+    slots = [eng.seq_alloc(cap) for _ in range(B)]
+    c0 = 0
+    while c0 < B:  # prompts packed into calls of at most 16384 tokens
+        c1, tok = c0, 0
+        while c1 < B and tok + lens[c1] <= 16384:
+            tok += lens[c1]
+            c1 += 1
+        eng.prefill([p.tolist() for p in prompts[c0:c1]], slots[c0:c1], sps[c0:c1])
+        c0 = c1
+    eng.decode(slots, N - 1)
+    got = [eng.read_tokens(s) for s in slots]
+    eng.close()
+    for i in range(B):
+        assert len(got[i][0]) == new[i] and got[i][1], (i, len(got[i][0]), new[i])
+    for r in (0, 1, 3, 8, 20, 39):  # rows 0, 3, 39 finish early
+        n = new[r]
+        teacher = torch.tensor([got[r][0]]).long()
+        ref_tok, _, margins = O.greedy_generate(shape, w, prompts[r][None], n, min_new_tokens=n, teacher=teacher)
+        agree = (teacher == ref_tok).numpy()
+        decisive = margins.numpy() > 2 * LOGIT_TOL
+        assert agree[decisive].all(), f"row {r} (context {lens[r]}): token differs from the oracle at a decisive margin"
+        assert agree.mean() >= 0.9, f"row {r}: agreement {agree.mean():.2f}"
