@@ -31,14 +31,16 @@ stream = torch.cuda.Stream()
 chunk = max(1, min(B, 16384 // T))
 SP = E.SamplingParams(N, N)
 steps = min(N - 1, 63)
-KNOBS = ("B200LLM_ATTN_STREAM", "B200LLM_ATTN_SPLITS", "B200LLM_ATTN_MERGE", "B200LLM_SKIP")
+KNOBS = ("B200LLM_ATTN_STREAM", "B200LLM_ATTN_SPLITS", "B200LLM_ATTN_MERGE", "B200LLM_SKIP", "B200LLM_FUSED_QKV",
+         "B200LLM_LNQKV_SPLIT", "B200LLM_LNUP_SPLIT", "B200LLM_FUSED_SPLITS", "REDUCE")
 
 
 def run(env: dict):
     for k in KNOBS:
         os.environ.pop(k, None)
     os.environ.update(env)
-    eng = E.Engine(shape, blob, max_seqs=B, max_seq_len=T + N, max_batch_tokens=min(B * T, 16384), max_new_tokens=N)
+    eng = E.Engine(shape, blob, max_seqs=B, max_seq_len=T + N, max_batch_tokens=min(B * T, 16384), max_new_tokens=N,
+                   decode_reduce=int(os.environ.get("REDUCE", "0")))  # REDUCE=3 in a case: the fused decode layer forced
     eng.set_stream(stream.cuda_stream)
     best = 1e9
     toks = None
