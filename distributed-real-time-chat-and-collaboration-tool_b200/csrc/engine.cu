@@ -1877,9 +1877,10 @@ int b200llm_op_gemm(const void* act, const void* w, const float* bias, void* out
   g.act_rows_alloc = tokens;
   g.force_orientation = orientation == 2 ? 0 : orientation;
   g.use_pair = orientation == 2 ? 1 : (orientation == 0 ? 0 : -1);  // 2: CTA pairs, 0: single-CTA tiles
-  if (orientation == 2 && epilogue == kEpiBiasResidF32 && split_k > 1) {  // K splits of a pair tile (reduce-add)
-    g.pair_split = split_k;
+  if (orientation == 2 && epilogue == kEpiBiasResidF32 && (split_k > 1 || split_k == -1)) {
+    g.pair_split = split_k;  // K splits of a pair tile (reduce-add): a count, or -1 = by the wave model
     g.split_k = 1;
+    g.cluster_split = 0;
   }
   g.pdl = 0;
   return gemm_bf16(g, reinterpret_cast<cudaStream_t>(stream));

@@ -231,7 +231,9 @@ int64_t b200llm_kernel_launches(const b200llm_engine* engine);
  *          small batches), 2 tokens on UMMA-M with CTA pairs (tcgen05 cta_group::2, 256x256 tiles).
  * split_k: 1 = none; n > 1 = n partial planes (B200LLM_EPI_PARTIAL_F32 only, the consumer reduces);
  *          -n = split K over a thread-block cluster of n CTAs (n <= 8) reduced on chip through
- *          distributed shared memory, with the normal bias / gelu / residual epilogue. */
+ *          distributed shared memory, with the normal bias / gelu / residual epilogue.
+ *          With CTA pairs and B200LLM_EPI_BIAS_RESID_F32: n > 1 = a tile's K range cut into n work
+ *          items whose products meet in the TMA reduce-add, -1 = that count by the wave cost model. */
 int b200llm_op_gemm(const void* act_dev, const void* w_dev, const float* bias_dev, void* out_dev,
                     int32_t tokens, int32_t features, int32_t k, int32_t ld_out, int32_t epilogue,
                     int32_t split_k, int32_t orientation, void* stream);

@@ -58,6 +58,7 @@ def test_gemm_bias_bf16(ops, cuda, tokens, features, k, orientation):
     (640, 768, 3072, "resid", 4),
     (300, 1024, 4096, "resid", 2),   # ragged rows with K splits (the bias is added by the first split only)
     (1000, 768, 3072, "resid", 5),   # a split count that does not divide the 48 k-blocks (10, 10, 10, 10, 8)
+    (4096, 768, 3072, "resid", -1),  # the split count by the wave model (what the engine passes)
 ])
 def test_gemm_cta_pair_umma(ops, cuda, tokens, features, k, epi, split):
     """tcgen05.mma.cta_group::2: two CTAs share one 256 x 256 tile (orientation code 2). `split` > 1: the K
