@@ -42,6 +42,7 @@ WORKLOADS = {
     "probe_b32": ("small", 32, 128, 32),
     "probe_b48": ("small", 48, 128, 32),
     "probe_long_ctx": ("small", 64, 512, 64),         # profiling probe: contexts like the byte-level gRPC stream
+    "probe_ctx96": ("small", 64, 96, 32),             # one 128-row pass of the decode attention kernel
     "probe_ctx256": ("small", 64, 256, 64),           # profiling probes: where the streaming decode attention takes over
     "probe_ctx192": ("small", 64, 192, 64),
     "probe_large_b32_ctx256": ("large", 32, 256, 64),
