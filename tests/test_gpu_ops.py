@@ -313,6 +313,53 @@ def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, mode):
         assert torch.equal(v_pool[p, :, L % page], cur[2])
 
 
+@pytest.mark.parametrize("seed", range(12))
+def test_decode_attention_kernels_agree_on_random_shapes(ops, cuda, seed):
+    """The two decode attention kernels (one CTA per unit / persistent warps with TMA tiles) on random row
+    counts, head counts, ragged contexts and split counts: each against the fp32 reference, and the K/V
+    append of both. Contexts are drawn around the tile, page and pass boundaries as well as uniformly."""
+    g = torch.Generator(device="cpu").manual_seed(1000 + seed)
+    n_head = [12, 16, 20][seed % 3]
+    B = int(torch.randint(1, 41, (1,), generator=g))
+    edges = torch.tensor([0, 1, 15, 16, 17, 31, 32, 33, 127, 128, 129, 159, 160, 161, 255, 256, 257, 511, 512, 513])
+    ctx = [int(edges[int(torch.randint(0, len(edges), (1,), generator=g))]) if int(torch.randint(0, 2, (1,), generator=g))
+           else int(torch.randint(0, 700, (1,), generator=g)) for _ in range(B)]
+    n_splits = [1, 1, 2, 3, 5, 8][int(torch.randint(0, 6, (1,), generator=g))]
+    d, page = n_head * 64, 16
+    max_pages = (max(ctx) + 1 + page - 1) // page
+    n_pages = B * max_pages + 7
+    page_table = torch.randperm(n_pages, generator=g)[: B * max_pages].int().view(B, max_pages).contiguous().to(cuda)
+    k0 = torch.zeros(n_pages, n_head, page, 64, dtype=torch.bfloat16, device=cuda)
+    v0 = torch.zeros_like(k0)
+    ks, vs = [], []
+    for b, L in enumerate(ctx):
+        k = (torch.randn(L, n_head, 64, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+        v = (torch.randn(L, n_head, 64, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+        ks.append(k)
+        vs.append(v)
+        if L:
+            pos = torch.arange(L, device=cuda)
+            pg = page_table[b, (pos // page).long()].long()
+            k0[pg, :, (pos % page).long()] = k
+            v0[pg, :, (pos % page).long()] = v
+    qkv = (torch.randn(B, 3 * d, generator=g) * 0.8).to(torch.bfloat16).to(cuda)
+    seq_len = torch.tensor(ctx, dtype=torch.int32, device=cuda)
+    outs = []
+    for streaming in (False, True):
+        kp, vp = k0.clone(), v0.clone()
+        out = ops.decode_attention(qkv, seq_len, page_table, kp, vp, n_head, n_splits, streaming=streaming)
+        torch.cuda.synchronize()
+        outs.append(out)
+        for b, L in enumerate(ctx):
+            cur = qkv[b].view(3, n_head, 64)
+            ref = _ref_attention(cur[0][None], torch.cat([ks[b], cur[1][None]], 0),
+                                 torch.cat([vs[b], cur[2][None]], 0)).reshape(d)
+            assert (out[b].float() - ref).abs().max().item() <= 2e-2, (streaming, b, L, n_splits)
+            p = page_table[b, L // page].item()
+            assert torch.equal(kp[p, :, L % page], cur[1]) and torch.equal(vp[p, :, L % page], cur[2])
+    assert (outs[0].float() - outs[1].float()).abs().max().item() <= 2e-2
+
+
 @pytest.mark.parametrize("prefix_suffix,n_head", [
     ([(0, 40), (64, 1), (16, 100), (496, 130)], 12),    # no prefix / one token / ragged tiles / long prefix
     ([(1008, 16), (32, 33)], 16),                       # Summarize-like: almost everything cached
