@@ -257,6 +257,8 @@ def test_prefill_attention(ops, cuda, lens, n_head):
     ([40, 500], 12, 3),
     ([1100, 3, 64, 700], 16, 16),
     ([300, 299], 20, 2),
+    ([3000, 2047, 1], 12, 8),      # several page-list refills per split (> 512 tokens each)
+    ([4100, 4095], 12, 16),        # beyond the 256 page ids one CTA stages in shared memory
 ])
 @pytest.mark.parametrize("mode", ["scratch-combine", "cluster-combine", "streaming", "streaming-merge"])
 def test_decode_attention_paged(ops, cuda, ctx_lens, n_head, n_splits, mode):
