@@ -23,7 +23,7 @@ for workload in sys.argv[1:] or ["smart_reply_b64"]:
     blob = W.synthetic_blob(shape)
     prompts = np.random.default_rng(0).integers(0, shape.vocab_size - 1, size=(B, T), dtype=np.int32)
     stream = torch.cuda.Stream()
-    chunk = max(1, min(B, 16384 // T))
+    chunk = int(os.environ.get("CHUNK", 0)) or max(1, min(B, 16384 // T))  # sequences per prefill call
     knob, modes = ("B200LLM_PAIR_SPLIT", ("1", "-1", "2", "3", "4")) if os.environ.get("PROBE") == "pair_split" \
         else ("B200LLM_PREFILL_ATTN", ("0", "1", "-1"))
     for mode in modes:
